@@ -1,0 +1,237 @@
+"""Batched entry point `schedule_batch` and the lifting of device records back to reference-shaped results.
+
+`schedule_batch(batch, algo_mask)` replaces, for every DAG instance and algorithm, the reference sequence
+  scheduler = XScheduler(nodes); [scheduler.add_task(t) ...]; schedule = scheduler.schedule()
+  makespan, stats = evaluator.simulate_execution(scheduler, schedule)
+(ref simulation.py:320-336) with one call into the CUDA library. PyTorch is used only for device buffers,
+pinned staging and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+from .lowering import DagBatch, _FIELDS_ALL
+
+
+def algos_of(mask: int) -> List[int]:
+    return [a for a in range(N.NUM_ALGOS) if mask & (1 << a)]
+
+
+@dataclass
+class ResultArrays:
+    """Host (numpy) image of dls_result_t for `algos` (slot order)."""
+    algos: List[int]
+    node_of: np.ndarray   # i8  [A, NT]
+    seq_pos: np.ndarray   # u16 [A, NT]
+    summary: np.ndarray   # structured [A, B]
+    fin: np.ndarray       # f64 [A, NK]
+    cnt: np.ndarray       # i32 [A, NK]
+    avail: np.ndarray     # f64 [A, NK]
+    peak: Optional[np.ndarray]    # f64 [A, NK]
+    cached: Optional[np.ndarray]  # u32 [A, NP]
+
+    @classmethod
+    def empty(cls, batch: DagBatch, mask: int, peak: bool = True, cached: bool = True) -> "ResultArrays":
+        al = algos_of(mask)
+        A = len(al)
+        return cls(
+            algos=al, node_of=np.full((A, batch.nt_inst), N.TASK_PENDING, np.int8),
+            seq_pos=np.full((A, batch.nt_inst), N.SEQ_NONE, np.uint16),
+            summary=np.zeros((A, batch.B), np.dtype(N.SUMMARY_DTYPE)), fin=np.zeros((A, batch.nk_inst), np.float64),
+            cnt=np.zeros((A, batch.nk_inst), np.int32), avail=np.zeros((A, batch.nk_inst), np.float64),
+            peak=np.zeros((A, batch.nk_inst), np.float64) if peak else None,
+            cached=np.zeros((A, batch.np_inst), np.uint32) if cached else None)
+
+    def slot(self, algo: int) -> int:
+        return self.algos.index(algo)
+
+    def host_struct(self) -> N.DlsResult:
+        r = N.DlsResult()
+        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail", "peak", "cached"):
+            a = getattr(self, f)
+            setattr(r, f, None if a is None else a.ctypes.data)
+        return r
+
+
+# ---- lifting (SURVEY.md section 8a' "RESULT LIFT") ---------------------------------------------------------
+
+def sequence_of(batch: DagBatch, res: ResultArrays, slot: int, b: int):
+    """(task indices in assignment order, their node indices) of instance b."""
+    ts = batch.task_slice(b)
+    node_of = res.node_of[slot, ts]
+    seq_pos = res.seq_pos[slot, ts]
+    done = np.nonzero(node_of >= 0)[0]
+    order = done[np.argsort(seq_pos[done], kind="stable")]
+    return order, node_of[order]
+
+
+def schedule_dict(batch: DagBatch, res: ResultArrays, slot: int, b: int, task_names: Sequence[str],
+                  node_ids: Sequence[str]) -> Dict[str, List[str]]:
+    """The dict `schedule()` returns: node id -> task ids in assignment order, keys in order of first
+    assignment, nodes without tasks absent (ref schedulers.py:156,196,208)."""
+    order, nodes = sequence_of(batch, res, slot, b)
+    out: Dict[str, List[str]] = {}
+    for i, k in zip(order.tolist(), nodes.tolist()):
+        out.setdefault(node_ids[k], []).append(task_names[i])
+    return out
+
+
+# ---- device path -----------------------------------------------------------------------------------------
+
+def _torch():
+    import torch
+    return torch
+
+
+_NP_VIEW = {np.dtype(np.uint16): np.int16, np.dtype(np.uint32): np.int32}
+
+
+def _to_torch_host(a: np.ndarray, pin: bool):
+    torch = _torch()
+    a = np.ascontiguousarray(a)
+    v = a.view(_NP_VIEW.get(a.dtype, a.dtype))
+    t = torch.from_numpy(v)
+    if pin and t.numel() > 0:
+        t = t.pin_memory()
+    return t
+
+
+class DeviceBatch:
+    """dls_batch_t whose arrays live in HBM (torch tensors keep them alive)."""
+
+    def __init__(self, host: DagBatch, device, non_blocking: bool = True, pinned: Optional[dict] = None):
+        torch = _torch()
+        if not torch.cuda.is_available():
+            raise RuntimeError("no CUDA device: the scheduling path has no CPU implementation")
+        self.host = host.validate()
+        self.device = torch.device(device)
+        self.tensors = {}
+        self.h2d_bytes = 0
+        for f in _FIELDS_ALL:
+            a = getattr(host, f)
+            if a is None:
+                continue
+            src = pinned[f] if pinned is not None else _to_torch_host(a, pin=False)
+            self.tensors[f] = src.to(self.device, non_blocking=non_blocking)
+            self.h2d_bytes += src.numel() * src.element_size()
+        self.struct = host.as_struct(lambda f, a: self.tensors[f].data_ptr())
+
+
+def pin_batch(host: DagBatch) -> dict:
+    """Pinned host staging copies of a batch's arrays (for timed host->device transfers)."""
+    return {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL if getattr(host, f) is not None}
+
+
+class BatchResult:
+    """Device-resident outputs of one `schedule_batch` call; `.host()` brings them back as ResultArrays."""
+
+    def __init__(self, batch: DagBatch, mask: int, device, peak: bool, cached: bool):
+        torch = _torch()
+        self.batch, self.mask, self.algos = batch, mask, algos_of(mask)
+        A = len(self.algos)
+        dev = device
+        self.node_of = torch.empty((A, batch.nt_inst), dtype=torch.int8, device=dev)
+        self.seq_pos = torch.empty((A, batch.nt_inst), dtype=torch.int16, device=dev)
+        self.summary = torch.empty((A, batch.B, N.SUMMARY_BYTES), dtype=torch.uint8, device=dev)
+        self.fin = torch.empty((A, batch.nk_inst), dtype=torch.float64, device=dev)
+        self.cnt = torch.empty((A, batch.nk_inst), dtype=torch.int32, device=dev)
+        self.avail = torch.empty((A, batch.nk_inst), dtype=torch.float64, device=dev)
+        self.peak = torch.empty((A, batch.nk_inst), dtype=torch.float64, device=dev) if peak else None
+        self.cached = torch.empty((A, batch.np_inst), dtype=torch.int32, device=dev) if cached else None
+        r = N.DlsResult()
+        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail", "peak", "cached"):
+            t = getattr(self, f)
+            setattr(r, f, None if t is None else t.data_ptr())
+        self.struct = r
+
+    def summary_host(self) -> np.ndarray:
+        """Only the fixed-size per-instance records (what multi-GPU runs all-gather)."""
+        return self.summary.cpu().numpy().view(np.dtype(N.SUMMARY_DTYPE)).reshape(len(self.algos), self.batch.B)
+
+    def d2h_bytes(self, full: bool = True) -> int:
+        ts = [self.summary] + ([self.node_of, self.seq_pos, self.fin, self.cnt, self.avail] if full else [])
+        if full:
+            ts += [t for t in (self.peak, self.cached) if t is not None]
+        return sum(t.numel() * t.element_size() for t in ts)
+
+    def host(self) -> ResultArrays:
+        A = len(self.algos)
+        return ResultArrays(
+            algos=self.algos, node_of=self.node_of.cpu().numpy(),
+            seq_pos=self.seq_pos.cpu().numpy().view(np.uint16),
+            summary=self.summary_host(), fin=self.fin.cpu().numpy(), cnt=self.cnt.cpu().numpy(),
+            avail=self.avail.cpu().numpy(), peak=None if self.peak is None else self.peak.cpu().numpy(),
+            cached=None if self.cached is None else self.cached.cpu().numpy().view(np.uint32))
+
+
+def workspace_bytes(dev_batch: DeviceBatch, mask: int) -> int:
+    return int(N.load().dls_workspace_bytes(C.byref(dev_batch.struct), mask))
+
+
+def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool = True, cached: bool = True,
+                   workspace=None, result: Optional[BatchResult] = None) -> BatchResult:
+    """Run the algorithms in `algo_mask` over every instance of `batch` on the GPU.
+
+    `batch` is a host `DagBatch` (copied to HBM here) or an already resident `DeviceBatch`. Work is enqueued
+    on torch's current stream of `device`; the returned BatchResult holds device tensors (synchronise / call
+    `.host()` to read them). Raises DlsError on a library error; infeasible tasks are data, not errors.
+    """
+    torch = _torch()
+    lib = N.load()
+    if not torch.cuda.is_available():
+        raise RuntimeError("no CUDA device: the scheduling path has no CPU implementation")
+    if isinstance(batch, DagBatch):
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        batch = DeviceBatch(batch, device)
+    device = batch.device
+    with torch.cuda.device(device):
+        if result is None:
+            result = BatchResult(batch.host, algo_mask, device, peak, cached)
+        need = int(lib.dls_workspace_bytes(C.byref(batch.struct), algo_mask))
+        if workspace is None or workspace.numel() < need:
+            workspace = torch.empty(max(need, 8), dtype=torch.uint8, device=device)
+        stream = torch.cuda.current_stream(device).cuda_stream
+        rc = lib.dls_schedule_batch(C.byref(batch.struct), C.byref(result.struct), algo_mask, workspace.data_ptr(),
+                                    workspace.numel(), C.c_void_p(stream))
+        N.check(rc)
+    result.workspace = workspace  # keep alive until the stream has run
+    result.dev_batch = batch
+    return result
+
+
+def priorities(batch, device=None):
+    """Kernel P alone: returns dict of numpy arrays depth/outdeg/up/order_dg/order_mru/order_cp."""
+    torch = _torch()
+    lib = N.load()
+    if isinstance(batch, DagBatch):
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        batch = DeviceBatch(batch, device)
+    hb = batch.host
+    dev = batch.device
+    with torch.cuda.device(dev):
+        out = {
+            "depth": torch.empty(hb.nt_topo, dtype=torch.int16, device=dev),
+            "outdeg": torch.empty(hb.nt_topo, dtype=torch.int16, device=dev),
+            "up": torch.empty(hb.nt_inst, dtype=torch.float64, device=dev),
+            "order_dg": torch.empty(hb.nt_topo, dtype=torch.int16, device=dev),
+            "order_mru": torch.empty(hb.nt_topo, dtype=torch.int16, device=dev),
+            "order_cp": torch.empty(hb.nt_inst, dtype=torch.int16, device=dev),
+        }
+        pr = N.DlsPrio()
+        for k, t in out.items():
+            setattr(pr, k, t.data_ptr())
+        need = int(lib.dls_workspace_bytes(C.byref(batch.struct), N.MASK_ALL))
+        ws = torch.empty(max(need, 8), dtype=torch.uint8, device=dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        N.check(lib.dls_priorities(C.byref(batch.struct), C.byref(pr), ws.data_ptr(), ws.numel(), C.c_void_p(stream)))
+        torch.cuda.synchronize(dev)
+    res = {}
+    for k, t in out.items():
+        a = t.cpu().numpy()
+        res[k] = a.view(np.uint16) if a.dtype == np.int16 else a
+    return res

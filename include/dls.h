@@ -1,0 +1,191 @@
+/*
+ * dls.h — C ABI of the B200-native batched DAG list scheduler.
+ *
+ * Drop-in boundary for ONE hot path of 2alaaa/distributed-llm-scheduler: the four
+ * memory-constrained list-scheduling algorithms of schedulers.py run over a batch of
+ * DAG instances, plus the makespan/cache statistics of simulation.py:simulate_execution.
+ * (All file:line citations below are into the reference repository.)
+ *
+ * Everything crossing this boundary is plain pointers and sizes. The library owns no
+ * memory between calls: inputs, outputs and scratch are caller-allocated DEVICE buffers,
+ * borrowed for the duration of the call; work is enqueued on the caller's CUDA stream.
+ * There is no CPU fallback: every entry point that computes needs a CUDA device.
+ *
+ * Lowered representation (what a DAG builder emits; SURVEY.md section 8(a')):
+ *   tasks    0..n-1 in add_task order                         (schedulers.py:43-48)
+ *   pred CSR dependencies of each task, in list order          (schedulers.py:14)
+ *   par  CSR distinct params of each task; param id = lexicographic rank of the param
+ *            name inside its DAG (needed by the (score, name) sort, schedulers.py:420)
+ *   rank[i]  position of task i in list(scheduler.pending_tasks) taken after the last
+ *            add_task — CPython set order, the reference's tie-break (schedulers.py:41,58)
+ *   mem,dur  Task.memory_required / Task.compute_time, fp64   (schedulers.py:12-13)
+ *   cap,spd  Node.total_memory / Node.compute_speed, fp64, in the order of the `nodes`
+ *            list given to the scheduler = node tie-break order (schedulers.py:23-25,34)
+ */
+#ifndef DLS_H_
+#define DLS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLS_VERSION 100 /* major*100 + minor */
+
+/* algorithm ids (slot order inside results = increasing id among those requested) */
+#define DLS_ALGO_DFS 0      /* DFSScheduler           schedulers.py:138-208 */
+#define DLS_ALGO_GREEDY 1   /* GreedyScheduler        schedulers.py:211-296 */
+#define DLS_ALGO_CRITICAL 2 /* CriticalPathScheduler  schedulers.py:299-372 */
+#define DLS_ALGO_MRU 3      /* MRUScheduler           schedulers.py:375-525 */
+#define DLS_NUM_ALGOS 4
+#define DLS_MASK_ALL 0xF
+
+/* limits */
+#define DLS_MAX_TASKS 65535  /* task ids are u16; 0xFFFF is the "none" marker */
+#define DLS_MAX_PARAMS 65535 /* param ids are u16 */
+#define DLS_MAX_NODES 32     /* one warp lane per node */
+
+/* error codes (negative); dls_last_error() gives the text for the calling thread */
+#define DLS_OK 0
+#define DLS_ERR_BAD_ARG (-1)   /* null pointer, negative size, inconsistent descriptor */
+#define DLS_ERR_TOO_LARGE (-2) /* n > 65535, K > 32, P > 65535, or per-DAG state exceeds shared memory */
+#define DLS_ERR_WORKSPACE (-3) /* workspace smaller than dls_workspace_bytes() */
+#define DLS_ERR_CUDA (-4)      /* a CUDA runtime call failed (text in dls_last_error) */
+
+/* dls_batch_t.flags (only meaningful when T == 1, i.e. topology shared by all instances) */
+#define DLS_F_DUR_PER_INSTANCE 1 /* dur is [B][n] instead of [n]  (config 3: perturbed durations) */
+#define DLS_F_MEM_PER_INSTANCE 2 /* mem is [B][n] instead of [n] */
+
+/* per-task verdict in node_of[] */
+#define DLS_TASK_FAILED (-1)  /* in scheduler.failed_tasks            (schedulers.py:128-131) */
+#define DLS_TASK_PENDING (-2) /* left in scheduler.pending_tasks      (schedulers.py:172-174) */
+#define DLS_SEQ_NONE 0xFFFFu
+
+/* dls_summary_t.status bits */
+#define DLS_ST_OK 0
+#define DLS_ST_BAD_TOPOLOGY 1 /* dependency cycle or index out of range: instance not scheduled */
+#define DLS_ST_CARRY 2        /* MRU: assign_task_to_node returned False after a node was chosen
+                                 (schedulers.py:82-83,509); the task would be retried next round.
+                                 Not replayed on the device: results of this instance are invalid. */
+
+/*
+ * A batch of B DAG instances over T topologies. T == B: every instance has its own
+ * topology (config 5, the simulation.py sweep). T == 1: one topology shared by all
+ * instances, values optionally per instance (config 3).
+ *
+ * Topology t owns tasks [task_off[t], task_off[t+1]) of the per-task arrays, entries
+ * [pred_off[t], pred_off[t+1]) of pred_idx, [par_off[t], par_off[t+1]) of par_idx and
+ * param ids [pid_off[t], pid_off[t+1]) of the per-param outputs. CSR row pointers are
+ * local to the topology's slice and have n_t+1 entries starting at task_off[t]+t.
+ */
+typedef struct dls_batch {
+  int32_t B;     /* DAG instances */
+  int32_t T;     /* topologies: B or 1 */
+  int32_t n_max; /* max tasks of any topology   (<= DLS_MAX_TASKS) */
+  int32_t K_max; /* max nodes of any instance   (<= DLS_MAX_NODES) */
+  int32_t P_max; /* max distinct params of any topology (<= DLS_MAX_PARAMS) */
+  int32_t E_max; /* max dependency entries of any topology */
+  int32_t R_max; /* max param references of any topology */
+  int32_t flags; /* DLS_F_* */
+  /* totals, known to the caller on the host (the library never reads device memory on the host) */
+  int64_t nt_topo; /* task_off[T]: tasks over all topologies */
+  int64_t nt_inst; /* NT: instance-tasks = T==1 ? B*n : task_off[T] */
+  int64_t e_total; /* pred_off[T] */
+  int64_t r_total; /* par_off[T] */
+  int64_t nk_inst; /* NK: instance-nodes = node_off ? node_off[B] : B*K_max */
+  int64_t np_inst; /* NP: instance-params = T==1 ? B*pid_off[1] : pid_off[T] */
+  const int64_t* task_off; /* [T+1] */
+  const int64_t* pred_off; /* [T+1] */
+  const int64_t* par_off;  /* [T+1] */
+  const int64_t* pid_off;  /* [T+1] */
+  const uint32_t* pred_ptr; /* [task_off[T]+T] */
+  const uint16_t* pred_idx; /* [pred_off[T]]   Task.dependencies             schedulers.py:14 */
+  const uint32_t* par_ptr;  /* [task_off[T]+T] */
+  const uint16_t* par_idx;  /* [par_off[T]]    Task.params_needed            schedulers.py:15 */
+  const uint16_t* rank;     /* [task_off[T]]   pi, set order of pending_tasks schedulers.py:41 */
+  const double* mem;        /* [task_off[T]] or [B*n] with DLS_F_MEM_PER_INSTANCE */
+  const double* dur;        /* [task_off[T]] or [B*n] with DLS_F_DUR_PER_INSTANCE */
+  const int64_t* node_off;  /* [B+1], or NULL: all instances use nodes 0..K_max-1 */
+  const double* cap;        /* Node.total_memory   schedulers.py:23 */
+  const double* spd;        /* Node.compute_speed  schedulers.py:25 */
+} dls_batch_t;
+
+/* Per (algorithm, instance) record. Mirrors what run_single_test reads after schedule()
+ * (simulation.py:336-346) plus simulate_execution's outputs (simulation.py:216-278). */
+typedef struct dls_summary {
+  double makespan;   /* max over nodes of the sequential sum of dur/spd   simulation.py:261-271 */
+  int32_t completed; /* len(scheduler.completed_tasks)                    simulation.py:339 */
+  int32_t failed;    /* len(scheduler.failed_tasks)                       simulation.py:340 */
+  int32_t pending;   /* len(scheduler.pending_tasks) after schedule() */
+  int32_t hits;      /* stats['param_cache_hits']                         simulation.py:253-258 */
+  int32_t misses;    /* stats['param_cache_misses'] */
+  int32_t rounds;    /* iterations of the while loop                      schedulers.py:167 */
+  int32_t status;    /* DLS_ST_* */
+  int32_t reserved;
+} dls_summary_t;
+
+/*
+ * Caller-allocated outputs. Leading dimension A = number of algorithms in algo_mask
+ * (slot s = s-th set bit). NT = batch->nt_inst, NK = batch->nk_inst, NP = batch->np_inst.
+ * Nullable: peak, cached.
+ */
+typedef struct dls_result {
+  int8_t* node_of;        /* [A][NT] node index, DLS_TASK_FAILED or DLS_TASK_PENDING   Task.assigned_node schedulers.py:93 */
+  uint16_t* seq_pos;      /* [A][NT] position in the global assignment sequence, DLS_SEQ_NONE if unassigned */
+  dls_summary_t* summary; /* [A][B] */
+  double* fin;            /* [A][NK] node finish time                       simulation.py:269 */
+  int32_t* cnt;           /* [A][NK] len(node.completed_tasks)              schedulers.py:123 */
+  double* avail;          /* [A][NK] final node.available_memory (bit-exact fp64 replay) schedulers.py:89,95,126 */
+  double* peak;           /* [A][NK] extension, no reference counterpart: max of total-available sampled
+                             between schedulers.py:95 and :126; NULL to skip */
+  uint32_t* cached;       /* [A][NP] bit k set = param cached on node k at the end (Node.cached_params,
+                             schedulers.py:26,88,428); NULL to skip */
+} dls_result_t;
+
+/* Outputs of the priority pass alone (kernel P). All nullable. Per topology-task arrays have
+ * nt_topo entries; per instance-task arrays have nt_inst entries. */
+typedef struct dls_prio {
+  uint16_t* depth;     /* [task_off[T]] DFSScheduler.compute_depth                 schedulers.py:140-152 */
+  uint16_t* outdeg;    /* [task_off[T]] len(task_dependencies[id]) (MRU urgency)   schedulers.py:468-469 */
+  double* up;          /* [NT]          CriticalPathScheduler.compute_critical_path schedulers.py:301-321 */
+  uint16_t* order_dg;  /* [task_off[T]] static processing order for DFS/Greedy: (depth asc, rank asc) */
+  uint16_t* order_mru; /* [task_off[T]] for MRU: (depth asc, outdeg desc, rank asc)  schedulers.py:475 */
+  uint16_t* order_cp;  /* [NT]          for Critical: (depth asc, up desc, rank asc) schedulers.py:343 */
+} dls_prio_t;
+
+/* Library version (DLS_VERSION of the build). */
+int dls_version(void);
+
+/* Text of the last error on the calling thread ("" if none). */
+const char* dls_last_error(void);
+
+/* Bytes of device scratch dls_schedule_batch / dls_priorities need for this batch
+ * (only the scalar fields of the descriptor are read). */
+size_t dls_workspace_bytes(const dls_batch_t* batch, int algo_mask);
+
+/*
+ * Replaces, for every instance b and every algorithm a in algo_mask:
+ *   scheduler = XScheduler(nodes); for t in tasks: scheduler.add_task(t); schedule = scheduler.schedule()
+ *   makespan, stats = evaluator.simulate_execution(scheduler, schedule)
+ * (schedulers.py:154,244,323,444; simulation.py:320-336). All pointers inside batch/result and
+ * `workspace` are device pointers; the structs themselves are host memory. Asynchronous on `cuda_stream`
+ * (a cudaStream_t, NULL = default stream). Returns DLS_OK or a negative DLS_ERR_*; never throws.
+ * Infeasible tasks are data (node_of = -1), not errors, like the reference (schedulers.py:128-131).
+ */
+int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace,
+                       size_t workspace_bytes, void* cuda_stream);
+
+/* Kernel P only: depth / out-degree / upward rank / static processing orders
+ * (compute_depth schedulers.py:140-152, compute_critical_path :301-321, the ready-list sorts :177,:343,:475). */
+int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, size_t workspace_bytes,
+                   void* cuda_stream);
+
+/* Number of kernel launches the library has enqueued since load (for bench accounting). */
+int64_t dls_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLS_H_ */

@@ -1,0 +1,64 @@
+"""Pins the CPU oracle (oracle/dls_oracle.c) to the reference: every golden fixture produced by running the
+unmodified reference (tests/golden/make_golden.py) must be reproduced bit-for-bit — task verdicts, node
+assignment, global assignment order, per-node fp64 state, makespan, cache hits/misses."""
+import numpy as np
+import pytest
+
+import golden_io
+from common import assert_matches_expected
+
+
+@pytest.mark.parametrize("fname", golden_io.ALL_FILES)
+def test_oracle_reproduces_reference_fixtures(oracle_mod, fname):
+    cases = golden_io.load(fname)
+    if not cases:
+        pytest.skip(f"{fname} not generated")
+    # group by algorithm mask so one batched oracle call covers many cases
+    for mask in sorted({c.mask for c in cases}):
+        sub = [c for c in cases if c.mask == mask]
+        batch = golden_io.batch_of(sub)
+        res = oracle_mod.schedule_batch(batch, mask, nthreads=4)
+        for b, c in enumerate(sub):
+            for slot, a in enumerate(res.algos):
+                assert_matches_expected(c.exp[a], batch, res, slot, b, f"{fname}:{c.label} algo={a}")
+
+
+def test_gpt2_paper_numbers():
+    """ref PDF section 6.1/6.2.2 and SURVEY.md 8(c): 99 tasks; MRU on the 4 laptops completes 99/99 with
+    24/28/22/25 tasks per node; DFS/Greedy 66 done, Critical 66 done."""
+    cases = {c.label: c for c in golden_io.load("cfg3_gpt2.npz")}
+    c = cases["gpt2|4laptops"]
+    assert c.n == 99
+    assert c.exp[3]["completed"] == 99 and c.exp[3]["cnt"].tolist() == [24, 28, 22, 25]
+    assert c.exp[0]["completed"] == 66 and c.exp[0]["cnt"].tolist() == [26, 11, 22, 7]
+    assert c.exp[2]["completed"] == 66 and c.exp[2]["cnt"].tolist() == [12, 36, 9, 9]
+    assert abs(c.exp[3]["makespan"] - 1.0375) < 1e-9 and abs(c.exp[2]["makespan"] - 0.675) < 1e-9
+
+
+def test_oracle_priorities_match_definitions(oracle_mod):
+    """depth / upward rank / out-degree and the static orders against direct numpy definitions."""
+    cases = golden_io.load("cfg2_sweep_seed0.npz")[::9] + golden_io.load("cfg3_gpt2.npz")[:1]
+    batch = golden_io.batch_of(cases)
+    pr = oracle_mod.priorities(batch, nthreads=2)
+    for b, c in enumerate(cases):
+        ts = batch.task_slice(b)
+        d = c.dag
+        depth = np.zeros(d.n, np.int64)
+        for _ in range(d.n + 1):
+            for i in range(d.n):
+                ps = d.pred_idx[d.pred_ptr[i]:d.pred_ptr[i + 1]]
+                if len(ps):
+                    depth[i] = 1 + depth[ps].max()
+        np.testing.assert_array_equal(pr["depth"][ts], depth)
+        outdeg = np.bincount(d.pred_idx, minlength=d.n)
+        np.testing.assert_array_equal(pr["outdeg"][ts], outdeg)
+        up = d.dur.copy()
+        for i in sorted(range(d.n), key=lambda i: -depth[i]):
+            succ = [j for j in range(d.n) if i in d.pred_idx[d.pred_ptr[j]:d.pred_ptr[j + 1]]]
+            if succ:
+                up[i] = d.dur[i] + max(up[j] for j in succ)
+        np.testing.assert_array_equal(pr["up"][ts].view(np.uint64), up.view(np.uint64))
+        key = lambda k: sorted(range(d.n), key=lambda i: (depth[i], -k[i], d.rank[i]))
+        assert pr["order_dg"][ts].tolist() == key(np.zeros(d.n))
+        assert pr["order_mru"][ts].tolist() == key(outdeg)
+        assert pr["order_cp"][ts].tolist() == key(up)
