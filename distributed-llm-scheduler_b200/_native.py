@@ -74,8 +74,9 @@ class DlsPrio(C.Structure):
 # Every symbol include/dls.h declares; tests check the built library exports all of them.
 EXPORTED_SYMBOLS = (
     "dls_version", "dls_last_error", "dls_workspace_bytes", "dls_schedule_batch", "dls_priorities",
-    "dls_launch_count",
+    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name",
 )
+NUM_KERNELS = 6
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -138,6 +139,12 @@ def load() -> C.CDLL:
         lib.dls_priorities.restype = C.c_int
         lib.dls_priorities.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsPrio), C.c_void_p, C.c_size_t, C.c_void_p]
         lib.dls_launch_count.restype = C.c_int64
+        lib.dls_profile_enable.restype = C.c_int
+        lib.dls_profile_enable.argtypes = [C.c_int]
+        lib.dls_profile_read.restype = C.c_int
+        lib.dls_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+        lib.dls_kernel_name.restype = C.c_char_p
+        lib.dls_kernel_name.argtypes = [C.c_int]
         _lib = lib
         return lib
 

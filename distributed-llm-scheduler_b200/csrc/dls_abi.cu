@@ -1,0 +1,202 @@
+// dls_abi.cu — the extern "C" entry points declared in include/dls.h.
+//
+// The library never allocates device memory and never synchronises the stream: scratch comes from the
+// caller (dls_workspace_bytes), results go to caller buffers, kernels are enqueued on the caller's stream.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "dls_common.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<int64_t> g_launches{0};
+dls::Profiler g_prof;
+const char* const kKernelNames[DLS_NUM_KERNELS] = {"priority_topology_kernel", "priority_critical_kernel",
+                                                   "sched_simple_kernel<DFS>", "sched_simple_kernel<Greedy>",
+                                                   "sched_simple_kernel<Critical>", "sched_mru_kernel"};
+
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+
+constexpr size_t kAlign = 256;
+size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+struct Layout {
+  size_t off_depth, off_outdeg, off_order_dg, off_order_mru, off_order_cp, off_up, off_succ_ptr, off_succ_idx,
+      off_status, total;
+  int cp_per_instance;
+};
+
+Layout layout_of(const dls_batch_t& b) {
+  Layout L;
+  L.cp_per_instance = !(b.T == 1 && !(b.flags & DLS_F_DUR_PER_INSTANCE));
+  const size_t nt = (size_t)b.nt_topo, ncp = (size_t)(L.cp_per_instance ? b.nt_inst : b.nt_topo);
+  size_t o = 0;
+  L.off_depth = o;     o = align_up(o + nt * sizeof(uint16_t));
+  L.off_outdeg = o;    o = align_up(o + nt * sizeof(uint16_t));
+  L.off_order_dg = o;  o = align_up(o + nt * sizeof(uint16_t));
+  L.off_order_mru = o; o = align_up(o + nt * sizeof(uint16_t));
+  L.off_order_cp = o;  o = align_up(o + ncp * sizeof(uint16_t));
+  L.off_up = o;        o = align_up(o + ncp * sizeof(double));
+  L.off_succ_ptr = o;  o = align_up(o + (nt + (size_t)b.T) * sizeof(uint32_t));
+  L.off_succ_idx = o;  o = align_up(o + (size_t)b.e_total * sizeof(uint16_t));
+  L.off_status = o;    o = align_up(o + (size_t)b.T * sizeof(int32_t));
+  L.total = o;
+  return L;
+}
+
+dls::Workspace carve(void* base, const Layout& L) {
+  char* p = static_cast<char*>(base);
+  dls::Workspace w;
+  w.depth = reinterpret_cast<uint16_t*>(p + L.off_depth);
+  w.outdeg = reinterpret_cast<uint16_t*>(p + L.off_outdeg);
+  w.order_dg = reinterpret_cast<uint16_t*>(p + L.off_order_dg);
+  w.order_mru = reinterpret_cast<uint16_t*>(p + L.off_order_mru);
+  w.order_cp = reinterpret_cast<uint16_t*>(p + L.off_order_cp);
+  w.up = reinterpret_cast<double*>(p + L.off_up);
+  w.succ_ptr = reinterpret_cast<uint32_t*>(p + L.off_succ_ptr);
+  w.succ_idx = reinterpret_cast<uint16_t*>(p + L.off_succ_idx);
+  w.topo_status = reinterpret_cast<int32_t*>(p + L.off_status);
+  w.cp_per_instance = L.cp_per_instance;
+  return w;
+}
+
+int smem_limit() {
+  int dev = 0, lim = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&lim, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess) return -1;
+  return lim;
+}
+
+int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
+  if (!b) return fail(DLS_ERR_BAD_ARG, "batch is NULL");
+  if (b->B <= 0) return fail(DLS_ERR_BAD_ARG, "B must be positive");
+  if (b->T != b->B && b->T != 1) return fail(DLS_ERR_BAD_ARG, "T must be B or 1");
+  if ((algo_mask & ~DLS_MASK_ALL) || algo_mask == 0) return fail(DLS_ERR_BAD_ARG, "algo_mask must select 1..4 of the algorithms");
+  if (b->n_max < 0 || b->K_max <= 0 || b->P_max < 0 || b->nt_topo < 0 || b->nt_inst < 0 || b->e_total < 0)
+    return fail(DLS_ERR_BAD_ARG, "negative size in descriptor");
+  if (b->n_max > DLS_MAX_TASKS) return fail(DLS_ERR_TOO_LARGE, "n_max > 65535 (task ids are u16)");
+  if (b->P_max > DLS_MAX_PARAMS) return fail(DLS_ERR_TOO_LARGE, "P_max > 65535 (param ids are u16)");
+  if (b->K_max > DLS_MAX_NODES) return fail(DLS_ERR_TOO_LARGE, "K_max > 32 (one warp lane per node)");
+  if (!b->task_off || !b->pred_off || !b->par_off || !b->pid_off || !b->pred_ptr || !b->par_ptr || !b->rank ||
+      !b->mem || !b->dur || !b->cap || !b->spd)
+    return fail(DLS_ERR_BAD_ARG, "NULL array in batch descriptor");
+  if ((b->e_total > 0 && !b->pred_idx) || (b->r_total > 0 && !b->par_idx))
+    return fail(DLS_ERR_BAD_ARG, "NULL index array in batch descriptor");
+  if (need_device) {
+    const int lim = smem_limit();
+    if (lim < 0) return fail(DLS_ERR_CUDA, std::string("no usable CUDA device: ") + cudaGetErrorString(cudaGetLastError()));
+    size_t need = dls::priority_smem_topo(b->n_max);
+    if (algo_mask & (1 << DLS_ALGO_CRITICAL)) need = std::max(need, dls::priority_smem_inst(b->n_max));
+    if (algo_mask & 7) need = std::max(need, dls::sched_smem_simple(b->n_max, b->P_max));
+    if (algo_mask & (1 << DLS_ALGO_MRU)) need = std::max(need, dls::sched_smem_mru(b->n_max, b->P_max, b->K_max));
+    if (need > (size_t)lim) {
+      char buf[160];
+      snprintf(buf, sizeof buf, "per-DAG state needs %zu B of shared memory, device offers %d B (n_max=%d P_max=%d)", need,
+               lim, b->n_max, b->P_max);
+      return fail(DLS_ERR_TOO_LARGE, buf);
+    }
+  }
+  return DLS_OK;
+}
+
+int cuda_fail(cudaError_t e, const char* why) {
+  return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
+}
+
+}  // namespace
+
+extern "C" {
+
+int dls_version(void) { return DLS_VERSION; }
+
+const char* dls_last_error(void) { return g_err.c_str(); }
+
+int64_t dls_launch_count(void) { return g_launches.load(); }
+
+size_t dls_workspace_bytes(const dls_batch_t* batch, int algo_mask) {
+  (void)algo_mask;
+  if (!batch) return 0;
+  return layout_of(*batch).total;
+}
+
+int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace,
+                       size_t workspace_bytes, void* cuda_stream) {
+  int rc = validate(batch, algo_mask, true);
+  if (rc != DLS_OK) return rc;
+  if (!result || !result->node_of || !result->seq_pos || !result->summary || !result->fin || !result->cnt || !result->avail)
+    return fail(DLS_ERR_BAD_ARG, "NULL required output in result");
+  const Layout L = layout_of(*batch);
+  if (!workspace || workspace_bytes < L.total) return fail(DLS_ERR_WORKSPACE, "workspace smaller than dls_workspace_bytes()");
+  if (reinterpret_cast<uintptr_t>(workspace) % kAlign) return fail(DLS_ERR_WORKSPACE, "workspace must be 256-byte aligned");
+  const dls::Workspace w = carve(workspace, L);
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  ctx.prof = g_prof.on ? &g_prof : nullptr;
+  cudaError_t e = dls::launch_priority(*batch, w, algo_mask, ctx);
+  if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
+int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+  int rc = validate(batch, DLS_MASK_ALL, true);
+  if (rc != DLS_OK) return rc;
+  if (!prio) return fail(DLS_ERR_BAD_ARG, "prio is NULL");
+  const Layout L = layout_of(*batch);
+  if (!workspace || workspace_bytes < L.total) return fail(DLS_ERR_WORKSPACE, "workspace smaller than dls_workspace_bytes()");
+  if (reinterpret_cast<uintptr_t>(workspace) % kAlign) return fail(DLS_ERR_WORKSPACE, "workspace must be 256-byte aligned");
+  const dls::Workspace w = carve(workspace, L);
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  ctx.prof = g_prof.on ? &g_prof : nullptr;
+  cudaStream_t st = ctx.st;
+  cudaError_t e = dls::launch_priority(*batch, w, DLS_MASK_ALL, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  const size_t nt = (size_t)batch->nt_topo, ncp = (size_t)(L.cp_per_instance ? batch->nt_inst : batch->nt_topo);
+  struct { void* dst; const void* src; size_t bytes; } copies[] = {
+      {prio->depth, w.depth, nt * sizeof(uint16_t)},         {prio->outdeg, w.outdeg, nt * sizeof(uint16_t)},
+      {prio->order_dg, w.order_dg, nt * sizeof(uint16_t)},   {prio->order_mru, w.order_mru, nt * sizeof(uint16_t)},
+      {prio->order_cp, w.order_cp, ncp * sizeof(uint16_t)},  {prio->up, w.up, ncp * sizeof(double)},
+  };
+  for (auto& c : copies) {
+    if (!c.dst || c.bytes == 0) continue;
+    e = cudaMemcpyAsync(c.dst, c.src, c.bytes, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpyAsync(priorities)");
+  }
+  g_err.clear();
+  return DLS_OK;
+}
+
+int dls_profile_enable(int on) {
+  g_prof.on = on != 0;
+  return DLS_OK;
+}
+
+int dls_profile_read(double* ms_per_kernel, int64_t* launches_per_kernel) {
+  if (!ms_per_kernel || !launches_per_kernel) return fail(DLS_ERR_BAD_ARG, "NULL output in dls_profile_read");
+  for (int i = 0; i < g_prof.n; ++i) {
+    cudaError_t e = cudaEventSynchronize(g_prof.ev[i][1]);
+    float ms = 0.f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, g_prof.ev[i][0], g_prof.ev[i][1]);
+    if (e != cudaSuccess) { g_prof.n = 0; return cuda_fail(e, "dls_profile_read"); }
+    ms_per_kernel[g_prof.kid[i]] += (double)ms;
+    launches_per_kernel[g_prof.kid[i]] += 1;
+  }
+  g_prof.n = 0;
+  return DLS_OK;
+}
+
+const char* dls_kernel_name(int kernel_id) {
+  return (kernel_id >= 0 && kernel_id < DLS_NUM_KERNELS) ? kKernelNames[kernel_id] : "";
+}
+
+}  // extern "C"

@@ -1,0 +1,179 @@
+// dls_common.cuh — shared device helpers for the sm_100a kernels behind include/dls.h.
+//
+// Numerics contract: every fp64 value that feeds a comparison is produced by the same IEEE operations, in
+// the same order, as the reference's Python floats (SURVEY.md section 7 "fp64 replay"). The library is
+// compiled with -fmad=false and the arithmetic below additionally uses the explicit round-to-nearest
+// intrinsics, so no FMA contraction can change a rounding.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dls.h"
+
+#define DLS_FULL_MASK 0xffffffffu
+
+namespace dls {
+
+// Scratch produced by the priority pass (kernel P) and consumed by the scheduling kernels (kernel S).
+struct Workspace {
+  uint16_t* depth;      // [nt_topo]   longest path from a source = round index          ref schedulers.py:140-152
+  uint16_t* outdeg;     // [nt_topo]   number of dependents (with multiplicity)           ref schedulers.py:468-469
+  uint16_t* order_dg;   // [nt_topo]   (depth asc, rank asc)
+  uint16_t* order_mru;  // [nt_topo]   (depth asc, outdeg desc, rank asc)
+  uint16_t* order_cp;   // [nt_cp]     (depth asc, up desc, rank asc)
+  double* up;           // [nt_cp]     upward rank                                        ref schedulers.py:301-321
+  uint32_t* succ_ptr;   // [nt_topo+T] reverse adjacency (task_dependencies)              ref schedulers.py:39,47-48
+  uint16_t* succ_idx;   // [e_total]
+  int32_t* topo_status; // [T]         0 ok, DLS_ST_BAD_TOPOLOGY
+  int cp_per_instance;  // order_cp/up indexed per instance (T==B or per-instance durations) or per topology
+};
+
+// One DAG instance resolved against the batch descriptor.
+struct Inst {
+  int n, K, P, topo;
+  uint32_t E, R;
+  const uint32_t* pred_ptr;
+  const uint16_t* pred_idx;
+  const uint32_t* par_ptr;
+  const uint16_t* par_idx;
+  const uint16_t* rank;
+  const double* mem;
+  const double* dur;
+  const double* cap;
+  const double* spd;
+  int64_t t_topo;  // offset of this topology in per-topology-task arrays
+  int64_t t_inst;  // offset of this instance in per-instance-task arrays
+  int64_t k_out;   // offset in per-instance-node outputs
+  int64_t p_out;   // offset in per-instance-param outputs
+};
+
+__device__ __forceinline__ void bind_topology(const dls_batch_t& b, int t, Inst& v) {
+  v.topo = t;
+  int64_t to = b.task_off[t];
+  v.t_topo = to;
+  v.n = (int)(b.task_off[t + 1] - to);
+  v.P = (int)(b.pid_off[t + 1] - b.pid_off[t]);
+  v.pred_ptr = b.pred_ptr + to + t;
+  v.pred_idx = b.pred_idx + b.pred_off[t];
+  v.par_ptr = b.par_ptr + to + t;
+  v.par_idx = b.par_idx + b.par_off[t];
+  v.E = (uint32_t)(b.pred_off[t + 1] - b.pred_off[t]);
+  v.R = (uint32_t)(b.par_off[t + 1] - b.par_off[t]);
+  v.rank = b.rank + to;
+}
+
+__device__ __forceinline__ void bind_instance(const dls_batch_t& b, int inst, Inst& v) {
+  int t = b.T == 1 ? 0 : inst;
+  bind_topology(b, t, v);
+  int64_t ti = b.T == 1 ? (int64_t)inst * v.n : v.t_topo;
+  v.t_inst = ti;
+  v.mem = b.mem + ((b.T == 1 && !(b.flags & DLS_F_MEM_PER_INSTANCE)) ? 0 : ti);
+  v.dur = b.dur + ((b.T == 1 && !(b.flags & DLS_F_DUR_PER_INSTANCE)) ? 0 : ti);
+  int64_t kin;
+  if (b.node_off) {
+    kin = b.node_off[inst];
+    v.K = (int)(b.node_off[inst + 1] - kin);
+    v.k_out = kin;
+  } else {
+    kin = 0;
+    v.K = b.K_max;
+    v.k_out = (int64_t)inst * b.K_max;
+  }
+  v.cap = b.cap + kin;
+  v.spd = b.spd + kin;
+  v.p_out = b.T == 1 ? (int64_t)inst * v.P : b.pid_off[t];
+}
+
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+// (key, lane) butterfly: winner = largest key among valid lanes, ties -> LOWEST lane. This is the reference's
+// "for node in self.nodes.values(): if ... > best" scan with a strict '>' (ref schedulers.py:189-192,355-358,
+// 500-502): the first node reaching the maximum keeps it. Returns -1 when no lane is valid.
+__device__ __forceinline__ int warp_argmax_first(bool valid, double key) {
+  unsigned any = __ballot_sync(DLS_FULL_MASK, valid);
+  if (any == 0) return -1;
+  int idx = valid ? lane_id() : 64;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    double k2 = __shfl_xor_sync(DLS_FULL_MASK, key, off);
+    int i2 = __shfl_xor_sync(DLS_FULL_MASK, idx, off);
+    bool v1 = idx < 64, v2 = i2 < 64;
+    bool take = v2 && (!v1 || k2 > key || (k2 == key && i2 < idx));
+    if (take) {
+      key = k2;
+      idx = i2;
+    }
+  }
+  return idx;
+}
+
+// Smallest (score, id) among valid lanes: the head of `evictable.sort()` over (score, param-name) tuples
+// (ref schedulers.py:417-420; param ids are lexicographic ranks of the names). Returns id or -1.
+__device__ __forceinline__ int warp_argmin_pair(bool valid, double score, int id, double* win_score) {
+  unsigned any = __ballot_sync(DLS_FULL_MASK, valid);
+  if (any == 0) return -1;
+  if (!valid) id = 0x7fffffff;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    double s2 = __shfl_xor_sync(DLS_FULL_MASK, score, off);
+    int i2 = __shfl_xor_sync(DLS_FULL_MASK, id, off);
+    bool v1 = id != 0x7fffffff, v2 = i2 != 0x7fffffff;
+    bool take = v2 && (!v1 || s2 < score || (s2 == score && i2 < id));
+    if (take) {
+      score = s2;
+      id = i2;
+    }
+  }
+  if (win_score) *win_score = score;
+  return id;
+}
+
+__device__ __forceinline__ double warp_bcast(double v, int src) { return __shfl_sync(DLS_FULL_MASK, v, src); }
+__device__ __forceinline__ int warp_bcast(int v, int src) { return __shfl_sync(DLS_FULL_MASK, v, src); }
+
+// calculate_memory_requirement: memory_needed = m; memory_needed += len(params_to_load) * 0.5  (ref schedulers.py:66-70)
+__device__ __forceinline__ double memory_requirement(double m, int params_to_load) {
+  return __dadd_rn(m, __dmul_rn((double)params_to_load, 0.5));
+}
+
+// Optional event bracketing of every launch (dls_profile_enable / dls_profile_read).
+struct Profiler {
+  static constexpr int kMaxRec = 4096;
+  bool on = false;
+  int n = 0, created = 0;
+  cudaEvent_t ev[kMaxRec][2];
+  int kid[kMaxRec];
+  // returns record index or -1
+  int begin(int kernel_id, cudaStream_t st) {
+    if (!on || n >= kMaxRec) return -1;
+    if (n >= created) {
+      if (cudaEventCreate(&ev[n][0]) != cudaSuccess || cudaEventCreate(&ev[n][1]) != cudaSuccess) return -1;
+      created = n + 1;
+    }
+    kid[n] = kernel_id;
+    cudaEventRecord(ev[n][0], st);
+    return n++;
+  }
+  void end(int rec, cudaStream_t st) {
+    if (rec >= 0) cudaEventRecord(ev[rec][1], st);
+  }
+};
+
+struct LaunchCtx {
+  cudaStream_t st;
+  int64_t launches = 0;
+  const char* why = "";
+  Profiler* prof = nullptr;
+};
+
+// Host-side launchers (one translation unit each).
+cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
+cudaError_t launch_schedule(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
+                            LaunchCtx& ctx);
+size_t priority_smem_topo(int n_max);
+size_t priority_smem_inst(int n_max);
+size_t sched_smem_simple(int n_max, int P_max);
+size_t sched_smem_mru(int n_max, int P_max, int K_max);
+
+}  // namespace dls

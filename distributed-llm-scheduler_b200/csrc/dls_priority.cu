@@ -1,0 +1,318 @@
+// dls_priority.cu — kernel P: priorities and the static processing orders.
+//
+// What the reference recomputes inside every schedule() call, once per DAG:
+//   depth[i]  = 0 if no deps else 1 + max(depth[dep])                      ref schedulers.py:140-152
+//   up[i]     = dur[i] (+ max(up[dependents]) if any)                       ref schedulers.py:301-321
+//   outdeg[i] = len(task_dependencies[i])                                   ref schedulers.py:468-469
+// and what its round structure implies: round r handles exactly the ready tasks of
+// depth r, in the order of the pending set (rank) after a stable sort by the algorithm's key, so the whole
+// processing order is static:  order = sort by (depth asc, key desc, rank asc).
+//
+// priority_topology_kernel: one CTA per topology. Level-synchronous relaxation for depth, reverse CSR by
+// counting sort, and stable counting sorts (warp __match_any placement) for the DFS/Greedy and MRU orders.
+// priority_critical_kernel: one CTA per instance. Upward rank level by level from the sinks, then the
+// within-level stable sort by rank-by-counting.
+#include "dls_common.cuh"
+
+namespace dls {
+
+namespace {
+
+constexpr int kThreadsP = 128;
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// Exclusive prefix sum of a[0..m) in shared memory by the whole CTA; returns the total. s_part: [blockDim/32 + 1].
+__device__ uint32_t block_exclusive_scan(uint32_t* a, int m, uint32_t* s_part) {
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int chunk = (m + nthr - 1) / nthr;
+  const int lo = min(tid * chunk, m), hi = min(lo + chunk, m);
+  uint32_t sum = 0;
+  for (int i = lo; i < hi; ++i) sum += a[i];
+  // scan of per-thread sums: warp scan + scan of warp totals
+  uint32_t incl = sum;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    uint32_t t = __shfl_up_sync(DLS_FULL_MASK, incl, off);
+    if ((tid & 31) >= off) incl += t;
+  }
+  const int wid = tid >> 5, nw = nthr >> 5;
+  if ((tid & 31) == 31) s_part[wid] = incl;
+  __syncthreads();
+  if (tid < 32) {
+    uint32_t v = tid < nw ? s_part[tid] : 0, inc = v;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      uint32_t t = __shfl_up_sync(DLS_FULL_MASK, inc, off);
+      if (tid >= off) inc += t;
+    }
+    if (tid < nw) s_part[tid] = inc - v;  // exclusive warp offsets
+    if (tid == 31) s_part[32] = inc;      // total
+  }
+  __syncthreads();
+  uint32_t run = s_part[wid] + (incl - sum);
+  for (int i = lo; i < hi; ++i) {
+    uint32_t t = a[i];
+    a[i] = run;
+    run += t;
+  }
+  uint32_t total = s_part[32];
+  __syncthreads();
+  return total;
+}
+
+// dst = src stably sorted by key(task) ascending, key in [0, nkeys). Histogram by all threads, placement by
+// warp 0 walking src in order, 32 at a time, with __match_any giving each lane its rank among equal keys.
+template <class KeyF>
+__device__ void stable_counting_sort(const uint16_t* src, uint16_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
+                                     uint32_t* s_part) {
+  for (int k = threadIdx.x; k <= nkeys; k += blockDim.x) s_hist[k] = 0;
+  __syncthreads();
+  for (int q = threadIdx.x; q < n; q += blockDim.x) atomicAdd(&s_hist[key(src[q])], 1u);
+  __syncthreads();
+  block_exclusive_scan(s_hist, nkeys, s_part);
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    for (int base = 0; base < n; base += 32) {
+      const int q = base + lane;
+      const bool valid = q < n;
+      const unsigned vm = __ballot_sync(DLS_FULL_MASK, valid);
+      if (valid) {
+        const int i = src[q];
+        const uint32_t k = key(i);
+        const unsigned peers = __match_any_sync(vm, k);
+        const uint32_t pos = s_hist[k] + __popc(peers & lanemask_lt());
+        dst[pos] = (uint16_t)i;
+        __syncwarp(vm);
+        if (lane == __ffs(peers) - 1) s_hist[k] += __popc(peers);
+        __syncwarp(vm);
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t s_part[33];
+  __shared__ int s_maxd, s_maxdeg;
+  const int t = blockIdx.x, tid = threadIdx.x;
+  Inst v;
+  bind_topology(b, t, v);
+  const int n = v.n;
+  const int n_al = (n + 3) & ~3;
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw);  // [n+2]
+  uint32_t* s_hist = s_cnt + (n + 2);                       // [n+2]
+  uint16_t* s_depth = reinterpret_cast<uint16_t*>(s_hist + (n + 2));  // [n_al]
+  uint16_t* s_ord = s_depth + n_al;                                     // [n_al]
+  uint16_t* s_tmp = s_ord + n_al;                                       // [n_al]
+
+  uint16_t* g_depth = w.depth + v.t_topo;
+  uint16_t* g_outdeg = w.outdeg + v.t_topo;
+  uint32_t* g_succ_ptr = w.succ_ptr + v.t_topo + t;
+  uint16_t* g_succ_idx = w.succ_idx + b.pred_off[t];
+
+  if (tid == 0) { s_maxd = 0; s_maxdeg = 0; }
+  __syncthreads();
+  // ---- validate the descriptor slice (never trust indices that address shared memory) ----
+  {
+    int bad = 0;
+    if (n > 0 && (v.pred_ptr[0] != 0 || v.par_ptr[0] != 0 || v.pred_ptr[n] != v.E || v.par_ptr[n] != v.R)) bad = 1;
+    for (int i = tid; i < n; i += blockDim.x) {
+      if (v.pred_ptr[i] > v.pred_ptr[i + 1] || v.par_ptr[i] > v.par_ptr[i + 1]) bad = 1;
+      if (v.rank[i] >= n) bad = 1;
+    }
+    for (uint32_t e = tid; e < v.E; e += blockDim.x)
+      if (v.pred_idx[e] >= n) bad = 1;
+    for (uint32_t e = tid; e < v.R; e += blockDim.x)
+      if (v.par_idx[e] >= v.P) bad = 1;
+    if (__syncthreads_or(bad)) {
+      if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
+      return;
+    }
+  }
+  // ---- depth: relax until a fixed point (<= levels+1 sweeps; more than n+1 sweeps means a cycle) ----
+  for (int i = tid; i < n; i += blockDim.x) s_depth[i] = 0;
+  __syncthreads();
+  int sweeps = 0, changed;
+  do {
+    changed = 0;
+    for (int i = tid; i < n; i += blockDim.x) {
+      int d = 0;
+      for (uint32_t e = v.pred_ptr[i]; e < v.pred_ptr[i + 1]; ++e) d = max(d, (int)s_depth[v.pred_idx[e]] + 1);
+      d = min(d, 65535);
+      if (d != s_depth[i]) {
+        s_depth[i] = (uint16_t)d;
+        changed = 1;
+      }
+    }
+    changed = __syncthreads_or(changed);
+    ++sweeps;
+  } while (changed && sweeps <= n + 1);
+  if (changed) {
+    if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
+    return;
+  }
+  if (tid == 0) w.topo_status[t] = DLS_ST_OK;
+  {
+    int md = 0;
+    for (int i = tid; i < n; i += blockDim.x) {
+      g_depth[i] = s_depth[i];
+      md = max(md, (int)s_depth[i]);
+    }
+    atomicMax(&s_maxd, md);
+  }
+  // ---- out-degree and reverse CSR (task_dependencies, ref schedulers.py:47-48) ----
+  for (int i = tid; i < n + 2; i += blockDim.x) s_cnt[i] = 0;
+  __syncthreads();
+  for (uint32_t e = tid; e < v.E; e += blockDim.x) atomicAdd(&s_cnt[v.pred_idx[e]], 1u);
+  __syncthreads();
+  {
+    int mdg = 0;
+    for (int i = tid; i < n; i += blockDim.x) {
+      g_outdeg[i] = (uint16_t)min(s_cnt[i], 65535u);
+      mdg = max(mdg, (int)min(s_cnt[i], 65535u));
+    }
+    atomicMax(&s_maxdeg, mdg);
+  }
+  __syncthreads();
+  block_exclusive_scan(s_cnt, n + 1, s_part);  // s_cnt[i] = start of i's dependents, s_cnt[n] = E
+  for (int i = tid; i <= n; i += blockDim.x) g_succ_ptr[i] = s_cnt[i];
+  __syncthreads();
+  for (int i = tid; i < n; i += blockDim.x)
+    for (uint32_t e = v.pred_ptr[i]; e < v.pred_ptr[i + 1]; ++e) {
+      uint32_t pos = atomicAdd(&s_cnt[v.pred_idx[e]], 1u);  // order inside a list is irrelevant to max() and counts
+      g_succ_idx[pos] = (uint16_t)i;
+    }
+  // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
+  for (int i = tid; i < n; i += blockDim.x) s_ord[v.rank[i]] = (uint16_t)i;
+  __syncthreads();
+  const int maxd = s_maxd, maxdeg = s_maxdeg;
+  // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
+  stable_counting_sort(s_ord, s_tmp, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, s_part);
+  for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = s_tmp[q];
+  __syncthreads();
+  if (want_mru) {
+    // MRU: (depth asc, urgency desc, ready-index asc) — ref schedulers.py:462-475. LSD: urgency first, then depth.
+    uint32_t* s_deg = s_cnt;  // reuse: out-degree per task
+    for (int i = tid; i < n; i += blockDim.x) s_deg[i] = g_outdeg[i];
+    __syncthreads();
+    stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, s_part);
+    stable_counting_sort(s_tmp, s_ord, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, s_part);
+    for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_ord[q];
+  }
+}
+
+__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int s_maxd;
+  const int inst = blockIdx.x, tid = threadIdx.x;
+  Inst v;
+  bind_instance(b, inst, v);
+  if (w.topo_status[v.topo] != DLS_ST_OK) return;
+  const int n = v.n;
+  if (n == 0) return;
+  const int n_al = (n + 3) & ~3;
+  double* s_up = reinterpret_cast<double*>(smem_raw);             // [n]
+  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(s_up + n);        // [n+2] first position of each level
+  uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
+  uint16_t* s_depth = s_ord + n_al;                               // [n_al]
+  const uint16_t* g_depth = w.depth + v.t_topo;
+  const uint32_t* succ_ptr = w.succ_ptr + v.t_topo + v.topo;
+  const uint16_t* succ_idx = w.succ_idx + b.pred_off[v.topo];
+  const int64_t cp_off = w.cp_per_instance ? v.t_inst : v.t_topo;
+
+  for (int q = tid; q < n; q += blockDim.x) {
+    s_ord[q] = w.order_dg[v.t_topo + q];
+    s_depth[q] = g_depth[q];
+  }
+  __syncthreads();
+  if (tid == 0) s_maxd = s_depth[s_ord[n - 1]];
+  for (int q = tid; q < n; q += blockDim.x) {
+    int d = s_depth[s_ord[q]];
+    if (q == 0 || s_depth[s_ord[q - 1]] != d) s_lvl[d] = q;
+  }
+  __syncthreads();
+  const int maxd = s_maxd;
+  if (tid == 0) s_lvl[maxd + 1] = n;
+  __syncthreads();
+  // upward rank, sinks first: every dependent lies on a deeper level, so it is final when read
+  for (int d = maxd; d >= 0; --d) {
+    for (int q = s_lvl[d] + tid; q < (int)s_lvl[d + 1]; q += blockDim.x) {
+      const int i = s_ord[q];
+      const uint32_t sb = succ_ptr[i], se = succ_ptr[i + 1];
+      double path = v.dur[i];
+      if (se > sb) {
+        double mx = s_up[succ_idx[sb]];
+        for (uint32_t e = sb + 1; e < se; ++e) {
+          double u = s_up[succ_idx[e]];
+          if (u > mx) mx = u;
+        }
+        path = __dadd_rn(path, mx);  // task.compute_time + max(...)  ref schedulers.py:314
+      }
+      s_up[i] = path;
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < n; i += blockDim.x) w.up[cp_off + i] = s_up[i];
+  // within-level stable sort by up desc: ready_tasks.sort(key=critical_path, reverse=True), ref schedulers.py:343
+  for (int q = tid; q < n; q += blockDim.x) {
+    const int i = s_ord[q];
+    const int d = s_depth[i];
+    const int ls = s_lvl[d], le = s_lvl[d + 1];
+    const double u = s_up[i];
+    int ahead = 0;
+    for (int q2 = ls; q2 < le; ++q2) {
+      const double u2 = s_up[s_ord[q2]];
+      ahead += (u2 > u) || (u2 == u && q2 < q);
+    }
+    w.order_cp[cp_off + ls + ahead] = (uint16_t)i;
+  }
+}
+
+}  // namespace
+
+size_t priority_smem_topo(int n_max) {
+  size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
+  return 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
+}
+
+size_t priority_smem_inst(int n_max) {
+  size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
+  return n * sizeof(double) + (n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
+}
+
+cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
+  cudaError_t e;
+  size_t sm1 = priority_smem_topo(b.n_max);
+  ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
+  e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+  if (e != cudaSuccess) return e;
+  int rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
+  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1);
+  if (ctx.prof) ctx.prof->end(rec, ctx.st);
+  ++ctx.launches;
+  ctx.why = "priority_topology_kernel launch";
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
+    size_t sm2 = priority_smem_inst(b.n_max);
+    ctx.why = "cudaFuncSetAttribute(priority_critical_kernel)";
+    e = cudaFuncSetAttribute(priority_critical_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    if (e != cudaSuccess) return e;
+    int grid = w.cp_per_instance ? b.B : 1;
+    rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;
+    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w);
+    if (ctx.prof) ctx.prof->end(rec, ctx.st);
+    ++ctx.launches;
+    ctx.why = "priority_critical_kernel launch";
+    e = cudaGetLastError();
+  }
+  return e;
+}
+
+}  // namespace dls

@@ -185,6 +185,21 @@ int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, 
 /* Number of kernel launches the library has enqueued since load (for bench accounting). */
 int64_t dls_launch_count(void);
 
+/* Measurement support (no reference counterpart): when enabled, every kernel the library enqueues is bracketed by
+ * CUDA events on the caller's stream. dls_profile_read waits for the recorded events, ADDS the elapsed
+ * milliseconds / launch counts per kernel id into the caller's arrays (DLS_NUM_KERNELS entries each) and clears
+ * the record list. At most 4096 launches are kept between reads. */
+#define DLS_KERNEL_PRIO_TOPOLOGY 0
+#define DLS_KERNEL_PRIO_CRITICAL 1
+#define DLS_KERNEL_SCHED_DFS 2
+#define DLS_KERNEL_SCHED_GREEDY 3
+#define DLS_KERNEL_SCHED_CRITICAL 4
+#define DLS_KERNEL_SCHED_MRU 5
+#define DLS_NUM_KERNELS 6
+int dls_profile_enable(int on);
+int dls_profile_read(double* ms_per_kernel, int64_t* launches_per_kernel);
+const char* dls_kernel_name(int kernel_id);
+
 #ifdef __cplusplus
 }
 #endif

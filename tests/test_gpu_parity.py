@@ -1,0 +1,141 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (dls_schedule_batch / dls_priorities via
+dls_b200.batch), against (1) the golden fixtures produced by the reference and (2) the CPU oracle on the same
+seeded inputs. Bar: bit-exact task order, node assignment, verdicts, fp64 node state and makespan bits
+(north star asks 1e-6 relative on makespan; assert_* checks both)."""
+import numpy as np
+import pytest
+
+import golden_io
+from common import assert_matches_expected, assert_results_equal
+from dls_b200 import _native as N
+from dls_b200.batch import priorities, schedule_batch
+from dls_b200.gen import perturbed_durations, random_dag_batch
+from dls_b200.lowering import DagBatch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("fname", golden_io.ALL_FILES)
+def test_cuda_reproduces_reference_fixtures(fname):
+    cases = golden_io.load(fname)
+    assert cases, f"{fname} missing"
+    for mask in sorted({c.mask for c in cases}):
+        sub = [c for c in cases if c.mask == mask]
+        batch = golden_io.batch_of(sub)
+        res = schedule_batch(batch, mask).host()
+        for b, c in enumerate(sub):
+            for slot, a in enumerate(res.algos):
+                assert_matches_expected(c.exp[a], batch, res, slot, b, f"{fname}:{c.label} algo={a}")
+
+
+@pytest.mark.parametrize("n,K,regime,B", [(1000, 8, 0.9, 96), (1000, 8, 0.8, 48), (1000, 4, 1.0, 48), (1000, 2, 0.9, 32),
+                                          (257, 8, 0.6, 64), (64, 8, 0.45, 128), (33, 4, 0.7, 128), (1, 2, 1.0, 8)])
+def test_cuda_matches_oracle_random_dags(oracle_mod, n, K, regime, B):
+    batch = random_dag_batch(B, n, K, regime, seed=n * 131 + K)
+    got = schedule_batch(batch, N.MASK_ALL).host()
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    assert_results_equal(got, want, f"random n={n} K={K} r={regime}")
+
+
+def test_single_algorithm_masks_and_slots(oracle_mod):
+    batch = random_dag_batch(16, 200, 8, 0.8, seed=5)
+    full = schedule_batch(batch, N.MASK_ALL).host()
+    for mask in (1, 2, 4, 8, 5, 10, 12):
+        got = schedule_batch(batch, mask).host()
+        for slot, a in enumerate(got.algos):
+            np.testing.assert_array_equal(got.node_of[slot], full.node_of[a])
+            np.testing.assert_array_equal(got.seq_pos[slot], full.seq_pos[a])
+            np.testing.assert_array_equal(got.summary[slot], full.summary[a])
+
+
+def test_priorities_match_oracle(oracle_mod):
+    for batch in (random_dag_batch(32, 1000, 8, 0.9, seed=3), random_dag_batch(64, 77, 4, 0.9, seed=4),
+                  golden_io.batch_of(golden_io.load("cfg2_sweep_seed0.npz")[::5]),
+                  golden_io.batch_of(golden_io.load("cfg3_gpt2.npz"))):
+        got = priorities(batch)
+        want = oracle_mod.priorities(batch, nthreads=4)
+        for k in ("depth", "outdeg", "order_dg", "order_mru", "order_cp"):
+            np.testing.assert_array_equal(got[k], want[k], err_msg=k)
+        np.testing.assert_array_equal(got["up"].view(np.uint64), want["up"].view(np.uint64), err_msg="up bits")
+
+
+def test_shared_topology_perturbed_durations(oracle_mod):
+    """Config 3 shape: GPT-2 DAG on 8 capped devices, durations perturbed per instance (T == 1)."""
+    base = [c for c in golden_io.load("cfg3_gpt2.npz") if c.label == "gpt2|8laptops"][0]
+    B = 512
+    dur = perturbed_durations(base.dag, B, 0.1, seed=0)
+    batch = DagBatch.shared_topology(base.dag, base.cap, base.spd, B, dur=dur)
+    got = schedule_batch(batch, N.MASK_ALL).host()
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    assert_results_equal(got, want, "gpt2 shared topology")
+    # instance 0 with unperturbed durations reproduces the fixture
+    plain = DagBatch.shared_topology(base.dag, base.cap, base.spd, 3)
+    res = schedule_batch(plain, N.MASK_ALL).host()
+    for b in range(3):
+        for slot, a in enumerate(res.algos):
+            assert_matches_expected(base.exp[a], plain, res, slot, b, f"gpt2 shared b={b} algo={a}")
+    # DFS/Greedy/MRU decisions do not depend on durations (SURVEY.md 8a'): only makespan moves
+    for slot in (0, 1, 3):
+        n = base.n
+        assert (got.node_of[slot].reshape(B, n) == got.node_of[slot, :n][None, :]).all()
+
+
+def test_size_independent_properties_full_size():
+    """At BASELINE.json's 1k-task size without an oracle run: structural invariants of any valid outcome."""
+    batch = random_dag_batch(2048, 1000, 8, 0.9, seed=11)
+    res = schedule_batch(batch, N.MASK_ALL).host()
+    n = 1000
+    for slot in range(4):
+        s = res.summary[slot]
+        assert (s["status"] == 0).all()
+        assert (s["completed"] + s["failed"] + s["pending"] == n).all()
+        node_of = res.node_of[slot].reshape(-1, n)
+        seq = res.seq_pos[slot].reshape(-1, n)
+        done = node_of >= 0
+        assert (done.sum(1) == s["completed"]).all()
+        assert ((node_of == -1).sum(1) == s["failed"]).all()
+        # assignment positions are a permutation of 0..completed-1
+        srt = np.sort(np.where(done, seq, 0xFFFF), 1)
+        want = np.where(np.arange(n)[None, :] < s["completed"][:, None], np.arange(n)[None, :], 0xFFFF)
+        assert (srt == want).all()
+        cnt = res.cnt[slot].reshape(-1, 8)
+        assert (cnt.sum(1) == s["completed"]).all()
+        fin = res.fin[slot].reshape(-1, 8)
+        np.testing.assert_array_equal(np.where(s["completed"] > 0, fin.max(1), 0.0), s["makespan"])
+        assert (s["hits"] + s["misses"] >= 0).all()
+    # dependencies respected: a completed task is sequenced after all its dependencies (spot check 64 instances)
+    for b in range(0, 2048, 32):
+        ts = batch.task_slice(b)
+        pp = batch.pred_ptr[b * (n + 1):(b + 1) * (n + 1)]
+        pi = batch.pred_idx[batch.pred_off[b]:batch.pred_off[b + 1]]
+        for slot in range(4):
+            node_of, seq = res.node_of[slot, ts], res.seq_pos[slot, ts].astype(np.int64)
+            child = np.repeat(np.arange(n), np.diff(pp))
+            ok = node_of[child] >= 0
+            assert (node_of[pi][ok] >= 0).all() and (seq[pi][ok] < seq[child][ok]).all()
+
+
+def test_error_codes():
+    import ctypes as C
+    lib = N.load()
+    batch = random_dag_batch(4, 16, 8, 0.9, seed=1)
+    with pytest.raises(N.DlsError) as ei:
+        schedule_batch(batch, 0)
+    assert ei.value.code == N.ERR_BAD_ARG
+    batch.K_max = 33
+    with pytest.raises(ValueError):
+        schedule_batch(batch, 1)
+    assert lib.dls_schedule_batch(None, None, 1, None, 0, None) == N.ERR_BAD_ARG
+    assert b"NULL" in lib.dls_last_error()
+
+
+def test_cycle_is_reported_not_hung():
+    from dls_b200.lowering import LoweredDag
+    dag = LoweredDag(names=["a", "b", "c"], param_names=["p"], pred_ptr=np.array([0, 1, 2, 3], np.uint32),
+                     pred_idx=np.array([2, 0, 1], np.uint16), par_ptr=np.array([0, 1, 1, 1], np.uint32),
+                     par_idx=np.array([0], np.uint16), rank=np.array([0, 1, 2], np.uint16),
+                     mem=np.ones(3), dur=np.ones(3))
+    batch = DagBatch.from_instances([dag], [(np.array([4.0, 4.0]), np.array([1.0, 1.0]))])
+    res = schedule_batch(batch, N.MASK_ALL).host()
+    assert (res.summary["status"] == N.ST_BAD_TOPOLOGY).all()
+    assert (res.node_of == N.TASK_PENDING).all()
