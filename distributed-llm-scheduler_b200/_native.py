@@ -74,8 +74,9 @@ class DlsPrio(C.Structure):
 # Every symbol include/dls.h declares; tests check the built library exports all of them.
 EXPORTED_SYMBOLS = (
     "dls_version", "dls_last_error", "dls_workspace_bytes", "dls_schedule_batch", "dls_priorities",
-    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name",
+    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static",
 )
+STATIC_SCRATCH_BYTES = 32 << 20
 NUM_KERNELS = 6
 
 NVCC_FLAGS = [
@@ -136,6 +137,8 @@ def load() -> C.CDLL:
         lib.dls_schedule_batch.restype = C.c_int
         lib.dls_schedule_batch.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsResult), C.c_int, C.c_void_p,
                                            C.c_size_t, C.c_void_p]
+        lib.dls_schedule_batch_static.restype = C.c_int
+        lib.dls_schedule_batch_static.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsResult), C.c_int, C.c_void_p]
         lib.dls_priorities.restype = C.c_int
         lib.dls_priorities.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsPrio), C.c_void_p, C.c_size_t, C.c_void_p]
         lib.dls_launch_count.restype = C.c_int64

@@ -5,6 +5,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "dls_common.cuh"
@@ -109,6 +110,34 @@ int cuda_fail(cudaError_t e, const char* why) {
   return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
 }
 
+// ---- built-in scratch for dls_schedule_batch_static --------------------------------------------------------------
+// The array is part of this library's device image: each GPU that loads the library carries its own copy from
+// load until exit. In HOST code the name below is only a handle for the runtime, not a device address; the
+// address a kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch[DLS_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices] = {};
+
+// Device address of g_static_scratch on the current device (looked up on the first call per device).
+int static_scratch_address(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) return fail(DLS_ERR_BAD_ARG, "device ordinal beyond the built-in scratch table");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(built-in scratch)");
+    if (!p) return fail(DLS_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the built-in scratch");
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return DLS_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -139,6 +168,39 @@ int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_
   ctx.st = static_cast<cudaStream_t>(cuda_stream);
   ctx.prof = g_prof.on ? &g_prof : nullptr;
   cudaError_t e = dls::launch_priority(*batch, w, algo_mask, ctx);
+  if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
+// See include/dls.h. Same work as dls_schedule_batch; the only difference is where the scratch lives.
+int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* cuda_stream) {
+  int rc = validate(batch, algo_mask, true);
+  if (rc != DLS_OK) return rc;
+  if (!result || !result->node_of || !result->seq_pos || !result->summary || !result->fin || !result->cnt || !result->avail)
+    return fail(DLS_ERR_BAD_ARG, "NULL required output in result");
+  const Layout L = layout_of(*batch);
+  if (L.total > (size_t)DLS_STATIC_SCRATCH_BYTES) {
+    char buf[200];
+    snprintf(buf, sizeof buf,
+             "batch needs %zu bytes of scratch but the built-in scratch holds %u bytes; split the batch or call "
+             "dls_schedule_batch with your own workspace", L.total, (unsigned)DLS_STATIC_SCRATCH_BYTES);
+    return fail(DLS_ERR_TOO_LARGE, buf);
+  }
+  void* base = nullptr;
+  rc = static_scratch_address(&base);  // first call on this device: resolves the array's device address
+  if (rc != DLS_OK) return rc;
+  const dls::Workspace w = carve(base, L);
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  ctx.prof = g_prof.on ? &g_prof : nullptr;
+  // The array still holds whatever the previous call left. The per-topology status words are the one region the
+  // scheduling kernels trust before looking at anything else, so they start from zero on every call.
+  cudaError_t e = cudaMemsetAsync(w.topo_status, 0, (size_t)batch->T * sizeof(int32_t), ctx.st);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(built-in scratch)");
+  e = dls::launch_priority(*batch, w, algo_mask, ctx);
   if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
   g_launches += ctx.launches;
   if (e != cudaSuccess) return cuda_fail(e, ctx.why);

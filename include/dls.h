@@ -182,6 +182,30 @@ int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_
 int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, size_t workspace_bytes,
                    void* cuda_stream);
 
+/*
+ * dls_schedule_batch without a caller-supplied workspace. (No counterpart in the reference.)
+ *
+ * Some hosts of this library cannot hand it scratch memory at all: a plugin that is only ever given its input
+ * and output buffers by an application that has already claimed the whole GPU for its own pools; a control loop
+ * that must not call cudaMalloc because that call may synchronise the device and stall everything queued on it;
+ * a binding in a runtime that has no device allocator to call in the first place. For them this entry point
+ * keeps the scratch (depth, orders, upward rank, reverse adjacency, status words) in a fixed array that lives
+ * inside the library's device image: DLS_STATIC_SCRATCH_BYTES bytes, resident on every GPU that loads the
+ * library until the process exits. It never calls cudaMalloc, cudaFree or any other allocating routine; inputs and
+ * outputs are still the caller's device buffers, exactly as for dls_schedule_batch, and results are identical.
+ *
+ * - A batch whose scratch need (dls_workspace_bytes) exceeds DLS_STATIC_SCRATCH_BYTES is refused with
+ *   DLS_ERR_TOO_LARGE and a message naming both numbers; nothing is launched. (About 1,300 DAGs of 1,000 tasks.)
+ * - The first call on each device looks up the array's device address (one cudaGetSymbolAddress, made with that
+ *   device current). Make that first call outside any stream capture.
+ * - There is ONE array per device and every call uses it. It still holds the previous call's contents when the
+ *   next call starts; the words that must start at zero are cleared on the stream before the kernels run. Two calls
+ *   whose GPU work can overlap (different streams, or different host threads on one device) race on it: serialise
+ *   them, or use dls_schedule_batch with separate workspaces instead.
+ */
+#define DLS_STATIC_SCRATCH_BYTES (32u << 20)
+int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* cuda_stream);
+
 /* Number of kernel launches the library has enqueued since load (for bench accounting). */
 int64_t dls_launch_count(void);
 
