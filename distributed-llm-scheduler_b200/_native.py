@@ -74,10 +74,10 @@ class DlsPrio(C.Structure):
 # Every symbol include/dls.h declares; tests check the built library exports all of them.
 EXPORTED_SYMBOLS = (
     "dls_version", "dls_last_error", "dls_workspace_bytes", "dls_schedule_batch", "dls_priorities",
-    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static",
+    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path",
 )
 STATIC_SCRATCH_BYTES = 32 << 20
-NUM_KERNELS = 6
+NUM_KERNELS = 13
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -139,6 +139,8 @@ def load() -> C.CDLL:
                                            C.c_size_t, C.c_void_p]
         lib.dls_schedule_batch_static.restype = C.c_int
         lib.dls_schedule_batch_static.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsResult), C.c_int, C.c_void_p]
+        lib.dls_set_stream_path.restype = C.c_int
+        lib.dls_set_stream_path.argtypes = [C.c_int]
         lib.dls_priorities.restype = C.c_int
         lib.dls_priorities.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsPrio), C.c_void_p, C.c_size_t, C.c_void_p]
         lib.dls_launch_count.restype = C.c_int64

@@ -173,13 +173,17 @@ def workspace_bytes(dev_batch: DeviceBatch, mask: int) -> int:
     return int(N.load().dls_workspace_bytes(C.byref(dev_batch.struct), mask))
 
 
-def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool = True, cached: bool = True,
+def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool = False, cached: bool = False,
                    workspace=None, result: Optional[BatchResult] = None) -> BatchResult:
     """Run the algorithms in `algo_mask` over every instance of `batch` on the GPU.
 
     `batch` is a host `DagBatch` (copied to HBM here) or an already resident `DeviceBatch`. Work is enqueued
     on torch's current stream of `device`; the returned BatchResult holds device tensors (synchronise / call
     `.host()` to read them). Raises DlsError on a library error; infeasible tasks are data, not errors.
+
+    `peak` (extension: per-node peak memory) and `cached` (final Node.cached_params as bitmasks) are produced by
+    the general warp-per-DAG kernels only; asking for either keeps the whole batch off the faster thread-per-DAG
+    path, so leave them off for sweeps.
     """
     torch = _torch()
     lib = N.load()

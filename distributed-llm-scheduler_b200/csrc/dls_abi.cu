@@ -17,7 +17,11 @@ std::atomic<int64_t> g_launches{0};
 dls::Profiler g_prof;
 const char* const kKernelNames[DLS_NUM_KERNELS] = {"priority_topology_kernel", "priority_critical_kernel",
                                                    "sched_simple_kernel<DFS>", "sched_simple_kernel<Greedy>",
-                                                   "sched_simple_kernel<Critical>", "sched_mru_kernel"};
+                                                   "sched_simple_kernel<Critical>", "sched_mru_kernel",
+                                                   "param_class_kernel", "stream_build_kernel",
+                                                   "sched_stream_kernel<DFS>", "sched_stream_kernel<Greedy>",
+                                                   "sched_stream_kernel<Critical>", "sched_stream_mru_kernel",
+                                                   "unpermute_kernel"};
 
 int fail(int code, const std::string& msg) {
   g_err = msg;
@@ -30,11 +34,17 @@ size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 struct Layout {
   size_t off_depth, off_outdeg, off_order_dg, off_order_mru, off_order_cp, off_up, off_succ_ptr, off_succ_idx,
       off_status, total;
+  // streamed path (present when `stream` is set)
+  size_t off_sid, off_erank, off_nshared, off_stream[3], off_ext[3], off_node_pos, off_route;
+  bool stream;
   int cp_per_instance;
 };
 
-Layout layout_of(const dls_batch_t& b) {
+int count_bits(int m) { int c = 0; for (; m; m &= m - 1) ++c; return c; }
+
+Layout layout_of(const dls_batch_t& b, int algo_mask = DLS_MASK_ALL, bool stream = false) {
   Layout L;
+  L.stream = stream;
   L.cp_per_instance = !(b.T == 1 && !(b.flags & DLS_F_DUR_PER_INSTANCE));
   const size_t nt = (size_t)b.nt_topo, ncp = (size_t)(L.cp_per_instance ? b.nt_inst : b.nt_topo);
   size_t o = 0;
@@ -47,6 +57,25 @@ Layout layout_of(const dls_batch_t& b) {
   L.off_succ_ptr = o;  o = align_up(o + (nt + (size_t)b.T) * sizeof(uint32_t));
   L.off_succ_idx = o;  o = align_up(o + (size_t)b.e_total * sizeof(uint16_t));
   L.off_status = o;    o = align_up(o + (size_t)b.T * sizeof(int32_t));
+  for (int k = 0; k < 3; ++k) L.off_stream[k] = L.off_ext[k] = 0;
+  L.off_sid = L.off_erank = L.off_nshared = L.off_node_pos = L.off_route = 0;
+  if (stream) {
+    const size_t np = (size_t)(b.T == 1 ? b.P_max : b.np_inst);
+    const size_t next = (size_t)(b.e_total + b.r_total) * (size_t)(b.T == 1 ? b.B : 1);
+    const int A = count_bits(algo_mask & DLS_MASK_ALL);
+    L.off_sid = o;     o = align_up(o + np * sizeof(uint16_t));
+    L.off_erank = o;   o = align_up(o + np * sizeof(uint16_t));
+    L.off_nshared = o; o = align_up(o + (size_t)b.T * sizeof(int32_t));
+    const bool need[3] = {(algo_mask & 3) != 0, (algo_mask & (1 << DLS_ALGO_CRITICAL)) != 0,
+                          (algo_mask & (1 << DLS_ALGO_MRU)) != 0};
+    for (int k = 0; k < 3; ++k) {
+      if (!need[k]) continue;
+      L.off_stream[k] = o; o = align_up(o + (size_t)b.nt_inst * 32);
+      L.off_ext[k] = o;    o = align_up(o + next * sizeof(uint16_t) + 64);
+    }
+    L.off_node_pos = o; o = align_up(o + (size_t)A * (size_t)b.nt_inst);
+    L.off_route = o;    o = align_up(o + (size_t)A * (size_t)b.B);
+  }
   L.total = o;
   return L;
 }
@@ -64,6 +93,20 @@ dls::Workspace carve(void* base, const Layout& L) {
   w.succ_idx = reinterpret_cast<uint16_t*>(p + L.off_succ_idx);
   w.topo_status = reinterpret_cast<int32_t*>(p + L.off_status);
   w.cp_per_instance = L.cp_per_instance;
+  w.par_sid = nullptr; w.erank = nullptr; w.nshared = nullptr; w.node_pos = nullptr; w.route = nullptr;
+  for (int k = 0; k < 3; ++k) { w.stream[k] = nullptr; w.ext[k] = nullptr; }
+  if (L.stream) {
+    w.par_sid = reinterpret_cast<uint16_t*>(p + L.off_sid);
+    w.erank = reinterpret_cast<uint16_t*>(p + L.off_erank);
+    w.nshared = reinterpret_cast<int32_t*>(p + L.off_nshared);
+    for (int k = 0; k < 3; ++k) {
+      if (!L.off_stream[k]) continue;
+      w.stream[k] = reinterpret_cast<dls::Rec*>(p + L.off_stream[k]);
+      w.ext[k] = reinterpret_cast<uint16_t*>(p + L.off_ext[k]);
+    }
+    w.node_pos = reinterpret_cast<int8_t*>(p + L.off_node_pos);
+    w.route = reinterpret_cast<uint8_t*>(p + L.off_route);
+  }
   return w;
 }
 
@@ -106,6 +149,8 @@ int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
   return DLS_OK;
 }
 
+bool g_stream_enabled = true;
+
 int cuda_fail(cudaError_t e, const char* why) {
   return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
 }
@@ -138,6 +183,42 @@ int static_scratch_address(void** out) {
   return DLS_OK;
 }
 
+// Enqueue everything for one batch. `ws_bytes` is what the caller provided; the streamed (thread-per-DAG) path is
+// used when the batch qualifies and its larger scratch fits, otherwise the warp-per-DAG kernels do all the work.
+int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace, size_t ws_bytes,
+                 void* cuda_stream, bool clear_status) {
+  const int lim = smem_limit();
+  bool stream = g_stream_enabled && dls::stream_path_possible(*batch, result, lim);
+  Layout L = layout_of(*batch, algo_mask, stream);
+  if (stream && ws_bytes < L.total) {
+    stream = false;
+    L = layout_of(*batch, algo_mask, false);
+  }
+  if (!workspace || ws_bytes < L.total) {
+    char buf[200];
+    snprintf(buf, sizeof buf, "scratch of %zu bytes is smaller than the %zu bytes this batch needs", ws_bytes, L.total);
+    return fail(DLS_ERR_WORKSPACE, buf);
+  }
+  if (reinterpret_cast<uintptr_t>(workspace) % kAlign) return fail(DLS_ERR_WORKSPACE, "workspace must be 256-byte aligned");
+  const dls::Workspace w = carve(workspace, L);
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  ctx.prof = g_prof.on ? &g_prof : nullptr;
+  cudaError_t e = cudaSuccess;
+  if (clear_status) {
+    e = cudaMemsetAsync(w.topo_status, 0, (size_t)batch->T * sizeof(int32_t), ctx.st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(built-in scratch)");
+  }
+  e = dls::launch_priority(*batch, w, algo_mask, ctx);
+  if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
+  if (e == cudaSuccess && stream) e = dls::launch_stream_sched(*batch, *result, w, algo_mask, ctx);
+  if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -149,9 +230,10 @@ const char* dls_last_error(void) { return g_err.c_str(); }
 int64_t dls_launch_count(void) { return g_launches.load(); }
 
 size_t dls_workspace_bytes(const dls_batch_t* batch, int algo_mask) {
-  (void)algo_mask;
   if (!batch) return 0;
-  return layout_of(*batch).total;
+  // Size for the larger of the two paths; which one runs is decided per call (see run_schedule).
+  const bool stream = dls::stream_path_possible(*batch, nullptr, 227 * 1024);
+  return layout_of(*batch, algo_mask, stream).total;
 }
 
 int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace,
@@ -160,19 +242,7 @@ int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_
   if (rc != DLS_OK) return rc;
   if (!result || !result->node_of || !result->seq_pos || !result->summary || !result->fin || !result->cnt || !result->avail)
     return fail(DLS_ERR_BAD_ARG, "NULL required output in result");
-  const Layout L = layout_of(*batch);
-  if (!workspace || workspace_bytes < L.total) return fail(DLS_ERR_WORKSPACE, "workspace smaller than dls_workspace_bytes()");
-  if (reinterpret_cast<uintptr_t>(workspace) % kAlign) return fail(DLS_ERR_WORKSPACE, "workspace must be 256-byte aligned");
-  const dls::Workspace w = carve(workspace, L);
-  dls::LaunchCtx ctx;
-  ctx.st = static_cast<cudaStream_t>(cuda_stream);
-  ctx.prof = g_prof.on ? &g_prof : nullptr;
-  cudaError_t e = dls::launch_priority(*batch, w, algo_mask, ctx);
-  if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
-  g_launches += ctx.launches;
-  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
-  g_err.clear();
-  return DLS_OK;
+  return run_schedule(batch, result, algo_mask, workspace, workspace_bytes, cuda_stream, false);
 }
 
 // See include/dls.h. Same work as dls_schedule_batch; the only difference is where the scratch lives.
@@ -181,7 +251,7 @@ int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, in
   if (rc != DLS_OK) return rc;
   if (!result || !result->node_of || !result->seq_pos || !result->summary || !result->fin || !result->cnt || !result->avail)
     return fail(DLS_ERR_BAD_ARG, "NULL required output in result");
-  const Layout L = layout_of(*batch);
+  const Layout L = layout_of(*batch, algo_mask, false);  // smallest scratch this batch can run with
   if (L.total > (size_t)DLS_STATIC_SCRATCH_BYTES) {
     char buf[200];
     snprintf(buf, sizeof buf,
@@ -192,20 +262,17 @@ int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, in
   void* base = nullptr;
   rc = static_scratch_address(&base);  // first call on this device: resolves the array's device address
   if (rc != DLS_OK) return rc;
-  const dls::Workspace w = carve(base, L);
-  dls::LaunchCtx ctx;
-  ctx.st = static_cast<cudaStream_t>(cuda_stream);
-  ctx.prof = g_prof.on ? &g_prof : nullptr;
   // The array still holds whatever the previous call left. The per-topology status words are the one region the
-  // scheduling kernels trust before looking at anything else, so they start from zero on every call.
-  cudaError_t e = cudaMemsetAsync(w.topo_status, 0, (size_t)batch->T * sizeof(int32_t), ctx.st);
-  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(built-in scratch)");
-  e = dls::launch_priority(*batch, w, algo_mask, ctx);
-  if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
-  g_launches += ctx.launches;
-  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
-  g_err.clear();
-  return DLS_OK;
+  // scheduling kernels trust before looking at anything else, so run_schedule clears them on the stream first.
+  return run_schedule(batch, result, algo_mask, base, (size_t)DLS_STATIC_SCRATCH_BYTES, cuda_stream, true);
+}
+
+/* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
+ * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
+int dls_set_stream_path(int enabled) {
+  const int old = g_stream_enabled ? 1 : 0;
+  g_stream_enabled = enabled != 0;
+  return old;
 }
 
 int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, size_t workspace_bytes, void* cuda_stream) {

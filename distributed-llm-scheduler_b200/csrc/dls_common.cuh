@@ -27,7 +27,31 @@ struct Workspace {
   uint16_t* succ_idx;   // [e_total]
   int32_t* topo_status; // [T]         0 ok, DLS_ST_BAD_TOPOLOGY
   int cp_per_instance;  // order_cp/up indexed per instance (T==B or per-instance durations) or per topology
+  // ---- streamed (thread-per-DAG) path; all null when that path is not used ----
+  uint16_t* par_sid;    // [np_topo]   dense id of a param shared by >= 2 tasks, 0xFFFF if private to one task
+  uint16_t* erank;      // [np_topo]   MRU eviction order of private params (valid when nshared == 0)
+  int32_t* nshared;     // [T]
+  struct Rec* stream[3];   // [nt_inst] task records in processing order: 0 DFS/Greedy, 1 Critical, 2 MRU
+  uint16_t* ext[3];        // overflow lists (dependencies beyond 3, params beyond 2), e+r entries per instance
+  int8_t* node_pos;     // [A][nt_inst] verdict per order position (node, -1 failed, -2 pending)
+  uint8_t* route;       // [A][B]      1 = instance left to the warp-per-DAG kernel
 };
+
+// One task in processing order, everything kernel S needs for a step in 32 bytes (one DRAM sector).
+struct __align__(16) Rec {
+  double m;          // Task.memory_required
+  double c;          // Task.compute_time
+  uint16_t pred[3];  // order positions of the first three dependencies
+  uint16_t npred;    // number of dependencies (beyond 3: ext list)
+  uint16_t a0, a1;   // DFS/Greedy/Critical: first two shared-param ids; MRU: eviction-order slots of first two params
+  uint16_t npriv;    // DFS/Greedy/Critical: params private to this task; MRU: all params of the task
+  uint8_t nsh;       // shared params of the task (beyond 2: ext list); 255 = too many, instance routed to the slow kernel
+  uint8_t flags;     // bit0: first task of a round
+};
+static_assert(sizeof(Rec) == 32, "Rec must be one 32-byte sector");
+constexpr int kRecFirst = 1;
+constexpr int kStreamDG = 0, kStreamCP = 1, kStreamMRU = 2;
+constexpr int kSharedCap = 32;   // shared params per DAG the streamed DFS/Greedy/Critical kernel keeps masks for
 
 // One DAG instance resolved against the batch descriptor.
 struct Inst {
@@ -137,6 +161,45 @@ __device__ __forceinline__ double memory_requirement(double m, int params_to_loa
   return __dadd_rn(m, __dmul_rn((double)params_to_load, 0.5));
 }
 
+// Exclusive prefix sum of a[0..m) in shared memory by the whole CTA; returns the total. s_part: [blockDim/32 + 1].
+__device__ inline uint32_t block_exclusive_scan(uint32_t* a, int m, uint32_t* s_part) {
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int chunk = (m + nthr - 1) / nthr;
+  const int lo = min(tid * chunk, m), hi = min(lo + chunk, m);
+  uint32_t sum = 0;
+  for (int i = lo; i < hi; ++i) sum += a[i];
+  // scan of per-thread sums: warp scan + scan of warp totals
+  uint32_t incl = sum;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    uint32_t t = __shfl_up_sync(DLS_FULL_MASK, incl, off);
+    if ((tid & 31) >= off) incl += t;
+  }
+  const int wid = tid >> 5, nw = nthr >> 5;
+  if ((tid & 31) == 31) s_part[wid] = incl;
+  __syncthreads();
+  if (tid < 32) {
+    uint32_t v = tid < nw ? s_part[tid] : 0, inc = v;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      uint32_t t = __shfl_up_sync(DLS_FULL_MASK, inc, off);
+      if (tid >= off) inc += t;
+    }
+    if (tid < nw) s_part[tid] = inc - v;  // exclusive warp offsets
+    if (tid == 31) s_part[32] = inc;      // total
+  }
+  __syncthreads();
+  uint32_t run = s_part[wid] + (incl - sum);
+  for (int i = lo; i < hi; ++i) {
+    uint32_t t = a[i];
+    a[i] = run;
+    run += t;
+  }
+  uint32_t total = s_part[32];
+  __syncthreads();
+  return total;
+}
+
 // Optional event bracketing of every launch (dls_profile_enable / dls_profile_read).
 struct Profiler {
   static constexpr int kMaxRec = 4096;
@@ -171,6 +234,11 @@ struct LaunchCtx {
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_schedule(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                             LaunchCtx& ctx);
+cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
+cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
+                                LaunchCtx& ctx);
+bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit);
+size_t priority_smem_param(int n_max, int P_max);
 size_t priority_smem_topo(int n_max);
 size_t priority_smem_inst(int n_max);
 size_t sched_smem_simple(int n_max, int P_max);

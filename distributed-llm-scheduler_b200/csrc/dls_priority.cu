@@ -26,45 +26,6 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
   return m;
 }
 
-// Exclusive prefix sum of a[0..m) in shared memory by the whole CTA; returns the total. s_part: [blockDim/32 + 1].
-__device__ uint32_t block_exclusive_scan(uint32_t* a, int m, uint32_t* s_part) {
-  const int tid = threadIdx.x, nthr = blockDim.x;
-  const int chunk = (m + nthr - 1) / nthr;
-  const int lo = min(tid * chunk, m), hi = min(lo + chunk, m);
-  uint32_t sum = 0;
-  for (int i = lo; i < hi; ++i) sum += a[i];
-  // scan of per-thread sums: warp scan + scan of warp totals
-  uint32_t incl = sum;
-#pragma unroll
-  for (int off = 1; off < 32; off <<= 1) {
-    uint32_t t = __shfl_up_sync(DLS_FULL_MASK, incl, off);
-    if ((tid & 31) >= off) incl += t;
-  }
-  const int wid = tid >> 5, nw = nthr >> 5;
-  if ((tid & 31) == 31) s_part[wid] = incl;
-  __syncthreads();
-  if (tid < 32) {
-    uint32_t v = tid < nw ? s_part[tid] : 0, inc = v;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      uint32_t t = __shfl_up_sync(DLS_FULL_MASK, inc, off);
-      if (tid >= off) inc += t;
-    }
-    if (tid < nw) s_part[tid] = inc - v;  // exclusive warp offsets
-    if (tid == 31) s_part[32] = inc;      // total
-  }
-  __syncthreads();
-  uint32_t run = s_part[wid] + (incl - sum);
-  for (int i = lo; i < hi; ++i) {
-    uint32_t t = a[i];
-    a[i] = run;
-    run += t;
-  }
-  uint32_t total = s_part[32];
-  __syncthreads();
-  return total;
-}
-
 // dst = src stably sorted by key(task) ascending, key in [0, nkeys). Histogram by all threads, placement by
 // warp 0 walking src in order, 32 at a time, with __match_any giving each lane its rank among equal keys.
 template <class KeyF>
@@ -207,6 +168,58 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   }
 }
 
+// Classify params of one topology (one CTA each):
+//   par_sid[p] = dense id among params referenced by >= 2 tasks ("shared"), 0xFFFF for params private to one task;
+//   nshared[t] = number of shared params;
+//   erank[p]   = (only when nshared == 0) position of p in the order (depth of its owner task asc, param id asc).
+// For a private param cached after its owner ran, MRU's eviction score is 0.0 + 1*10 + 100.0/(step - last + 1) with
+// last = owner's round = depth+1 (ref schedulers.py:385-393,514-516) and never a +1000 (its only user is done), so
+// `evictable.sort()` over (score, name) (ref :420) visits such params exactly in erank order: older rounds first
+// (the score is strictly decreasing in step-last for any reachable step count), equal rounds by param id.
+__global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, Workspace w) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t s_part[33];
+  __shared__ int s_maxd;
+  const int t = blockIdx.x, tid = threadIdx.x;
+  Inst v;
+  bind_topology(b, t, v);
+  if (w.topo_status[t] != DLS_ST_OK) return;
+  const int n = v.n, P = v.P;
+  const int P_al = (P + 3) & ~3;
+  uint32_t* s_rc = reinterpret_cast<uint32_t*>(smem_raw);             // [P+2]
+  uint32_t* s_hist = s_rc + (P + 2);                                  // [n+2]
+  uint16_t* s_ownd = reinterpret_cast<uint16_t*>(s_hist + (n + 2));   // [P_al]
+  uint16_t* s_src = s_ownd + P_al;                                    // [P_al]
+  uint16_t* s_dst = s_src + P_al;                                     // [P_al]
+  const int64_t p_topo = b.pid_off[t];
+  uint16_t* g_sid = w.par_sid + p_topo;
+  uint16_t* g_erank = w.erank + p_topo;
+  const uint16_t* g_depth = w.depth + v.t_topo;
+  if (tid == 0) s_maxd = 0;
+  for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
+  __syncthreads();
+  for (uint32_t e = tid; e < v.R; e += blockDim.x) atomicAdd(&s_rc[v.par_idx[e]], 1u);
+  __syncthreads();
+  for (int p = tid; p < P; p += blockDim.x) s_rc[p] = s_rc[p] >= 2 ? 1u : 0u;
+  __syncthreads();
+  // keep the flags: after the scan, flag[p] = (scan[p+1] != scan[p])
+  const uint32_t nsh = block_exclusive_scan(s_rc, P + 1, s_part);
+  for (int p = tid; p < P; p += blockDim.x) g_sid[p] = (s_rc[p + 1] != s_rc[p]) ? (uint16_t)s_rc[p] : (uint16_t)0xFFFF;
+  if (tid == 0) w.nshared[t] = (int)nsh;
+  if (nsh != 0) return;
+  int md = 0;
+  for (int i = tid; i < n; i += blockDim.x) {
+    const int d = g_depth[i];
+    md = max(md, d);
+    for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) s_ownd[v.par_idx[e]] = (uint16_t)d;
+  }
+  atomicMax(&s_maxd, md);
+  for (int p = tid; p < P; p += blockDim.x) s_src[p] = (uint16_t)p;
+  __syncthreads();
+  stable_counting_sort(s_src, s_dst, P, s_maxd + 1, [&](int p) { return (uint32_t)s_ownd[p]; }, s_hist, s_part);
+  for (int q = tid; q < P; q += blockDim.x) g_erank[s_dst[q]] = (uint16_t)q;
+}
+
 __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
@@ -281,6 +294,11 @@ size_t priority_smem_topo(int n_max) {
   return 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
 }
 
+size_t priority_smem_param(int n_max, int P_max) {
+  size_t n = (size_t)n_max, P = (size_t)P_max, P_al = (P + 3) & ~(size_t)3;
+  return (P + 2 + n + 2) * sizeof(uint32_t) + 3 * P_al * sizeof(uint16_t);
+}
+
 size_t priority_smem_inst(int n_max) {
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
   return n * sizeof(double) + (n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
@@ -299,6 +317,19 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
   ctx.why = "priority_topology_kernel launch";
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
+  if (w.par_sid) {
+    size_t smp = priority_smem_param(b.n_max, b.P_max);
+    ctx.why = "cudaFuncSetAttribute(param_class_kernel)";
+    e = cudaFuncSetAttribute(param_class_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp);
+    if (e != cudaSuccess) return e;
+    rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PARAM_CLASS, ctx.st) : -1;
+    param_class_kernel<<<b.T, kThreadsP, smp, ctx.st>>>(b, w);
+    if (ctx.prof) ctx.prof->end(rec, ctx.st);
+    ++ctx.launches;
+    ctx.why = "param_class_kernel launch";
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
     size_t sm2 = priority_smem_inst(b.n_max);
     ctx.why = "cudaFuncSetAttribute(priority_critical_kernel)";

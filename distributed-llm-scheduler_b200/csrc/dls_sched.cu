@@ -106,6 +106,7 @@ template <int ALGO>
 __global__ void __launch_bounds__(32) sched_simple_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot) {
   extern __shared__ __align__(16) uint32_t smem[];
   const int inst = blockIdx.x, lane = threadIdx.x;
+  if (w.route && w.route[(int64_t)slot * b.B + inst] != 1) return;  // already done by the thread-per-DAG kernel
   Inst v;
   bind_instance(b, inst, v);
   const OutPtrs o = bind_out(b, r, slot, inst, v);
@@ -311,6 +312,7 @@ __device__ __forceinline__ void rcnt_add(const MruState& ms, const Inst& v, int 
 __global__ void __launch_bounds__(32) sched_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot) {
   extern __shared__ __align__(16) uint32_t smem[];
   const int inst = blockIdx.x, lane = threadIdx.x;
+  if (w.route && w.route[(int64_t)slot * b.B + inst] != 1) return;  // already done by the thread-per-DAG kernel
   Inst v;
   bind_instance(b, inst, v);
   const OutPtrs o = bind_out(b, r, slot, inst, v);

@@ -1,0 +1,697 @@
+// dls_stream.cu — the throughput path: one THREAD per DAG instance over an order-permuted record stream.
+//
+// Why: the list-scheduling loop is a serial chain of n dependent steps per DAG, but a sweep has ~10^5..10^6
+// independent DAGs. With one warp per DAG every instruction of the chain serves one DAG (≈340 warp-instructions per
+// task-step, profiles/r1a_*); with one thread per DAG the same instruction serves 32. To make that work the
+// per-thread memory accesses must not scatter: stream_build_kernel rewrites each DAG, once per processing order, as
+// a contiguous array of 32-byte records (one DRAM sector per step, dependencies already translated to order
+// positions), so every step of every thread reads exactly one fully used sector, and per-thread mutable state lives
+// in shared memory laid out [word][lane] (each lane owns a bank: no conflicts whatever the index).
+//
+// Verdicts are written in order-position space (sequential bytes per thread); unpermute_kernel maps them back to
+// task ids and derives seq_pos by a prefix count. Instances the fast kernels cannot take (more than 8 nodes, more
+// than 32 shared params, MRU with any shared param, bad topology) are flagged in `route` and picked up by the
+// warp-per-DAG kernels of dls_sched.cu, which remain the general implementation.
+//
+// All fp64 arithmetic is the same op-by-op replay as in dls_sched.cu (see the header comment there).
+#include <math.h>
+
+#include "dls_common.cuh"
+
+namespace dls {
+
+namespace {
+
+constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG kernels
+constexpr int kBuildThreads = 128;
+
+__device__ __forceinline__ int64_t ext_offset(const dls_batch_t& b, int inst, const Inst& v) {
+  return b.T == 1 ? (int64_t)inst * (int64_t)(v.E + v.R) : b.pred_off[inst] + b.par_off[inst];
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// stream_build_kernel: grid (B, 3). One CTA rewrites one instance for one processing order.
+// -------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t b, Workspace w, int kind_mask) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t s_part[33];
+  const int inst = blockIdx.x, kind = blockIdx.y, tid = threadIdx.x;
+  if (!((kind_mask >> kind) & 1)) return;
+  Inst v;
+  bind_instance(b, inst, v);
+  if (w.topo_status[v.topo] != DLS_ST_OK) return;
+  const int n = v.n;
+  if (n == 0) return;
+  const int nsh_topo = w.nshared[v.topo];
+  if (kind == kStreamMRU ? nsh_topo != 0 : nsh_topo > kSharedCap) return;  // routed to the general kernels
+  uint32_t* s_extoff = reinterpret_cast<uint32_t*>(smem_raw);           // [n+1]
+  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));    // [n] task -> order position
+  const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
+                        : kind == kStreamMRU ? w.order_mru + v.t_topo
+                                             : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
+  const uint16_t* depth = w.depth + v.t_topo;
+  const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
+  const uint16_t* erank = w.erank + b.pid_off[v.topo];
+  Rec* out = w.stream[kind] + v.t_inst;
+  uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
+
+  for (int t = tid; t < n; t += blockDim.x) {
+    const int i = order[t];
+    s_pos[i] = (uint16_t)t;
+    const int npred = (int)(v.pred_ptr[i + 1] - v.pred_ptr[i]);
+    int extra = max(0, npred - 3);
+    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+    if (kind == kStreamMRU) {
+      extra += max(0, (int)(qe - qb) - 2);
+    } else {
+      int nsh = 0;
+      for (uint32_t e = qb; e < qe; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
+      extra += max(0, nsh - 2);
+    }
+    s_extoff[t] = (uint32_t)extra;
+  }
+  if (tid == 0) s_extoff[n] = 0;
+  __syncthreads();
+  block_exclusive_scan(s_extoff, n + 1, s_part);
+  for (int t = tid; t < n; t += blockDim.x) {
+    const int i = order[t];
+    Rec rc;
+    rc.m = v.mem[i];
+    rc.c = v.dur[i];
+    const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
+    uint32_t xo = s_extoff[t];
+    rc.pred[0] = rc.pred[1] = rc.pred[2] = 0;
+    rc.npred = (uint16_t)min(pe - pb, 65535u);
+    for (uint32_t e = pb; e < pe; ++e) {
+      const uint16_t pp = s_pos[v.pred_idx[e]];
+      if (e - pb < 3) rc.pred[e - pb] = pp;
+      else ext[xo++] = pp;
+    }
+    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+    rc.a0 = rc.a1 = 0;
+    if (kind == kStreamMRU) {
+      rc.npriv = (uint16_t)(qe - qb);
+      rc.nsh = 0;
+      for (uint32_t e = qb; e < qe; ++e) {
+        const uint16_t slot = erank[v.par_idx[e]];
+        if (e - qb == 0) rc.a0 = slot;
+        else if (e - qb == 1) rc.a1 = slot;
+        else ext[xo++] = slot;
+      }
+    } else {
+      int nsh = 0, npriv = 0;
+      for (uint32_t e = qb; e < qe; ++e) {
+        const uint16_t s = sid[v.par_idx[e]];
+        if (s == 0xFFFF) { ++npriv; continue; }
+        if (nsh == 0) rc.a0 = s;
+        else if (nsh == 1) rc.a1 = s;
+        else ext[xo++] = s;
+        ++nsh;
+      }
+      rc.npriv = (uint16_t)npriv;
+      rc.nsh = (uint8_t)min(nsh, 255);
+    }
+    rc.flags = (t == 0 || depth[order[t - 1]] != depth[i]) ? kRecFirst : 0;
+    out[t] = rc;
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// Shared pieces of the thread-per-DAG kernels
+// -------------------------------------------------------------------------------------------------------------------
+struct RecRegs {
+  uint4 lo, hi;
+};
+__device__ __forceinline__ RecRegs load_rec(const Rec* p) {
+  RecRegs r;
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  r.lo = __ldg(q);
+  r.hi = __ldg(q + 1);
+  return r;
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// Per-warp shared-memory slab: word `wd` of the calling lane.
+struct Slab {
+  uint32_t* u;  // [words][32]
+  double* d;    // [dwords][32]
+  int lane;
+  __device__ __forceinline__ uint32_t& w(int wd) const { return u[wd * 32 + lane]; }
+  __device__ __forceinline__ double& f(int k) const { return d[k * 32 + lane]; }
+};
+
+template <int KMAX>
+__device__ __forceinline__ double pick(const double (&a)[KMAX], int k) {
+  double x = a[0];
+#pragma unroll
+  for (int j = 1; j < KMAX; ++j) x = (k == j) ? a[j] : x;
+  return x;
+}
+
+struct ThreadOut {
+  int completed, failed, hits, misses, rounds, status;
+  bool fail_rest;
+};
+
+template <int KMAX>
+__device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int slot,
+                                              int inst, const Inst& v, const double (&avail)[KMAX], const Slab& sl,
+                                              int fin_base, int cnt_base, const ThreadOut& to) {
+  const int64_t ko = (int64_t)slot * b.nk_inst + v.k_out;
+  double mk = 0.0;
+  bool any = false;
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    if (k < v.K) {
+      const double f = sl.f(fin_base + k);
+      const int c = (int)sl.w(cnt_base + k);
+      r.fin[ko + k] = f;
+      r.cnt[ko + k] = c;
+      r.avail[ko + k] = avail[k];
+      if (c > 0 && (!any || f > mk)) { mk = f; any = true; }
+    }
+  }
+  dls_summary_t s;
+  s.makespan = any ? mk : 0.0;
+  s.completed = to.completed;
+  s.failed = to.fail_rest ? v.n - to.completed : to.failed;
+  s.pending = v.n - s.completed - s.failed;
+  s.hits = to.hits;
+  s.misses = to.misses;
+  s.rounds = to.rounds;
+  s.status = to.status;
+  s.reserved = 0;
+  r.summary[(int64_t)slot * b.B + inst] = s;
+  w.route[(int64_t)slot * b.B + inst] = to.fail_rest ? 2 : 0;
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// DFS / Greedy / Critical, one thread per DAG
+// -------------------------------------------------------------------------------------------------------------------
+template <int ALGO, int KMAX>
+__global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int nw_done) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  // slab layout per warp: doubles fin[KMAX], spd[KMAX]; words done[nw_done], smask[kSharedCap/4], cnt[KMAX]
+  constexpr int kD = 2 * KMAX;
+  const int kW = nw_done + kSharedCap / 4 + KMAX;
+  const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
+  Slab sl;
+  sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
+  sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
+  sl.lane = lane;
+  const int FIN = 0, SPD = KMAX, DONE = 0, SMASK = nw_done, CNT = nw_done + kSharedCap / 4;
+
+  const int inst = blockIdx.x * kTPB + threadIdx.x;
+  const bool have = inst < b.B;
+  Inst v;
+  v.n = 0; v.K = 0; v.topo = 0; v.t_inst = 0;
+  bool elig = false;
+  if (have) {
+    bind_instance(b, inst, v);
+    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] <= kSharedCap;
+    if (!elig) w.route[(int64_t)slot * b.B + inst] = 1;
+  }
+  const int n = elig ? v.n : 0, K = v.K;
+  const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
+  if (n_warp == 0) return;
+  constexpr int kind = ALGO == DLS_ALGO_CRITICAL ? kStreamCP : kStreamDG;
+  const Rec* rec = w.stream[kind] + v.t_inst;
+  const uint16_t* ext = w.ext[kind] + (elig ? ext_offset(b, inst, v) : 0);
+  int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+
+  double avail[KMAX], spd[ALGO == DLS_ALGO_CRITICAL ? KMAX : 1];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    const bool on = elig && k < K;
+    avail[k] = on ? v.cap[k] : 0.0;
+    const double s = on ? v.spd[k] : 1.0;
+    if constexpr (ALGO == DLS_ALGO_CRITICAL) spd[k] = s;
+    sl.f(FIN + k) = 0.0;
+    sl.f(SPD + k) = s;
+    sl.w(CNT + k) = 0;
+  }
+  for (int x = 0; x < nw_done + kSharedCap / 4; ++x) sl.w(x) = 0;
+
+  ThreadOut to;
+  to.completed = to.failed = to.hits = to.misses = to.rounds = 0;
+  to.status = DLS_ST_OK;
+  to.fail_rest = false;
+  bool running = elig, any_ready = false, any_assigned = false;
+  uint32_t curw = 0;
+  uint32_t xpos = 0;
+  RecRegs cur;
+  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
+  if (n > 0) cur = load_rec(rec);
+  for (int t = 0; t < n_warp; ++t) {
+    RecRegs nxt = cur;
+    if (t + 1 < n) nxt = load_rec(rec + t + 1);
+    if (t + 8 < n) prefetch_l2(rec + t + 8);
+    if (t < n) {
+      const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
+      const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
+      const int npred = cur.hi.y >> 16, npriv = cur.hi.w & 0xffff, nsh = (cur.hi.w >> 16) & 0xff;
+      const int flags = cur.hi.w >> 24;
+      if ((t & 31) == 0) curw = 0;
+      if (flags & kRecFirst) {
+        if (t > 0 && running) {
+          if (!any_ready) running = false;                       // ready list empty (ref schedulers.py:172-174)
+          else if (!any_assigned) { running = false; to.fail_rest = true; }  // no progress (ref :202-206)
+        }
+        if (running) { ++to.rounds; any_ready = any_assigned = false; }
+      }
+      int verdict = DLS_TASK_PENDING;
+      const uint32_t x_pred = xpos, x_sh = xpos + (uint32_t)max(0, npred - 3);
+      xpos = x_sh + (uint32_t)max(0, nsh - 2);
+      if (running) {
+        auto done_bit = [&](int p) -> bool {
+          const uint32_t wd = ((p >> 5) == (t >> 5)) ? curw : sl.w(DONE + (p >> 5));
+          return (wd >> (p & 31)) & 1u;
+        };
+        bool ready = true;
+        if (npred > 0) ready = done_bit(cur.hi.x & 0xffff);
+        if (npred > 1) ready = ready && done_bit(cur.hi.x >> 16);
+        if (npred > 2) ready = ready && done_bit(cur.hi.y & 0xffff);
+        for (int j = 3; j < npred; ++j) ready = ready && done_bit(ext[x_pred + j - 3]);
+        if (ready) {
+          any_ready = true;
+          // shared params not yet cached, per node, packed one byte per node
+          unsigned long long miss = 0;
+          for (int j = 0; j < nsh; ++j) {
+            const int s = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
+            const uint32_t mask = (sl.w(SMASK + (s >> 2)) >> ((s & 3) * 8)) & 0xffu;
+            const unsigned long long spread = ((unsigned long long)(mask ^ 0xffu) * 0x0101010101010101ull) & 0x8040201008040201ull;
+            miss += ((spread + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
+          }
+          const double need0 = memory_requirement(m, npriv);
+          int best = -1, lbest = 0;
+          double bv = ALGO == DLS_ALGO_DFS ? -1.0 : 0.0;  // max_memory = -1 (ref :187) / best_speed = 0 (ref :353)
+          int bl = 0x7fffffff;                             // min_params_to_load = inf (ref :268)
+#pragma unroll
+          for (int k = 0; k < KMAX; ++k) {
+            const int lk = npriv + (int)((miss >> (8 * k)) & 0xffull);
+            const double need = nsh ? memory_requirement(m, lk) : need0;
+            const bool fits = k < K && need <= avail[k];  // can_fit_on_node (ref :74-76)
+            bool take;
+            double key = avail[k];
+            if constexpr (ALGO == DLS_ALGO_DFS) take = fits && avail[k] > bv;                         // ref :190
+            else if constexpr (ALGO == DLS_ALGO_GREEDY) take = fits && (lk < bl || (lk == bl && avail[k] > bv));  // ref :276-278
+            else { key = spd[k]; take = fits && key > bv; }                                           // ref :356
+            if (take) {
+              best = k;
+              lbest = lk;
+              bl = lk;
+              bv = key;
+            }
+          }
+          if (best >= 0) {
+            double a = pick<KMAX>(avail, best);
+            for (int j = 0; j < lbest; ++j) a = __dsub_rn(a, 0.5);  // node.available_memory -= 0.5 per loaded param (ref :89)
+            a = __dsub_rn(a, m);                                     // ref :95
+            a = __dadd_rn(a, m);                                     // complete_task frees it again (ref :126)
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
+            sl.f(FIN + best) = __dadd_rn(sl.f(FIN + best), __ddiv_rn(c, sl.f(SPD + best)));  // ref simulation.py:261-264
+            sl.w(CNT + best) += 1;
+            to.misses += lbest;
+            to.hits += npriv + nsh - lbest;
+            for (int j = 0; j < nsh; ++j) {
+              const int s = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
+              sl.w(SMASK + (s >> 2)) |= (1u << best) << ((s & 3) * 8);
+            }
+            curw |= 1u << (t & 31);
+            sl.w(DONE + (t >> 5)) = curw;
+            verdict = best;
+            ++to.completed;
+            any_assigned = true;
+          } else {
+            verdict = DLS_TASK_FAILED;  // fail_task (ref :128-131)
+            ++to.failed;
+          }
+        }
+      }
+      npos[t] = (int8_t)verdict;
+    }
+    cur = nxt;
+  }
+  if (elig) {
+    if (running) {
+      if (any_ready && !any_assigned) to.fail_rest = true;
+      else if (any_ready && to.completed + to.failed < n) ++to.rounds;  // one more iteration finds nothing ready
+    }
+    finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, to);
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// MRU for DAGs whose params are all private to one task, one thread per DAG.
+// Node k's cached params are the slots of `pnode` holding k (4 bits per slot, slots in eviction order, 0xF = not
+// cached); evicting = taking the lowest slots that hold k. curs[k] is a lower bound of the first such slot.
+// -------------------------------------------------------------------------------------------------------------------
+template <int KMAX>
+struct MruNodes {
+  double avail[KMAX];
+};
+
+__device__ __forceinline__ uint32_t nibble_eq_mask(uint32_t word, uint32_t k) {
+  // bit 4j+3 set iff nibble j of `word` equals k
+  const uint32_t x = word ^ (k * 0x11111111u);
+  return ~(((x & 0x77777777u) + 0x77777777u) | x) & 0x88888888u;
+}
+
+// evict_params_for_task (ref schedulers.py:404-442) on node k. Returns the reference's bool; updates avail_k, pnode
+// and the cursor. Candidates are visited in slot order (== sorted (score, name) order, see param_class_kernel).
+__device__ bool evict_private(const Slab& sl, int PN, int nslots, int k, double need, double& avail_k, uint32_t& cursor) {
+  const double shortage = __dsub_rn(need, avail_k);
+  if (shortage <= 0.0) return true;
+  double freed = 0.0;
+  int nev = 0;
+  uint32_t pos = cursor;       // first slot not yet examined
+  uint32_t first_hit = 0xffffffffu;
+  const uint32_t nwords = (uint32_t)(nslots + 7) >> 3;
+  bool ok = false;
+  uint32_t wd = pos >> 3;
+  uint32_t hits = wd < nwords ? (nibble_eq_mask(sl.w(PN + wd), (uint32_t)k) & (0xffffffffu << ((pos & 7) * 4))) : 0;
+  while (true) {
+    if (freed >= shortage) { ok = true; break; }
+    while (hits == 0 && ++wd < nwords) hits = nibble_eq_mask(sl.w(PN + wd), (uint32_t)k);
+    if (wd >= nwords) break;  // candidates exhausted
+    const uint32_t bit = __ffs(hits) - 1;
+    hits &= hits - 1;
+    const uint32_t slot = (wd << 3) + (bit >> 2);
+    if (first_hit == 0xffffffffu) first_hit = slot;
+    pos = slot + 1;
+    avail_k = __dadd_rn(avail_k, 0.5);  // ref :429
+    freed = __dadd_rn(freed, 0.5);      // ref :431
+    ++nev;
+  }
+  if (ok) {
+    // commit: clear the nev lowest slots of node k starting at first_hit (they are exactly the ones counted above)
+    uint32_t w2 = first_hit >> 3;
+    int left = nev;
+    uint32_t h2 = nibble_eq_mask(sl.w(PN + w2), (uint32_t)k) & (0xffffffffu << ((first_hit & 7) * 4));
+    while (left > 0) {
+      while (h2 == 0) h2 = nibble_eq_mask(sl.w(PN + (++w2)), (uint32_t)k);
+      uint32_t word = sl.w(PN + w2);
+      while (h2 && left > 0) {
+        const uint32_t bit = __ffs(h2) - 1;
+        h2 &= h2 - 1;
+        word |= 0xFu << (bit - 3);
+        --left;
+      }
+      sl.w(PN + w2) = word;
+    }
+    cursor = pos;
+  } else {
+    for (int j = 0; j < nev; ++j) avail_k = __dsub_rn(avail_k, 0.5);  // rollback (ref :438-441); nothing was cleared
+    cursor = first_hit == 0xffffffffu ? (uint32_t)nslots : first_hit;
+  }
+  return ok;
+}
+
+template <int KMAX>
+__global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+                                                                int nw_done, int nw_pn) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  // slab per warp: doubles fin[KMAX], spd[KMAX]; words done[nw_done], pnode[nw_pn], cnt[KMAX], curs[KMAX]
+  constexpr int kD = 2 * KMAX;
+  const int kW = nw_done + nw_pn + 2 * KMAX;
+  const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
+  Slab sl;
+  sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
+  sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
+  sl.lane = lane;
+  const int FIN = 0, SPD = KMAX, DONE = 0, PN = nw_done, CNT = nw_done + nw_pn, CURS = CNT + KMAX;
+
+  const int inst = blockIdx.x * kTPB + threadIdx.x;
+  const bool have = inst < b.B;
+  Inst v;
+  v.n = 0; v.K = 0; v.topo = 0; v.P = 0; v.t_inst = 0;
+  bool elig = false;
+  if (have) {
+    bind_instance(b, inst, v);
+    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] == 0 && v.P <= nw_pn * 8;
+    if (!elig) w.route[(int64_t)slot * b.B + inst] = 1;
+  }
+  const int n = elig ? v.n : 0, K = v.K, nslots = v.P;
+  const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
+  if (n_warp == 0) return;
+  const Rec* rec = w.stream[kStreamMRU] + v.t_inst;
+  const uint16_t* ext = w.ext[kStreamMRU] + (elig ? ext_offset(b, inst, v) : 0);
+  int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+
+  double avail[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    const bool on = elig && k < K;
+    avail[k] = on ? v.cap[k] : 0.0;
+    sl.f(FIN + k) = 0.0;
+    sl.f(SPD + k) = on ? v.spd[k] : 1.0;
+    sl.w(CNT + k) = 0;
+    sl.w(CURS + k) = (uint32_t)nslots;  // nothing cached yet
+  }
+  for (int x = 0; x < nw_done; ++x) sl.w(DONE + x) = 0;
+  for (int x = 0; x < nw_pn; ++x) sl.w(PN + x) = 0xffffffffu;
+
+  ThreadOut to;
+  to.completed = to.failed = to.hits = to.misses = to.rounds = 0;
+  to.status = DLS_ST_OK;
+  to.fail_rest = false;
+  int carried = 0;
+  bool running = elig, any_ready = false, any_assigned = false;
+  uint32_t curw = 0, xpos = 0;
+  RecRegs cur;
+  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
+  if (n > 0) cur = load_rec(rec);
+  for (int t = 0; t < n_warp; ++t) {
+    RecRegs nxt = cur;
+    if (t + 1 < n) nxt = load_rec(rec + t + 1);
+    if (t + 8 < n) prefetch_l2(rec + t + 8);
+    if (t < n) {
+      const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
+      const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
+      const int npred = cur.hi.y >> 16, npar = cur.hi.w & 0xffff;
+      const int flags = cur.hi.w >> 24;
+      if ((t & 31) == 0) curw = 0;
+      if (flags & kRecFirst) {
+        if (t > 0 && running) {
+          if (!any_ready) running = false;
+          else if (!any_assigned) { running = false; to.fail_rest = true; }
+        }
+        if (running) { ++to.rounds; any_ready = any_assigned = false; }  // self.time_step += 1 (ref :453)
+      }
+      int verdict = DLS_TASK_PENDING;
+      const uint32_t x_pred = xpos, x_par = xpos + (uint32_t)max(0, npred - 3);
+      xpos = x_par + (uint32_t)max(0, npar - 2);
+      if (running) {
+        auto done_bit = [&](int p) -> bool {
+          const uint32_t wd = ((p >> 5) == (t >> 5)) ? curw : sl.w(DONE + (p >> 5));
+          return (wd >> (p & 31)) & 1u;
+        };
+        bool ready = true;
+        if (npred > 0) ready = done_bit(cur.hi.x & 0xffff);
+        if (npred > 1) ready = ready && done_bit(cur.hi.x >> 16);
+        if (npred > 2) ready = ready && done_bit(cur.hi.y & 0xffff);
+        for (int j = 3; j < npred; ++j) ready = ready && done_bit(ext[x_pred + j - 3]);
+        if (ready) {
+          any_ready = true;
+          // none of the task's (private) params is cached anywhere: params_to_load = npar on every node
+          const double need = memory_requirement(m, npar);
+          int best = -1;
+          double best_score = -INFINITY;
+#pragma unroll
+          for (int k = 0; k < KMAX; ++k) {
+            if (k < K) {
+              double score = 0.0;
+              score = __dadd_rn(score, 0.0);  // cached * 20 with cached == 0 (ref :486-487)
+              bool cand = true;
+              if (need <= avail[k]) {
+                score = __dadd_rn(score, avail[k]);  // ref :490-491
+              } else {
+                uint32_t cu = sl.w(CURS + k);
+                const bool ok = evict_private(sl, PN, nslots, k, need, avail[k], cu);  // mutates the node (ref :492)
+                sl.w(CURS + k) = cu;
+                if (ok) score = __dadd_rn(score, 5.0);
+                else cand = false;
+              }
+              score = __dsub_rn(score, __dmul_rn((double)(int)sl.w(CNT + k), 0.5));  // ref :498
+              if (cand && score > best_score) { best_score = score; best = k; }
+            }
+          }
+          if (best >= 0) {
+            double a = pick<KMAX>(avail, best);
+            if (!(need <= a)) {  // ref :506-507
+              uint32_t cu = sl.w(CURS + best);
+              evict_private(sl, PN, nslots, best, need, a, cu);
+              sl.w(CURS + best) = cu;
+            }
+            if (need > a) {
+              // assign_task_to_node refuses (ref :82-83): the reference retries next round; flagged, not replayed
+              to.status |= DLS_ST_CARRY;
+              ++carried;
+#pragma unroll
+              for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
+            } else {
+              for (int j = 0; j < npar; ++j) a = __dsub_rn(a, 0.5);
+              a = __dsub_rn(a, m);
+              a = __dadd_rn(a, m);
+#pragma unroll
+              for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
+              sl.f(FIN + best) = __dadd_rn(sl.f(FIN + best), __ddiv_rn(c, sl.f(SPD + best)));
+              sl.w(CNT + best) += 1;
+              to.misses += npar;
+              uint32_t cu = sl.w(CURS + best);
+              for (int j = 0; j < npar; ++j) {
+                const uint32_t s = j == 0 ? (cur.hi.z & 0xffff) : j == 1 ? (cur.hi.z >> 16) : (uint32_t)ext[x_par + j - 2];
+                const uint32_t sh = (s & 7) * 4;
+                uint32_t& word = sl.w(PN + (s >> 3));
+                word = (word & ~(0xFu << sh)) | ((uint32_t)best << sh);  // node.cached_params.add(param)
+                cu = min(cu, s);
+              }
+              sl.w(CURS + best) = cu;
+              curw |= 1u << (t & 31);
+              sl.w(DONE + (t >> 5)) = curw;
+              verdict = best;
+              ++to.completed;
+              any_assigned = true;
+            }
+          } else {
+            verdict = DLS_TASK_FAILED;
+            ++to.failed;
+          }
+        }
+      }
+      npos[t] = (int8_t)verdict;
+    }
+    cur = nxt;
+  }
+  if (elig) {
+    if (running) {
+      if (any_ready && !any_assigned) to.fail_rest = true;
+      else if (any_ready && to.completed + to.failed + carried < n) ++to.rounds;
+    }
+    finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, to);
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------------
+// unpermute_kernel: one warp per instance. node_of[order[t]] = verdict[t]; seq_pos = prefix count of assignments.
+// -------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int kind) {
+  const int inst = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (inst >= b.B) return;
+  const int route = w.route[(int64_t)slot * b.B + inst];
+  if (route == 1) return;  // the warp-per-DAG kernel writes this instance
+  Inst v;
+  bind_instance(b, inst, v);
+  const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
+                        : kind == kStreamMRU ? w.order_mru + v.t_topo
+                                             : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
+  const int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  int8_t* node_of = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
+  uint16_t* seq_pos = r.seq_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  int base = 0;
+  for (int t0 = 0; t0 < v.n; t0 += 32) {
+    const int t = t0 + lane;
+    int verdict = DLS_TASK_PENDING;
+    if (t < v.n) verdict = npos[t];
+    const unsigned asg = __ballot_sync(DLS_FULL_MASK, verdict >= 0);
+    if (t < v.n) {
+      const int i = order[t];
+      if (route == 2 && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
+      node_of[i] = (int8_t)verdict;
+      seq_pos[i] = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
+    }
+    base += __popc(asg);
+  }
+}
+
+template <int KMAX>
+size_t smem_simple(int nw_done) {
+  return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(nw_done + kSharedCap / 4 + KMAX) * 32 * 4);
+}
+template <int KMAX>
+size_t smem_mru(int nw_done, int nw_pn) {
+  return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(nw_done + nw_pn + 2 * KMAX) * 32 * 4);
+}
+
+}  // namespace
+
+// The streamed path needs K <= 8 nodes and per-thread state small enough for a useful number of resident warps.
+bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit) {
+  if (b.K_max > 8) return false;
+  if (r && (r->peak || r->cached)) return false;  // extension outputs are produced by the general kernels only
+  const int nw_done = (b.n_max + 31) / 32, nw_pn = (b.P_max + 7) / 8;
+  const size_t need = std::max(smem_simple<8>(nw_done), smem_mru<8>(nw_done, nw_pn));
+  return need <= (size_t)smem_limit / 2 && b.n_max >= 1;  // at least two CTAs (4 warps) per SM
+}
+
+template <class Kern, class... Args>
+static cudaError_t launch_fast(Kern kern, int kernel_id, dim3 grid, int threads, size_t smem, LaunchCtx& ctx, Args... args) {
+  ctx.why = "cudaFuncSetAttribute(stream kernel)";
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int rec = ctx.prof ? ctx.prof->begin(kernel_id, ctx.st) : -1;
+  kern<<<grid, threads, smem, ctx.st>>>(args...);
+  if (ctx.prof) ctx.prof->end(rec, ctx.st);
+  ++ctx.launches;
+  ctx.why = "stream kernel launch";
+  return cudaGetLastError();
+}
+
+cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
+  int kinds = 0;
+  if (algo_mask & 3) kinds |= 1 << kStreamDG;
+  if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
+  if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
+  const size_t smem = ((size_t)b.n_max + 1) * sizeof(uint32_t) + (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
+  return launch_fast(stream_build_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B, 3), kBuildThreads, smem, ctx, b, w, kinds);
+}
+
+template <int KMAX>
+static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
+                                         LaunchCtx& ctx) {
+  const int nw_done = (b.n_max + 31) / 32, nw_pn = (b.P_max + 7) / 8;
+  const dim3 grid((b.B + kTPB - 1) / kTPB), ugrid((b.B + 3) / 4);
+  int slot = 0;
+  cudaError_t e = cudaSuccess;
+  if (algo_mask & (1 << DLS_ALGO_DFS)) {
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX>, DLS_KERNEL_STREAM_DFS, grid, kTPB, smem_simple<KMAX>(nw_done),
+                    ctx, b, r, w, slot, nw_done);
+    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamDG);
+    if (e != cudaSuccess) return e;
+    ++slot;
+  }
+  if (algo_mask & (1 << DLS_ALGO_GREEDY)) {
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
+                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done);
+    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamDG);
+    if (e != cudaSuccess) return e;
+    ++slot;
+  }
+  if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
+                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done);
+    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamCP);
+    if (e != cudaSuccess) return e;
+    ++slot;
+  }
+  if (algo_mask & (1 << DLS_ALGO_MRU)) {
+    e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, grid, kTPB, smem_mru<KMAX>(nw_done, nw_pn), ctx, b,
+                    r, w, slot, nw_done, nw_pn);
+    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamMRU);
+    if (e != cudaSuccess) return e;
+    ++slot;
+  }
+  return e;
+}
+
+cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
+                                LaunchCtx& ctx) {
+  if (b.K_max <= 2) return launch_stream_sched_k<2>(b, r, w, algo_mask, ctx);
+  if (b.K_max <= 4) return launch_stream_sched_k<4>(b, r, w, algo_mask, ctx);
+  return launch_stream_sched_k<8>(b, r, w, algo_mask, ctx);
+}
+
+}  // namespace dls

@@ -295,6 +295,22 @@ class DagBatch:
             mem=self.mem[t0:t1], dur=self.dur[t0:t1], node_off=node_off, cap=cap, spd=spd,
             dags=None if self.dags is None else self.dags[lo:hi])
 
+    def repeat(self, k: int) -> "DagBatch":
+        """The batch followed by k-1 copies of itself (T == B only): cheap way to build large synthetic sweeps."""
+        assert self.T == self.B and k >= 1
+        if k == 1:
+            return self
+        til = lambda a: np.tile(a, k)
+        offs = lambda a: np.concatenate([[0], np.cumsum(np.tile(np.diff(a), k))]).astype(np.int64)
+        return DagBatch(
+            B=self.B * k, T=self.B * k, n_max=self.n_max, K_max=self.K_max, P_max=self.P_max, E_max=self.E_max,
+            R_max=self.R_max, flags=0, task_off=offs(self.task_off), pred_off=offs(self.pred_off),
+            par_off=offs(self.par_off), pid_off=offs(self.pid_off), pred_ptr=til(self.pred_ptr),
+            pred_idx=til(self.pred_idx), par_ptr=til(self.par_ptr), par_idx=til(self.par_idx), rank=til(self.rank),
+            mem=til(self.mem), dur=til(self.dur), node_off=None if self.node_off is None else offs(self.node_off),
+            cap=self.cap if self.node_off is None else til(self.cap),
+            spd=self.spd if self.node_off is None else til(self.spd), dags=None)
+
     def validate(self):
         if self.K_max > N.MAX_NODES:
             raise ValueError(f"K_max={self.K_max} > {N.MAX_NODES}")

@@ -113,7 +113,7 @@ class BaseScheduler:
         cap = np.asarray([float(x.available_memory) for x in node_list], np.float64)
         _, spd = lower_nodes(node_list)
         batch = DagBatch.from_instances([dag], [(cap, spd)])
-        res = schedule_batch(batch, 1 << self.ALGO).host()
+        res = schedule_batch(batch, 1 << self.ALGO, peak=False, cached=True).host()
         self._lift(batch, res, dag, node_list)
         return schedule_dict(batch, res, 0, 0, dag.names, [x.id for x in node_list])
 

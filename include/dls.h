@@ -194,8 +194,9 @@ int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, 
  * library until the process exits. It never calls cudaMalloc, cudaFree or any other allocating routine; inputs and
  * outputs are still the caller's device buffers, exactly as for dls_schedule_batch, and results are identical.
  *
- * - A batch whose scratch need (dls_workspace_bytes) exceeds DLS_STATIC_SCRATCH_BYTES is refused with
- *   DLS_ERR_TOO_LARGE and a message naming both numbers; nothing is launched. (About 1,300 DAGs of 1,000 tasks.)
+ * - A batch whose smallest workable scratch exceeds DLS_STATIC_SCRATCH_BYTES is refused with DLS_ERR_TOO_LARGE and
+ *   a message naming both numbers; nothing is launched. (About 1,300 DAGs of 1,000 tasks. Within the limit, the
+ *   faster streamed kernels are used when their larger scratch also fits, else the general ones.)
  * - The first call on each device looks up the array's device address (one cudaGetSymbolAddress, made with that
  *   device current). Make that first call outside any stream capture.
  * - There is ONE array per device and every call uses it. It still holds the previous call's contents when the
@@ -205,6 +206,11 @@ int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, 
  */
 #define DLS_STATIC_SCRATCH_BYTES (32u << 20)
 int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* cuda_stream);
+
+/* Test/measurement switch (no reference counterpart). Qualifying batches (K <= 8 nodes, small per-DAG state, no
+ * extension outputs requested) normally run on the thread-per-DAG streamed kernels; 0 forces the general
+ * warp-per-DAG kernels for everything, 1 restores the default. Returns the previous setting. */
+int dls_set_stream_path(int enabled);
 
 /* Number of kernel launches the library has enqueued since load (for bench accounting). */
 int64_t dls_launch_count(void);
@@ -219,7 +225,14 @@ int64_t dls_launch_count(void);
 #define DLS_KERNEL_SCHED_GREEDY 3
 #define DLS_KERNEL_SCHED_CRITICAL 4
 #define DLS_KERNEL_SCHED_MRU 5
-#define DLS_NUM_KERNELS 6
+#define DLS_KERNEL_PARAM_CLASS 6
+#define DLS_KERNEL_STREAM_BUILD 7
+#define DLS_KERNEL_STREAM_DFS 8
+#define DLS_KERNEL_STREAM_GREEDY 9
+#define DLS_KERNEL_STREAM_CRITICAL 10
+#define DLS_KERNEL_STREAM_MRU 11
+#define DLS_KERNEL_UNPERMUTE 12
+#define DLS_NUM_KERNELS 13
 int dls_profile_enable(int on);
 int dls_profile_read(double* ms_per_kernel, int64_t* launches_per_kernel);
 const char* dls_kernel_name(int kernel_id);

@@ -64,3 +64,12 @@ def assert_results_equal(a: ResultArrays, b: ResultArrays, what: str = ""):
         np.testing.assert_array_equal(bits(a.peak), bits(b.peak), err_msg=what + " peak bits")
     if a.cached is not None and b.cached is not None:
         np.testing.assert_array_equal(a.cached, b.cached, err_msg=what + " cached")
+
+
+def run_both_paths(batch, mask):
+    """Yield (label, ResultArrays) for the two device implementations: the general warp-per-DAG kernels (which also
+    produce the peak/cached extensions) and the thread-per-DAG streamed kernels (taken when no extension output is
+    requested and the batch qualifies; otherwise the library falls back to the general ones by itself)."""
+    from dls_b200.batch import schedule_batch
+    yield "general", schedule_batch(batch, mask, peak=True, cached=True).host()
+    yield "streamed", schedule_batch(batch, mask, peak=False, cached=False).host()

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import golden_io
-from common import assert_matches_expected, assert_results_equal
+from common import assert_matches_expected, assert_results_equal, run_both_paths
 from dls_b200 import _native as N
 from dls_b200.batch import priorities, schedule_batch
 from dls_b200.gen import perturbed_durations, random_dag_batch
@@ -22,19 +22,19 @@ def test_cuda_reproduces_reference_fixtures(fname):
     for mask in sorted({c.mask for c in cases}):
         sub = [c for c in cases if c.mask == mask]
         batch = golden_io.batch_of(sub)
-        res = schedule_batch(batch, mask).host()
-        for b, c in enumerate(sub):
-            for slot, a in enumerate(res.algos):
-                assert_matches_expected(c.exp[a], batch, res, slot, b, f"{fname}:{c.label} algo={a}")
+        for path, res in run_both_paths(batch, mask):
+            for b, c in enumerate(sub):
+                for slot, a in enumerate(res.algos):
+                    assert_matches_expected(c.exp[a], batch, res, slot, b, f"{path} {fname}:{c.label} algo={a}")
 
 
 @pytest.mark.parametrize("n,K,regime,B", [(1000, 8, 0.9, 96), (1000, 8, 0.8, 48), (1000, 4, 1.0, 48), (1000, 2, 0.9, 32),
                                           (257, 8, 0.6, 64), (64, 8, 0.45, 128), (33, 4, 0.7, 128), (1, 2, 1.0, 8)])
 def test_cuda_matches_oracle_random_dags(oracle_mod, n, K, regime, B):
     batch = random_dag_batch(B, n, K, regime, seed=n * 131 + K)
-    got = schedule_batch(batch, N.MASK_ALL).host()
     want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
-    assert_results_equal(got, want, f"random n={n} K={K} r={regime}")
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} random n={n} K={K} r={regime}")
 
 
 def test_single_algorithm_masks_and_slots(oracle_mod):
@@ -65,15 +65,15 @@ def test_shared_topology_perturbed_durations(oracle_mod):
     B = 512
     dur = perturbed_durations(base.dag, B, 0.1, seed=0)
     batch = DagBatch.shared_topology(base.dag, base.cap, base.spd, B, dur=dur)
-    got = schedule_batch(batch, N.MASK_ALL).host()
     want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
-    assert_results_equal(got, want, "gpt2 shared topology")
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} gpt2 shared topology")
     # instance 0 with unperturbed durations reproduces the fixture
     plain = DagBatch.shared_topology(base.dag, base.cap, base.spd, 3)
-    res = schedule_batch(plain, N.MASK_ALL).host()
-    for b in range(3):
-        for slot, a in enumerate(res.algos):
-            assert_matches_expected(base.exp[a], plain, res, slot, b, f"gpt2 shared b={b} algo={a}")
+    for path, res in run_both_paths(plain, N.MASK_ALL):
+        for b in range(3):
+            for slot, a in enumerate(res.algos):
+                assert_matches_expected(base.exp[a], plain, res, slot, b, f"{path} gpt2 shared b={b} algo={a}")
     # DFS/Greedy/MRU decisions do not depend on durations (SURVEY.md 8a'): only makespan moves
     for slot in (0, 1, 3):
         n = base.n
@@ -113,6 +113,40 @@ def test_size_independent_properties_full_size():
             child = np.repeat(np.arange(n), np.diff(pp))
             ok = node_of[child] >= 0
             assert (node_of[pi][ok] >= 0).all() and (seq[pi][ok] < seq[child][ok]).all()
+
+
+def test_streamed_path_is_taken_and_falls_back():
+    """The thread-per-DAG kernels really run for qualifying batches (their launches are counted), instances they
+    cannot take (shared params under MRU: pipeline DAGs) are routed to the general kernels, and forcing the general
+    path gives identical results."""
+    import ctypes as C
+    lib = N.load()
+    lib.dls_profile_enable(1)
+    ms = (C.c_double * N.NUM_KERNELS)()
+    cnt = (C.c_int64 * N.NUM_KERNELS)()
+    lib.dls_profile_read(ms, cnt)
+    for i in range(N.NUM_KERNELS):
+        cnt[i] = 0
+    batch = random_dag_batch(64, 100, 8, 0.7, seed=77)
+    fast = schedule_batch(batch, N.MASK_ALL).host()
+    lib.dls_profile_read(ms, cnt)
+    lib.dls_profile_enable(0)
+    names = {lib.dls_kernel_name(k).decode(): int(cnt[k]) for k in range(N.NUM_KERNELS)}
+    assert names["sched_stream_kernel<DFS>"] == 1 and names["sched_stream_mru_kernel"] == 1 and names["unpermute_kernel"] == 4
+    old = lib.dls_set_stream_path(0)
+    try:
+        slow = schedule_batch(batch, N.MASK_ALL).host()
+    finally:
+        lib.dls_set_stream_path(old)
+    assert_results_equal(fast, slow, "streamed vs forced general")
+    # mixed batch: random DAGs (all private params) + pipeline DAGs (shared params)
+    cases = golden_io.load("cfg2_sweep_seed0.npz")
+    mixed = [c for c in cases if c.label.startswith(("Pipeline", "Random-Small"))][:40]
+    mb = golden_io.batch_of(mixed)
+    res = schedule_batch(mb, N.MASK_ALL).host()
+    for b, c in enumerate(mixed):
+        for slot, a in enumerate(res.algos):
+            assert_matches_expected(c.exp[a], mb, res, slot, b, f"mixed {c.label} algo={a}")
 
 
 def test_error_codes():
