@@ -135,8 +135,8 @@ int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
   if (need_device) {
     const int lim = smem_limit();
     if (lim < 0) return fail(DLS_ERR_CUDA, std::string("no usable CUDA device: ") + cudaGetErrorString(cudaGetLastError()));
-    size_t need = dls::priority_smem_topo(b->n_max);
-    if (algo_mask & (1 << DLS_ALGO_CRITICAL)) need = std::max(need, dls::priority_smem_inst(b->n_max));
+    size_t need = dls::priority_smem_topo(b->n_max, -1);
+    if (algo_mask & (1 << DLS_ALGO_CRITICAL)) need = std::max(need, dls::priority_smem_inst(b->n_max, false));
     if (algo_mask & 7) need = std::max(need, dls::sched_smem_simple(b->n_max, b->P_max));
     if (algo_mask & (1 << DLS_ALGO_MRU)) need = std::max(need, dls::sched_smem_mru(b->n_max, b->P_max, b->K_max));
     if (need > (size_t)lim) {

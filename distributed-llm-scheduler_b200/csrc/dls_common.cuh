@@ -239,8 +239,8 @@ cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, con
                                 LaunchCtx& ctx);
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit);
 size_t priority_smem_param(int n_max, int P_max);
-size_t priority_smem_topo(int n_max);
-size_t priority_smem_inst(int n_max);
+size_t priority_smem_topo(int n_max, int E_max);
+size_t priority_smem_inst(int n_max, bool with_key);
 size_t sched_smem_simple(int n_max, int P_max);
 size_t sched_smem_mru(int n_max, int P_max, int K_max);
 

@@ -57,7 +57,7 @@ __device__ void stable_counting_sort(const uint16_t* src, uint16_t* dst, int n, 
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru) {
+__global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru, int stage) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_part[33];
   __shared__ int s_maxd, s_maxdeg;
@@ -71,6 +71,11 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   uint16_t* s_depth = reinterpret_cast<uint16_t*>(s_hist + (n + 2));  // [n_al]
   uint16_t* s_ord = s_depth + n_al;                                     // [n_al]
   uint16_t* s_tmp = s_ord + n_al;                                       // [n_al]
+  // with `stage`: dependency CSR copied to shared memory (it is walked once per relaxation sweep)
+  uint32_t* s_pptr = reinterpret_cast<uint32_t*>(s_tmp + n_al);         // [n+1]
+  uint16_t* s_pidx = reinterpret_cast<uint16_t*>(s_pptr + (n + 1));     // [E]
+  const uint32_t* pptr = stage ? s_pptr : v.pred_ptr;
+  const uint16_t* pidx = stage ? s_pidx : v.pred_idx;
 
   uint16_t* g_depth = w.depth + v.t_topo;
   uint16_t* g_outdeg = w.outdeg + v.t_topo;
@@ -82,6 +87,10 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   // ---- validate the descriptor slice (never trust indices that address shared memory) ----
   {
     int bad = 0;
+    if (n > b.n_max || v.P > b.P_max || v.E > (uint32_t)b.E_max || v.R > (uint32_t)b.R_max) {
+      if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;  // descriptor maxima are what shared memory was sized for
+      return;
+    }
     if (n > 0 && (v.pred_ptr[0] != 0 || v.par_ptr[0] != 0 || v.pred_ptr[n] != v.E || v.par_ptr[n] != v.R)) bad = 1;
     for (int i = tid; i < n; i += blockDim.x) {
       if (v.pred_ptr[i] > v.pred_ptr[i + 1] || v.par_ptr[i] > v.par_ptr[i + 1]) bad = 1;
@@ -97,14 +106,19 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     }
   }
   // ---- depth: relax until a fixed point (<= levels+1 sweeps; more than n+1 sweeps means a cycle) ----
+  // The dependency CSR is staged in shared memory once: every sweep walks it again.
   for (int i = tid; i < n; i += blockDim.x) s_depth[i] = 0;
+  if (stage) {
+    for (int i = tid; i <= n; i += blockDim.x) s_pptr[i] = v.pred_ptr[i];
+    for (uint32_t e = tid; e < v.E; e += blockDim.x) s_pidx[e] = v.pred_idx[e];
+  }
   __syncthreads();
   int sweeps = 0, changed;
   do {
     changed = 0;
     for (int i = tid; i < n; i += blockDim.x) {
       int d = 0;
-      for (uint32_t e = v.pred_ptr[i]; e < v.pred_ptr[i + 1]; ++e) d = max(d, (int)s_depth[v.pred_idx[e]] + 1);
+      for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) d = max(d, (int)s_depth[pidx[e]] + 1);
       d = min(d, 65535);
       if (d != s_depth[i]) {
         s_depth[i] = (uint16_t)d;
@@ -130,7 +144,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   // ---- out-degree and reverse CSR (task_dependencies, ref schedulers.py:47-48) ----
   for (int i = tid; i < n + 2; i += blockDim.x) s_cnt[i] = 0;
   __syncthreads();
-  for (uint32_t e = tid; e < v.E; e += blockDim.x) atomicAdd(&s_cnt[v.pred_idx[e]], 1u);
+  for (uint32_t e = tid; e < v.E; e += blockDim.x) atomicAdd(&s_cnt[pidx[e]], 1u);
   __syncthreads();
   {
     int mdg = 0;
@@ -145,8 +159,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   for (int i = tid; i <= n; i += blockDim.x) g_succ_ptr[i] = s_cnt[i];
   __syncthreads();
   for (int i = tid; i < n; i += blockDim.x)
-    for (uint32_t e = v.pred_ptr[i]; e < v.pred_ptr[i + 1]; ++e) {
-      uint32_t pos = atomicAdd(&s_cnt[v.pred_idx[e]], 1u);  // order inside a list is irrelevant to max() and counts
+    for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) {
+      uint32_t pos = atomicAdd(&s_cnt[pidx[e]], 1u);  // order inside a list is irrelevant to max() and counts
       g_succ_idx[pos] = (uint16_t)i;
     }
   // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
@@ -220,7 +234,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   for (int q = tid; q < P; q += blockDim.x) g_erank[s_dst[q]] = (uint16_t)q;
 }
 
-__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w) {
+__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
   const int inst = blockIdx.x, tid = threadIdx.x;
@@ -231,7 +245,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   if (n == 0) return;
   const int n_al = (n + 3) & ~3;
   double* s_up = reinterpret_cast<double*>(smem_raw);             // [n]
-  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(s_up + n);        // [n+2] first position of each level
+  double* s_key = s_up + n;                                        // [n]   up[] in DFS/Greedy order (only with use_key)
+  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(s_up + (use_key ? 2 * n : n));  // [n+2] first position of each level
   uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
   uint16_t* s_depth = s_ord + n_al;                               // [n_al]
   const uint16_t* g_depth = w.depth + v.t_topo;
@@ -271,17 +286,25 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     }
     __syncthreads();
   }
-  for (int i = tid; i < n; i += blockDim.x) w.up[cp_off + i] = s_up[i];
-  // within-level stable sort by up desc: ready_tasks.sort(key=critical_path, reverse=True), ref schedulers.py:343
+  for (int i = tid; i < n; i += blockDim.x) {
+    w.up[cp_off + i] = s_up[i];
+    if (use_key) s_key[i] = s_up[s_ord[i]];  // keys in pi order inside each level: the loops below read them sequentially
+  }
+  __syncthreads();
+  // within-level stable sort by up desc: ready_tasks.sort(key=critical_path, reverse=True), ref schedulers.py:343.
+  // Position of q = #{q2 in level: key[q2] > key[q]} + #{q2 < q in level: key[q2] == key[q]}.
   for (int q = tid; q < n; q += blockDim.x) {
     const int i = s_ord[q];
     const int d = s_depth[i];
     const int ls = s_lvl[d], le = s_lvl[d + 1];
     const double u = s_up[i];
     int ahead = 0;
-    for (int q2 = ls; q2 < le; ++q2) {
-      const double u2 = s_up[s_ord[q2]];
-      ahead += (u2 > u) || (u2 == u && q2 < q);
+    if (use_key) {
+      for (int q2 = ls; q2 < q; ++q2) ahead += s_key[q2] >= u;
+      for (int q2 = q + 1; q2 < le; ++q2) ahead += s_key[q2] > u;
+    } else {  // very large DAGs: no room for the second key array
+      for (int q2 = ls; q2 < q; ++q2) ahead += s_up[s_ord[q2]] >= u;
+      for (int q2 = q + 1; q2 < le; ++q2) ahead += s_up[s_ord[q2]] > u;
     }
     w.order_cp[cp_off + ls + ahead] = (uint16_t)i;
   }
@@ -289,9 +312,11 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
 
 }  // namespace
 
-size_t priority_smem_topo(int n_max) {
+size_t priority_smem_topo(int n_max, int E_max) {  // E_max < 0: without the staged dependency CSR
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
-  return 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
+  size_t base = 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
+  if (E_max < 0) return base;
+  return base + (n + 1) * sizeof(uint32_t) + (((size_t)E_max + 1) & ~(size_t)1) * sizeof(uint16_t);
 }
 
 size_t priority_smem_param(int n_max, int P_max) {
@@ -299,19 +324,21 @@ size_t priority_smem_param(int n_max, int P_max) {
   return (P + 2 + n + 2) * sizeof(uint32_t) + 3 * P_al * sizeof(uint16_t);
 }
 
-size_t priority_smem_inst(int n_max) {
+size_t priority_smem_inst(int n_max, bool with_key) {
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
-  return n * sizeof(double) + (n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
+  return (with_key ? 2 : 1) * n * sizeof(double) + (n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
 }
 
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
   cudaError_t e;
-  size_t sm1 = priority_smem_topo(b.n_max);
+  size_t sm1 = priority_smem_topo(b.n_max, b.E_max);
+  const int stage = sm1 <= 64 * 1024;  // staging pays while several CTAs still fit an SM
+  if (!stage) sm1 = priority_smem_topo(b.n_max, -1);
   ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
   e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   if (e != cudaSuccess) return e;
   int rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
-  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1);
+  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage);
   if (ctx.prof) ctx.prof->end(rec, ctx.st);
   ++ctx.launches;
   ctx.why = "priority_topology_kernel launch";
@@ -331,13 +358,15 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     if (e != cudaSuccess) return e;
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
-    size_t sm2 = priority_smem_inst(b.n_max);
+    size_t sm2 = priority_smem_inst(b.n_max, true);
+    const int use_key = sm2 <= 96 * 1024;
+    if (!use_key) sm2 = priority_smem_inst(b.n_max, false);
     ctx.why = "cudaFuncSetAttribute(priority_critical_kernel)";
     e = cudaFuncSetAttribute(priority_critical_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     int grid = w.cp_per_instance ? b.B : 1;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;
-    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w);
+    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w, use_key);
     if (ctx.prof) ctx.prof->end(rec, ctx.st);
     ++ctx.launches;
     ctx.why = "priority_critical_kernel launch";

@@ -117,6 +117,142 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
 }
 
 // -------------------------------------------------------------------------------------------------------------------
+// stream_build_staged_kernel: grid B. One CTA per instance builds all requested streams.
+// Phase 1 reads the instance's arrays ONCE, in task order (fully coalesced), into task-indexed 32-byte records in
+// shared memory. Phase 2, per processing order, permutes them through shared memory and writes the stream
+// coalesced. Used when the staged records fit shared memory (n up to ~5.5k); otherwise stream_build_kernel.
+// -------------------------------------------------------------------------------------------------------------------
+struct __align__(16) TaskRec {   // like Rec, but dependencies/params still as task / param ids, plus the depth
+  double m, c;
+  uint16_t pred[3];
+  uint16_t npred;
+  uint16_t p0, p1;   // first two param ids
+  uint16_t npar;
+  uint16_t depth;
+};
+static_assert(sizeof(TaskRec) == 32, "TaskRec is 32 bytes");
+
+__global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_batch_t b, Workspace w, int kind_mask) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ uint32_t s_part[33];
+  __shared__ int s_any_ext;
+  const int inst = blockIdx.x, tid = threadIdx.x;
+  Inst v;
+  bind_instance(b, inst, v);
+  if (w.topo_status[v.topo] != DLS_ST_OK) return;
+  const int n = v.n;
+  if (n == 0) return;
+  const int nsh_topo = w.nshared[v.topo];
+  TaskRec* s_task = reinterpret_cast<TaskRec*>(smem_raw);                    // [n]
+  uint32_t* s_extoff = reinterpret_cast<uint32_t*>(s_task + n);              // [n+1]
+  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));         // [n]
+  const uint16_t* depth = w.depth + v.t_topo;
+  const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
+  const uint16_t* erank = w.erank + b.pid_off[v.topo];
+  if (tid == 0) s_any_ext = 0;
+  __syncthreads();
+  // ---- phase 1: task-order gather ----
+  int any_ext = 0;
+  for (int i = tid; i < n; i += blockDim.x) {
+    TaskRec tr;
+    tr.m = v.mem[i];
+    tr.c = v.dur[i];
+    const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
+    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+    tr.npred = (uint16_t)min(pe - pb, 65535u);
+    tr.npar = (uint16_t)min(qe - qb, 65535u);
+    tr.pred[0] = pe - pb > 0 ? v.pred_idx[pb] : 0;
+    tr.pred[1] = pe - pb > 1 ? v.pred_idx[pb + 1] : 0;
+    tr.pred[2] = pe - pb > 2 ? v.pred_idx[pb + 2] : 0;
+    tr.p0 = qe - qb > 0 ? v.par_idx[qb] : 0;
+    tr.p1 = qe - qb > 1 ? v.par_idx[qb + 1] : 0;
+    tr.depth = depth[i];
+    s_task[i] = tr;
+    any_ext |= (pe - pb > 3) || (qe - qb > 2);
+  }
+  if (any_ext) s_any_ext = 1;
+  __syncthreads();
+  const bool ext_needed = s_any_ext != 0;
+  // ---- phase 2: one pass per processing order ----
+  for (int kind = 0; kind < 3; ++kind) {
+    if (!((kind_mask >> kind) & 1)) continue;
+    if (kind == kStreamMRU ? nsh_topo != 0 : nsh_topo > kSharedCap) continue;  // routed to the general kernels
+    const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
+                          : kind == kStreamMRU ? w.order_mru + v.t_topo
+                                               : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
+    Rec* out = w.stream[kind] + v.t_inst;
+    uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
+    __syncthreads();  // previous pass is done with s_pos / s_extoff
+    for (int t = tid; t < n; t += blockDim.x) s_pos[order[t]] = (uint16_t)t;
+    if (ext_needed) {
+      for (int t = tid; t < n; t += blockDim.x) {
+        const int i = order[t];
+        const TaskRec& tr = s_task[i];
+        int extra = max(0, (int)tr.npred - 3);
+        if (kind == kStreamMRU) {
+          extra += max(0, (int)tr.npar - 2);
+        } else if (nsh_topo > 0) {
+          int nsh = 0;
+          for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
+          extra += max(0, nsh - 2);
+        }
+        s_extoff[t] = (uint32_t)extra;
+      }
+      if (tid == 0) s_extoff[n] = 0;
+      __syncthreads();
+      block_exclusive_scan(s_extoff, n + 1, s_part);
+    } else {
+      __syncthreads();
+    }
+    for (int t = tid; t < n; t += blockDim.x) {
+      const int i = order[t];
+      const TaskRec tr = s_task[i];
+      Rec rc;
+      rc.m = tr.m;
+      rc.c = tr.c;
+      rc.npred = tr.npred;
+      rc.pred[0] = s_pos[tr.pred[0]];
+      rc.pred[1] = s_pos[tr.pred[1]];
+      rc.pred[2] = s_pos[tr.pred[2]];
+      uint32_t xo = ext_needed ? s_extoff[t] : 0;
+      if (tr.npred > 3) {
+        const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
+        for (uint32_t e = pb + 3; e < pe; ++e) ext[xo++] = s_pos[v.pred_idx[e]];
+      }
+      rc.a0 = rc.a1 = 0;
+      if (kind == kStreamMRU) {
+        rc.npriv = tr.npar;
+        rc.nsh = 0;
+        if (tr.npar > 0) rc.a0 = erank[tr.p0];
+        if (tr.npar > 1) rc.a1 = erank[tr.p1];
+        if (tr.npar > 2) {
+          const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+          for (uint32_t e = qb + 2; e < qe; ++e) ext[xo++] = erank[v.par_idx[e]];
+        }
+      } else if (nsh_topo == 0) {
+        rc.npriv = tr.npar;
+        rc.nsh = 0;
+      } else {
+        int nsh = 0, npriv = 0;
+        const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+        for (uint32_t e = qb; e < qe; ++e) {
+          const uint16_t sd = sid[v.par_idx[e]];
+          if (sd == 0xFFFF) { ++npriv; continue; }
+          if (nsh == 0) rc.a0 = sd;
+          else if (nsh == 1) rc.a1 = sd;
+          else ext[xo++] = sd;
+          ++nsh;
+        }
+        rc.npriv = (uint16_t)npriv;
+        rc.nsh = (uint8_t)min(nsh, 255);
+      }
+      rc.flags = (t == 0 || s_task[order[t - 1]].depth != tr.depth) ? kRecFirst : 0;
+      out[t] = rc;
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------------
 // Shared pieces of the thread-per-DAG kernels
 // -------------------------------------------------------------------------------------------------------------------
 struct RecRegs {
@@ -220,16 +356,32 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
   const uint16_t* ext = w.ext[kind] + (elig ? ext_offset(b, inst, v) : 0);
   int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
 
-  double avail[KMAX], spd[ALGO == DLS_ALGO_CRITICAL ? KMAX : 1];
+  // Node state. avail[k] of a node that does not exist is -inf: it never fits and never wins a max.
+  double avail[KMAX];
+  // Critical: nodes ranked by (speed desc, index asc) once; key = rank*KMAX + k, nodes with speed <= 0 never chosen
+  // ("node.compute_speed > best_speed" with best_speed = 0, ref schedulers.py:353-358).
+  int ckey[ALGO == DLS_ALGO_CRITICAL ? KMAX : 1];
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) {
     const bool on = elig && k < K;
-    avail[k] = on ? v.cap[k] : 0.0;
-    const double s = on ? v.spd[k] : 1.0;
-    if constexpr (ALGO == DLS_ALGO_CRITICAL) spd[k] = s;
+    avail[k] = on ? v.cap[k] : -INFINITY;
+    const double sp = on ? v.spd[k] : 1.0;
     sl.f(FIN + k) = 0.0;
-    sl.f(SPD + k) = s;
+    sl.f(SPD + k) = sp;
     sl.w(CNT + k) = 0;
+  }
+  if constexpr (ALGO == DLS_ALGO_CRITICAL) {
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      const double sk = sl.f(SPD + k);
+      int rank = 0;
+#pragma unroll
+      for (int j = 0; j < KMAX; ++j) {
+        const double sj = sl.f(SPD + j);
+        rank += (j < K) && (sj > sk || (sj == sk && j < k));
+      }
+      ckey[k] = (k < K && sk > 0.0) ? rank * KMAX + k : 0x7fffffff;
+    }
   }
   for (int x = 0; x < nw_done + kSharedCap / 4; ++x) sl.w(x) = 0;
 
@@ -264,51 +416,73 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       const uint32_t x_pred = xpos, x_sh = xpos + (uint32_t)max(0, npred - 3);
       xpos = x_sh + (uint32_t)max(0, nsh - 2);
       if (running) {
-        auto done_bit = [&](int p) -> bool {
-          const uint32_t wd = ((p >> 5) == (t >> 5)) ? curw : sl.w(DONE + (p >> 5));
-          return (wd >> (p & 31)) & 1u;
-        };
-        bool ready = true;
-        if (npred > 0) ready = done_bit(cur.hi.x & 0xffff);
-        if (npred > 1) ready = ready && done_bit(cur.hi.x >> 16);
-        if (npred > 2) ready = ready && done_bit(cur.hi.y & 0xffff);
+        // is_task_ready (ref :50-53). The done word of the current 32-group is written through on every assignment,
+        // so shared memory is always current; unused dependency slots hold position 0 and are masked by the count.
+        auto done_bit = [&](uint32_t p) -> uint32_t { return (sl.w(DONE + (p >> 5)) >> (p & 31)) & 1u; };
+        const uint32_t b0 = done_bit(cur.hi.x & 0xffff) | (npred < 1);
+        const uint32_t b1 = done_bit(cur.hi.x >> 16) | (npred < 2);
+        const uint32_t b2 = done_bit(cur.hi.y & 0xffff) | (npred < 3);
+        bool ready = (b0 & b1 & b2) != 0;
         for (int j = 3; j < npred; ++j) ready = ready && done_bit(ext[x_pred + j - 3]);
         if (ready) {
           any_ready = true;
-          // shared params not yet cached, per node, packed one byte per node
-          unsigned long long miss = 0;
-          for (int j = 0; j < nsh; ++j) {
-            const int s = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
-            const uint32_t mask = (sl.w(SMASK + (s >> 2)) >> ((s & 3) * 8)) & 0xffu;
-            const unsigned long long spread = ((unsigned long long)(mask ^ 0xffu) * 0x0101010101010101ull) & 0x8040201008040201ull;
-            miss += ((spread + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
-          }
-          const double need0 = memory_requirement(m, npriv);
-          int best = -1, lbest = 0;
-          double bv = ALGO == DLS_ALGO_DFS ? -1.0 : 0.0;  // max_memory = -1 (ref :187) / best_speed = 0 (ref :353)
-          int bl = 0x7fffffff;                             // min_params_to_load = inf (ref :268)
+          int best = -1, lbest = npriv;
+          double a = 0.0;  // available memory of the chosen node
+          if (nsh == 0) {
+            // Every param of the task is private: params_to_load and hence the requirement are the same on every
+            // node, so "fits" is avail >= need and the best fitting node is the first maximum, if that one fits.
+            const double need = memory_requirement(m, npriv);
+            if constexpr (ALGO == DLS_ALGO_CRITICAL) {
+              int bk = 0x7fffffff;
 #pragma unroll
-          for (int k = 0; k < KMAX; ++k) {
-            const int lk = npriv + (int)((miss >> (8 * k)) & 0xffull);
-            const double need = nsh ? memory_requirement(m, lk) : need0;
-            const bool fits = k < K && need <= avail[k];  // can_fit_on_node (ref :74-76)
-            bool take;
-            double key = avail[k];
-            if constexpr (ALGO == DLS_ALGO_DFS) take = fits && avail[k] > bv;                         // ref :190
-            else if constexpr (ALGO == DLS_ALGO_GREEDY) take = fits && (lk < bl || (lk == bl && avail[k] > bv));  // ref :276-278
-            else { key = spd[k]; take = fits && key > bv; }                                           // ref :356
-            if (take) {
-              best = k;
-              lbest = lk;
-              bl = lk;
-              bv = key;
+              for (int k = 0; k < KMAX; ++k) bk = min(bk, need <= avail[k] ? ckey[k] : 0x7fffffff);
+              if (bk != 0x7fffffff) { best = bk & (KMAX - 1); a = pick<KMAX>(avail, best); }
+            } else {
+              // DFS: strict '>' from max_memory = -1 (ref :186-192). Greedy: first fitting node, then strictly more
+              // available memory among equal params_to_load (ref :267-281) == first maximum among fitting nodes.
+              double bv = ALGO == DLS_ALGO_DFS ? -1.0 : -INFINITY;
+#pragma unroll
+              for (int k = 0; k < KMAX; ++k)
+                if (avail[k] > bv) { bv = avail[k]; best = k; }
+              if (!(need <= bv)) best = -1;
+              a = bv;
             }
+          } else {
+            // shared params not yet cached, per node, packed one byte per node
+            unsigned long long miss = 0;
+            for (int j = 0; j < nsh; ++j) {
+              const int sd = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
+              const uint32_t mask = (sl.w(SMASK + (sd >> 2)) >> ((sd & 3) * 8)) & 0xffu;
+              const unsigned long long spread = ((unsigned long long)(mask ^ 0xffu) * 0x0101010101010101ull) & 0x8040201008040201ull;
+              miss += ((spread + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
+            }
+            double bv = ALGO == DLS_ALGO_DFS ? -1.0 : 0.0;  // max_memory = -1 (ref :187) / best_available_memory = 0 (ref :269)
+            int bl = 0x7fffffff, bk = 0x7fffffff;             // min_params_to_load = inf (ref :268)
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) {
+              const int lk = npriv + (int)((miss >> (8 * k)) & 0xffull);
+              const bool fits = memory_requirement(m, lk) <= avail[k];  // can_fit_on_node (ref :74-76)
+              bool take;
+              if constexpr (ALGO == DLS_ALGO_DFS) take = fits && avail[k] > bv;                                     // ref :190
+              else if constexpr (ALGO == DLS_ALGO_GREEDY) take = fits && (lk < bl || (lk == bl && avail[k] > bv));  // ref :276-278
+              else take = fits && ckey[k] < bk;                                                                     // ref :356
+              if (take) {
+                best = k;
+                lbest = lk;
+                bl = lk;
+                bv = avail[k];
+                if constexpr (ALGO == DLS_ALGO_CRITICAL) bk = ckey[k];
+              }
+            }
+            a = bv;
+            if constexpr (ALGO == DLS_ALGO_CRITICAL) { if (best >= 0) a = pick<KMAX>(avail, best); }
           }
           if (best >= 0) {
-            double a = pick<KMAX>(avail, best);
-            for (int j = 0; j < lbest; ++j) a = __dsub_rn(a, 0.5);  // node.available_memory -= 0.5 per loaded param (ref :89)
-            a = __dsub_rn(a, m);                                     // ref :95
-            a = __dadd_rn(a, m);                                     // complete_task frees it again (ref :126)
+            if (lbest > 0) a = __dsub_rn(a, 0.5);  // node.available_memory -= 0.5 per loaded param (ref :89)
+            if (lbest > 1) a = __dsub_rn(a, 0.5);
+            for (int j = 2; j < lbest; ++j) a = __dsub_rn(a, 0.5);
+            a = __dsub_rn(a, m);                   // ref :95
+            a = __dadd_rn(a, m);                   // complete_task frees it again (ref :126)
 #pragma unroll
             for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
             sl.f(FIN + best) = __dadd_rn(sl.f(FIN + best), __ddiv_rn(c, sl.f(SPD + best)));  // ref simulation.py:261-264
@@ -316,8 +490,8 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
             to.misses += lbest;
             to.hits += npriv + nsh - lbest;
             for (int j = 0; j < nsh; ++j) {
-              const int s = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
-              sl.w(SMASK + (s >> 2)) |= (1u << best) << ((s & 3) * 8);
+              const int sd = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
+              sl.w(SMASK + (sd >> 2)) |= (1u << best) << ((sd & 3) * 8);
             }
             curw |= 1u << (t & 31);
             sl.w(DONE + (t >> 5)) = curw;
@@ -367,7 +541,7 @@ __device__ bool evict_private(const Slab& sl, int PN, int nslots, int k, double 
   double freed = 0.0;
   int nev = 0;
   uint32_t pos = cursor;       // first slot not yet examined
-  uint32_t first_hit = 0xffffffffu;
+  uint32_t hit[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};  // first evicted slots (commit without rescanning)
   const uint32_t nwords = (uint32_t)(nslots + 7) >> 3;
   bool ok = false;
   uint32_t wd = pos >> 3;
@@ -379,32 +553,40 @@ __device__ bool evict_private(const Slab& sl, int PN, int nslots, int k, double 
     const uint32_t bit = __ffs(hits) - 1;
     hits &= hits - 1;
     const uint32_t slot = (wd << 3) + (bit >> 2);
-    if (first_hit == 0xffffffffu) first_hit = slot;
+    if (nev == 0) hit[0] = slot;
+    else if (nev == 1) hit[1] = slot;
+    else if (nev == 2) hit[2] = slot;
+    else if (nev == 3) hit[3] = slot;
     pos = slot + 1;
     avail_k = __dadd_rn(avail_k, 0.5);  // ref :429
     freed = __dadd_rn(freed, 0.5);      // ref :431
     ++nev;
   }
   if (ok) {
-    // commit: clear the nev lowest slots of node k starting at first_hit (they are exactly the ones counted above)
-    uint32_t w2 = first_hit >> 3;
-    int left = nev;
-    uint32_t h2 = nibble_eq_mask(sl.w(PN + w2), (uint32_t)k) & (0xffffffffu << ((first_hit & 7) * 4));
-    while (left > 0) {
-      while (h2 == 0) h2 = nibble_eq_mask(sl.w(PN + (++w2)), (uint32_t)k);
-      uint32_t word = sl.w(PN + w2);
-      while (h2 && left > 0) {
-        const uint32_t bit = __ffs(h2) - 1;
-        h2 &= h2 - 1;
-        word |= 0xFu << (bit - 3);
-        --left;
+    // commit: node.cached_params.remove(param) for the nev lowest slots of node k
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (q < nev) sl.w(PN + (hit[q] >> 3)) |= 0xFu << ((hit[q] & 7) * 4);
+    if (nev > 4) {  // rare: more than four params evicted at once; walk on from the fourth
+      uint32_t w2 = (hit[3] + 1) >> 3;
+      int left = nev - 4;
+      uint32_t h2 = nibble_eq_mask(sl.w(PN + w2), (uint32_t)k) & (0xffffffffu << (((hit[3] + 1) & 7) * 4));
+      while (left > 0) {
+        while (h2 == 0) h2 = nibble_eq_mask(sl.w(PN + (++w2)), (uint32_t)k);
+        uint32_t word = sl.w(PN + w2);
+        while (h2 && left > 0) {
+          const uint32_t bit = __ffs(h2) - 1;
+          h2 &= h2 - 1;
+          word |= 0xFu << (bit - 3);
+          --left;
+        }
+        sl.w(PN + w2) = word;
       }
-      sl.w(PN + w2) = word;
     }
     cursor = pos;
   } else {
-    for (int j = 0; j < nev; ++j) avail_k = __dsub_rn(avail_k, 0.5);  // rollback (ref :438-441); nothing was cleared
-    cursor = first_hit == 0xffffffffu ? (uint32_t)nslots : first_hit;
+    for (int q = 0; q < nev; ++q) avail_k = __dsub_rn(avail_k, 0.5);  // rollback (ref :438-441); nothing was cleared
+    cursor = hit[0] == 0xffffffffu ? (uint32_t)nslots : hit[0];
   }
   return ok;
 }
@@ -414,15 +596,16 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
                                                                 int nw_done, int nw_pn) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab per warp: doubles fin[KMAX], spd[KMAX]; words done[nw_done], pnode[nw_pn], cnt[KMAX], curs[KMAX]
-  constexpr int kD = 2 * KMAX;
+  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX]; words done[nw_done], pnode[nw_pn], cnt[KMAX], curs[KMAX]
+  constexpr int kD = 3 * KMAX;
   const int kW = nw_done + nw_pn + 2 * KMAX;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
   sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
-  const int FIN = 0, SPD = KMAX, DONE = 0, PN = nw_done, CNT = nw_done + nw_pn, CURS = CNT + KMAX;
+  // HCNT[k] = len(node.completed_tasks) * 0.5 kept as a double: every += 0.5 is exact (ref schedulers.py:498)
+  const int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, DONE = 0, PN = nw_done, CNT = nw_done + nw_pn, CURS = CNT + KMAX;
 
   const int inst = blockIdx.x * kTPB + threadIdx.x;
   const bool have = inst < b.B;
@@ -441,13 +624,14 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
   const uint16_t* ext = w.ext[kStreamMRU] + (elig ? ext_offset(b, inst, v) : 0);
   int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
 
-  double avail[KMAX];
+  double avail[KMAX];  // -inf for nodes that do not exist: they never fit
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) {
     const bool on = elig && k < K;
-    avail[k] = on ? v.cap[k] : 0.0;
+    avail[k] = on ? v.cap[k] : -INFINITY;
     sl.f(FIN + k) = 0.0;
     sl.f(SPD + k) = on ? v.spd[k] : 1.0;
+    sl.f(HCNT + k) = 0.0;
     sl.w(CNT + k) = 0;
     sl.w(CURS + k) = (uint32_t)nslots;  // nothing cached yet
   }
@@ -485,38 +669,49 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
       const uint32_t x_pred = xpos, x_par = xpos + (uint32_t)max(0, npred - 3);
       xpos = x_par + (uint32_t)max(0, npar - 2);
       if (running) {
-        auto done_bit = [&](int p) -> bool {
-          const uint32_t wd = ((p >> 5) == (t >> 5)) ? curw : sl.w(DONE + (p >> 5));
-          return (wd >> (p & 31)) & 1u;
-        };
-        bool ready = true;
-        if (npred > 0) ready = done_bit(cur.hi.x & 0xffff);
-        if (npred > 1) ready = ready && done_bit(cur.hi.x >> 16);
-        if (npred > 2) ready = ready && done_bit(cur.hi.y & 0xffff);
+        auto done_bit = [&](uint32_t p) -> uint32_t { return (sl.w(DONE + (p >> 5)) >> (p & 31)) & 1u; };
+        const uint32_t b0 = done_bit(cur.hi.x & 0xffff) | (npred < 1);
+        const uint32_t b1 = done_bit(cur.hi.x >> 16) | (npred < 2);
+        const uint32_t b2 = done_bit(cur.hi.y & 0xffff) | (npred < 3);
+        bool ready = (b0 & b1 & b2) != 0;
         for (int j = 3; j < npred; ++j) ready = ready && done_bit(ext[x_pred + j - 3]);
         if (ready) {
           any_ready = true;
           // none of the task's (private) params is cached anywhere: params_to_load = npar on every node
           const double need = memory_requirement(m, npar);
+          bool all_fit = true;
+#pragma unroll
+          for (int k = 0; k < KMAX; ++k) all_fit = all_fit && (k >= K || need <= avail[k]);
           int best = -1;
           double best_score = -INFINITY;
+          if (all_fit) {
+            // no memory pressure: score = 0.0 + cached*20 + available_memory - len(completed_tasks)*0.5 with cached == 0
+            double hc[KMAX];
 #pragma unroll
-          for (int k = 0; k < KMAX; ++k) {
-            if (k < K) {
-              double score = 0.0;
-              score = __dadd_rn(score, 0.0);  // cached * 20 with cached == 0 (ref :486-487)
-              bool cand = true;
-              if (need <= avail[k]) {
-                score = __dadd_rn(score, avail[k]);  // ref :490-491
-              } else {
-                uint32_t cu = sl.w(CURS + k);
-                const bool ok = evict_private(sl, PN, nslots, k, need, avail[k], cu);  // mutates the node (ref :492)
-                sl.w(CURS + k) = cu;
-                if (ok) score = __dadd_rn(score, 5.0);
-                else cand = false;
+            for (int k = 0; k < KMAX; ++k) hc[k] = sl.f(HCNT + k);
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) {
+              const double score = __dsub_rn(__dadd_rn(0.0, avail[k]), hc[k]);  // ref :483-498 (avail = -inf off the end)
+              if (score > best_score) { best_score = score; best = k; }
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) {
+              if (k < K) {
+                double score = 0.0;
+                bool cand = true;
+                if (need <= avail[k]) {
+                  score = __dadd_rn(score, avail[k]);  // ref :490-491
+                } else {
+                  uint32_t cu = sl.w(CURS + k);
+                  const bool ok = evict_private(sl, PN, nslots, k, need, avail[k], cu);  // mutates the node (ref :492)
+                  sl.w(CURS + k) = cu;
+                  if (ok) score = __dadd_rn(score, 5.0);
+                  else cand = false;
+                }
+                score = __dsub_rn(score, sl.f(HCNT + k));  // ref :498
+                if (cand && score > best_score) { best_score = score; best = k; }
               }
-              score = __dsub_rn(score, __dmul_rn((double)(int)sl.w(CNT + k), 0.5));  // ref :498
-              if (cand && score > best_score) { best_score = score; best = k; }
             }
           }
           if (best >= 0) {
@@ -533,21 +728,24 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
 #pragma unroll
               for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
             } else {
-              for (int j = 0; j < npar; ++j) a = __dsub_rn(a, 0.5);
+              if (npar > 0) a = __dsub_rn(a, 0.5);
+              if (npar > 1) a = __dsub_rn(a, 0.5);
+              for (int j = 2; j < npar; ++j) a = __dsub_rn(a, 0.5);
               a = __dsub_rn(a, m);
               a = __dadd_rn(a, m);
 #pragma unroll
               for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
               sl.f(FIN + best) = __dadd_rn(sl.f(FIN + best), __ddiv_rn(c, sl.f(SPD + best)));
+              sl.f(HCNT + best) = __dadd_rn(sl.f(HCNT + best), 0.5);
               sl.w(CNT + best) += 1;
               to.misses += npar;
               uint32_t cu = sl.w(CURS + best);
               for (int j = 0; j < npar; ++j) {
-                const uint32_t s = j == 0 ? (cur.hi.z & 0xffff) : j == 1 ? (cur.hi.z >> 16) : (uint32_t)ext[x_par + j - 2];
-                const uint32_t sh = (s & 7) * 4;
-                uint32_t& word = sl.w(PN + (s >> 3));
+                const uint32_t sd = j == 0 ? (cur.hi.z & 0xffff) : j == 1 ? (cur.hi.z >> 16) : (uint32_t)ext[x_par + j - 2];
+                const uint32_t sh = (sd & 7) * 4;
+                uint32_t& word = sl.w(PN + (sd >> 3));
                 word = (word & ~(0xFu << sh)) | ((uint32_t)best << sh);  // node.cached_params.add(param)
-                cu = min(cu, s);
+                cu = min(cu, sd);
               }
               sl.w(CURS + best) = cu;
               curw |= 1u << (t & 31);
@@ -578,11 +776,20 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
 // -------------------------------------------------------------------------------------------------------------------
 // unpermute_kernel: one warp per instance. node_of[order[t]] = verdict[t]; seq_pos = prefix count of assignments.
 // -------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int kind) {
-  const int inst = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+struct SlotKinds {
+  int kind[4];
+};
+
+// grid (ceil(B/4), A): one warp per (instance, algorithm slot). With `staged`, verdicts are scattered into shared
+// memory first and written out coalesced; without (per-instance arrays too large), they are scattered directly.
+__global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_result_t r, Workspace w, SlotKinds sk, int n_al,
+                                                        int staged) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int inst = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, slot = blockIdx.y;
   if (inst >= b.B) return;
   const int route = w.route[(int64_t)slot * b.B + inst];
   if (route == 1) return;  // the warp-per-DAG kernel writes this instance
+  const int kind = sk.kind[slot];
   Inst v;
   bind_instance(b, inst, v);
   const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
@@ -591,6 +798,8 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   const int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
   int8_t* node_of = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
   uint16_t* seq_pos = r.seq_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  int8_t* s_node = reinterpret_cast<int8_t*>(smem_raw) + (size_t)(threadIdx.x >> 5) * 3 * n_al;
+  uint16_t* s_seq = reinterpret_cast<uint16_t*>(s_node + n_al);
   int base = 0;
   for (int t0 = 0; t0 < v.n; t0 += 32) {
     const int t = t0 + lane;
@@ -600,10 +809,18 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
     if (t < v.n) {
       const int i = order[t];
       if (route == 2 && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
-      node_of[i] = (int8_t)verdict;
-      seq_pos[i] = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
+      const uint16_t sq = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
+      if (staged) { s_node[i] = (int8_t)verdict; s_seq[i] = sq; }
+      else { node_of[i] = (int8_t)verdict; seq_pos[i] = sq; }
     }
     base += __popc(asg);
+  }
+  if (staged) {
+    __syncwarp();
+    for (int i = lane; i < v.n; i += 32) {
+      node_of[i] = s_node[i];
+      seq_pos[i] = s_seq[i];
+    }
   }
 }
 
@@ -613,7 +830,7 @@ size_t smem_simple(int nw_done) {
 }
 template <int KMAX>
 size_t smem_mru(int nw_done, int nw_pn) {
-  return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(nw_done + nw_pn + 2 * KMAX) * 32 * 4);
+  return (size_t)(kTPB / 32) * ((size_t)3 * KMAX * 32 * 8 + (size_t)(nw_done + nw_pn + 2 * KMAX) * 32 * 4);
 }
 
 }  // namespace
@@ -645,6 +862,10 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
   if (algo_mask & 3) kinds |= 1 << kStreamDG;
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
   if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
+  const size_t staged = (size_t)b.n_max * 32 + ((size_t)b.n_max + 1) * sizeof(uint32_t) +
+                        (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
+  if (staged <= 180 * 1024)
+    return launch_fast(stream_build_staged_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B), kBuildThreads, staged, ctx, b, w, kinds);
   const size_t smem = ((size_t)b.n_max + 1) * sizeof(uint32_t) + (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
   return launch_fast(stream_build_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B, 3), kBuildThreads, smem, ctx, b, w, kinds);
 }
@@ -653,38 +874,40 @@ template <int KMAX>
 static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                          LaunchCtx& ctx) {
   const int nw_done = (b.n_max + 31) / 32, nw_pn = (b.P_max + 7) / 8;
-  const dim3 grid((b.B + kTPB - 1) / kTPB), ugrid((b.B + 3) / 4);
+  const dim3 grid((b.B + kTPB - 1) / kTPB);
   int slot = 0;
+  SlotKinds sk = {{0, 0, 0, 0}};
   cudaError_t e = cudaSuccess;
   if (algo_mask & (1 << DLS_ALGO_DFS)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX>, DLS_KERNEL_STREAM_DFS, grid, kTPB, smem_simple<KMAX>(nw_done),
                     ctx, b, r, w, slot, nw_done);
-    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamDG);
     if (e != cudaSuccess) return e;
-    ++slot;
+    sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_GREEDY)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
                     smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done);
-    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamDG);
     if (e != cudaSuccess) return e;
-    ++slot;
+    sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
                     smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done);
-    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamCP);
     if (e != cudaSuccess) return e;
-    ++slot;
+    sk.kind[slot++] = kStreamCP;
   }
   if (algo_mask & (1 << DLS_ALGO_MRU)) {
     e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, grid, kTPB, smem_mru<KMAX>(nw_done, nw_pn), ctx, b,
                     r, w, slot, nw_done, nw_pn);
-    if (e == cudaSuccess) e = launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, ugrid, 128, 0, ctx, b, r, w, slot, kStreamMRU);
     if (e != cudaSuccess) return e;
-    ++slot;
+    sk.kind[slot++] = kStreamMRU;
   }
-  return e;
+  // verdicts of all slots back to task ids in one launch
+  const int n_al = (b.n_max + 3) & ~3;
+  const size_t usm = (size_t)4 * 3 * n_al;
+  const int staged = usm <= 160 * 1024;
+  return launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, dim3((b.B + 3) / 4, slot), 128, staged ? usm : 0, ctx, b, r, w, sk,
+                     n_al, staged);
 }
 
 cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
