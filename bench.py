@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--instances", type=int, default=16384, help="DAG instances per GPU per step")
+    ap.add_argument("--instances", type=int, default=131072, help="DAG instances per GPU per step")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
@@ -199,7 +199,7 @@ def main():
     from dls_b200 import _native as N
     from dls_b200.batch import BatchResult, DeviceBatch, pin_batch, schedule_batch
     from dls_b200.dist import gather_summaries
-    from dls_b200.gen import random_dag_batch
+    from dls_b200.gen import random_dag_batch_device
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the scheduling path has no CPU implementation")
@@ -210,8 +210,10 @@ def main():
     lib = N.load()
 
     B = args.instances
-    host = random_dag_batch(B, N_TASKS, K_NODES, REGIME, seed=1000 + rank)  # this rank's shard of the sweep
-    dev = DeviceBatch(host, device)
+    # this rank's shard of the sweep, built on the device by the library's generator kernels;
+    # the host copy feeds the end-to-end leg (pinned host inputs) and the CPU baseline sample
+    dev = random_dag_batch_device(B, N_TASKS, K_NODES, REGIME, seed=1000 + rank, device=device)
+    host = dev.to_host()
     res = BatchResult(host, N.MASK_ALL, device, peak=False, cached=False)
     ws = torch.empty(int(lib.dls_workspace_bytes(C.byref(dev.struct), N.MASK_ALL)), dtype=torch.uint8, device=device)
     gathered = None

@@ -64,6 +64,13 @@ class DlsResult(C.Structure):
     ]
 
 
+class DlsGen(C.Structure):
+    _fields_ = [
+        ("B", C.c_int32), ("n", C.c_int32), ("K", C.c_int32), ("max_deps", C.c_int32), ("regime", C.c_double),
+        ("seed", C.c_uint64), ("rank", C.c_void_p), ("param_pos", C.c_void_p),
+    ]
+
+
 class DlsPrio(C.Structure):
     _fields_ = [
         ("depth", C.c_void_p), ("outdeg", C.c_void_p), ("up", C.c_void_p), ("order_dg", C.c_void_p),
@@ -74,7 +81,7 @@ class DlsPrio(C.Structure):
 # Every symbol include/dls.h declares; tests check the built library exports all of them.
 EXPORTED_SYMBOLS = (
     "dls_version", "dls_last_error", "dls_workspace_bytes", "dls_schedule_batch", "dls_priorities",
-    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path",
+    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path", "dls_generate_counts", "dls_generate_fill",
 )
 STATIC_SCRATCH_BYTES = 32 << 20
 NUM_KERNELS = 13
@@ -139,6 +146,10 @@ def load() -> C.CDLL:
                                            C.c_size_t, C.c_void_p]
         lib.dls_schedule_batch_static.restype = C.c_int
         lib.dls_schedule_batch_static.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsResult), C.c_int, C.c_void_p]
+        lib.dls_generate_counts.restype = C.c_int
+        lib.dls_generate_counts.argtypes = [C.POINTER(DlsGen), C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.dls_generate_fill.restype = C.c_int
+        lib.dls_generate_fill.argtypes = [C.POINTER(DlsGen), C.POINTER(DlsBatch), C.c_void_p]
         lib.dls_set_stream_path.restype = C.c_int
         lib.dls_set_stream_path.argtypes = [C.c_int]
         lib.dls_priorities.restype = C.c_int

@@ -122,6 +122,30 @@ class DeviceBatch:
         self.struct = host.as_struct(lambda f, a: self.tensors[f].data_ptr())
 
 
+    @classmethod
+    def from_tensors(cls, meta: DagBatch, tensors: dict, device) -> "DeviceBatch":
+        """Wrap arrays that already live on the device (e.g. built by gen.random_dag_batch_device). `meta` carries
+        the scalar fields and the (small) offset tables on the host; its large arrays may be None."""
+        self = cls.__new__(cls)
+        self.host = meta.validate()
+        self.device = _torch().device(device)
+        self.tensors = dict(tensors)
+        self.h2d_bytes = 0
+        self.struct = meta.as_struct_present(lambda f: self.tensors[f].data_ptr() if f in self.tensors else None)
+        return self
+
+    def to_host(self) -> DagBatch:
+        """Copy every array back (device-generated batches: to feed the CPU oracle in tests)."""
+        import dataclasses
+        vals = {}
+        for f, t in self.tensors.items():
+            a = t.cpu().numpy()
+            want = {"pred_ptr": np.uint32, "par_ptr": np.uint32, "pred_idx": np.uint16, "par_idx": np.uint16,
+                    "rank": np.uint16}.get(f)
+            vals[f] = a.view(want) if want is not None else a
+        return dataclasses.replace(self.host, **vals)
+
+
 def pin_batch(host: DagBatch) -> dict:
     """Pinned host staging copies of a batch's arrays (for timed host->device transfers)."""
     return {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL if getattr(host, f) is not None}

@@ -267,6 +267,42 @@ int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, in
   return run_schedule(batch, result, algo_mask, base, (size_t)DLS_STATIC_SCRATCH_BYTES, cuda_stream, true);
 }
 
+static int check_gen(const dls_gen_t* g) {
+  if (!g || !g->rank || !g->param_pos) return fail(DLS_ERR_BAD_ARG, "NULL in dls_gen_t");
+  if (g->B <= 0 || g->n <= 0 || g->K <= 0) return fail(DLS_ERR_BAD_ARG, "B, n, K must be positive");
+  if (g->n > 20000 || g->K > DLS_MAX_NODES || g->max_deps < 0 || g->max_deps > 8)
+    return fail(DLS_ERR_TOO_LARGE, "generator limits: n <= 20000, K <= 32, max_deps <= 8");
+  return DLS_OK;
+}
+
+int dls_generate_counts(const dls_gen_t* gen, int32_t* e_count, int32_t* r_count, void* cuda_stream) {
+  int rc = check_gen(gen);
+  if (rc != DLS_OK) return rc;
+  if (!e_count || !r_count) return fail(DLS_ERR_BAD_ARG, "NULL count output");
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  cudaError_t e = dls::launch_gen_count(*gen, e_count, r_count, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
+int dls_generate_fill(const dls_gen_t* gen, const dls_batch_t* out, void* cuda_stream) {
+  int rc = check_gen(gen);
+  if (rc != DLS_OK) return rc;
+  if (!out || out->B != gen->B || out->T != gen->B || !out->node_off) return fail(DLS_ERR_BAD_ARG, "output batch does not match the generator");
+  rc = validate(out, DLS_MASK_ALL, false);
+  if (rc != DLS_OK) return rc;
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  cudaError_t e = dls::launch_gen_fill(*gen, *out, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
 /* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
 int dls_set_stream_path(int enabled) {

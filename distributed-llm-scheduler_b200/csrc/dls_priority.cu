@@ -113,21 +113,53 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     for (uint32_t e = tid; e < v.E; e += blockDim.x) s_pidx[e] = v.pred_idx[e];
   }
   __syncthreads();
-  int sweeps = 0, changed;
-  do {
-    changed = 0;
-    for (int i = tid; i < n; i += blockDim.x) {
-      int d = 0;
-      for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) d = max(d, (int)s_depth[pidx[e]] + 1);
-      d = min(d, 65535);
-      if (d != s_depth[i]) {
-        s_depth[i] = (uint16_t)d;
-        changed = 1;
+  // Tasks are usually listed in a topological order already (every dependency has a smaller index: all of the
+  // reference's generators emit them that way). Then one in-order pass by a single warp is exact: a chunk of 32
+  // tasks is repeated only while some task of the chunk still depends on another task of the same chunk.
+  int unsorted = 0;
+  for (int i = tid; i < n; i += blockDim.x)
+    for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) unsorted |= pidx[e] >= i;
+  unsorted = __syncthreads_or(unsorted);
+  int sweeps = 0, changed = 0;
+  if (!unsorted) {
+    if (tid < 32) {
+      for (int base = 0; base < n; base += 32) {
+        const int i = base + tid;
+        const uint32_t eb = i < n ? pptr[i] : 0, ee = i < n ? pptr[i + 1] : 0;
+        bool again;
+        do {
+          int d = 0;
+          bool inside = false;  // depends on a task of this chunk whose depth may still move
+          for (uint32_t e = eb; e < ee; ++e) {
+            const int p = pidx[e];
+            d = max(d, (int)s_depth[p] + 1);
+            inside |= p >= base;
+          }
+          d = min(d, 65535);
+          const bool moved = i < n && d != s_depth[i];
+          if (moved) s_depth[i] = (uint16_t)d;
+          __syncwarp();
+          again = __any_sync(DLS_FULL_MASK, moved && true) && __any_sync(DLS_FULL_MASK, inside);
+        } while (again);
       }
     }
-    changed = __syncthreads_or(changed);
-    ++sweeps;
-  } while (changed && sweeps <= n + 1);
+    __syncthreads();
+  } else {
+    do {
+      changed = 0;
+      for (int i = tid; i < n; i += blockDim.x) {
+        int d = 0;
+        for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) d = max(d, (int)s_depth[pidx[e]] + 1);
+        d = min(d, 65535);
+        if (d != s_depth[i]) {
+          s_depth[i] = (uint16_t)d;
+          changed = 1;
+        }
+      }
+      changed = __syncthreads_or(changed);
+      ++sweeps;
+    } while (changed && sweeps <= n + 1);
+  }
   if (changed) {
     if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
     return;
@@ -234,7 +266,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   for (int q = tid; q < P; q += blockDim.x) g_erank[s_dst[q]] = (uint16_t)q;
 }
 
-__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key) {
+__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key, int m_sort) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
   const int inst = blockIdx.x, tid = threadIdx.x;
@@ -245,8 +277,11 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   if (n == 0) return;
   const int n_al = (n + 3) & ~3;
   double* s_up = reinterpret_cast<double*>(smem_raw);             // [n]
-  double* s_key = s_up + n;                                        // [n]   up[] in DFS/Greedy order (only with use_key)
-  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(s_up + (use_key ? 2 * n : n));  // [n+2] first position of each level
+  // sort scratch: counting with keys (use_key): s_key[n]; bitonic (m_sort = power of two >= n): s_key[m], s_lq[m]
+  double* s_key = s_up + n;
+  const int nkey = m_sort ? m_sort : (use_key ? n : 0);
+  uint32_t* s_lq = reinterpret_cast<uint32_t*>(s_key + nkey);      // [m_sort] (level << 16 | position)
+  uint32_t* s_lvl = s_lq + m_sort;                                 // [n+2] first position of each level
   uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
   uint16_t* s_depth = s_ord + n_al;                               // [n_al]
   const uint16_t* g_depth = w.depth + v.t_topo;
@@ -288,7 +323,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   }
   for (int i = tid; i < n; i += blockDim.x) {
     w.up[cp_off + i] = s_up[i];
-    if (use_key) s_key[i] = s_up[s_ord[i]];  // keys in pi order inside each level: the loops below read them sequentially
+    if (use_key || m_sort) s_key[i] = s_up[s_ord[i]];  // keys in pi order inside each level
   }
   __syncthreads();
   // within-level stable sort by up desc: ready_tasks.sort(key=critical_path, reverse=True), ref schedulers.py:343.
@@ -324,9 +359,15 @@ size_t priority_smem_param(int n_max, int P_max) {
   return (P + 2 + n + 2) * sizeof(uint32_t) + 3 * P_al * sizeof(uint16_t);
 }
 
+// A block-wide bitonic network over (level, up, position) was tried for the Critical order (round 1c): with its
+// ~55 barriers per 1k-task DAG it ran 2x SLOWER than the per-level counting below, so it is not used.
+static int bitonic_size(int) { return 0; }
+
 size_t priority_smem_inst(int n_max, bool with_key) {
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
-  return (with_key ? 2 : 1) * n * sizeof(double) + (n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
+  const size_t m = with_key ? (size_t)bitonic_size(n_max) : 0;
+  const size_t nkey = m ? m : (with_key ? n : 0);
+  return (n + nkey) * sizeof(double) + (m + n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
 }
 
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
@@ -361,12 +402,13 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     size_t sm2 = priority_smem_inst(b.n_max, true);
     const int use_key = sm2 <= 96 * 1024;
     if (!use_key) sm2 = priority_smem_inst(b.n_max, false);
+    const int m_sort = use_key ? bitonic_size(b.n_max) : 0;
     ctx.why = "cudaFuncSetAttribute(priority_critical_kernel)";
     e = cudaFuncSetAttribute(priority_critical_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     int grid = w.cp_per_instance ? b.B : 1;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;
-    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w, use_key);
+    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w, use_key, m_sort);
     if (ctx.prof) ctx.prof->end(rec, ctx.st);
     ++ctx.launches;
     ctx.why = "priority_critical_kernel launch";

@@ -112,3 +112,58 @@ def perturbed_durations(dag: LoweredDag, B: int, eps: float = 0.1, seed: int = 0
     """Config 3: dur_i * (1 + e), e ~ U(-eps, eps), one row per instance."""
     rng = np.random.default_rng(seed)
     return dag.dur[None, :] * (1.0 + rng.uniform(-eps, eps, (B, dag.n)))
+
+
+def random_dag_batch_device(B: int, n: int, K: int = 8, regime: float = 0.9, seed: int = 0, max_deps: int = 3,
+                            device=None, rank: Optional[np.ndarray] = None):
+    """Config-5 sweep inputs built ON the GPU by the library's generator kernels (dls_generate_counts/_fill).
+    Returns a DeviceBatch; `.to_host()` copies it back for oracle checks. torch is used for the buffers and for the
+    two prefix sums over per-instance counts."""
+    import ctypes as C
+
+    import torch
+
+    from . import _native as N
+    from .batch import DeviceBatch
+    lib = N.load()
+    if not torch.cuda.is_available():
+        raise RuntimeError("no CUDA device: the generator kernels have no CPU implementation")
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    with torch.cuda.device(dev):
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        rank_h = task_rank(n) if rank is None else rank.astype(np.uint16)
+        rank_d = torch.from_numpy(rank_h.view(np.int16)).to(dev)
+        ppos_d = torch.from_numpy(_param_name_order(n).astype(np.uint16).view(np.int16)).to(dev)
+        g = N.DlsGen(B=B, n=n, K=K, max_deps=max_deps, regime=regime, seed=seed, rank=rank_d.data_ptr(),
+                     param_pos=ppos_d.data_ptr())
+        e_cnt = torch.empty(B, dtype=torch.int32, device=dev)
+        r_cnt = torch.empty(B, dtype=torch.int32, device=dev)
+        N.check(lib.dls_generate_counts(C.byref(g), e_cnt.data_ptr(), r_cnt.data_ptr(), stream))
+        zero = torch.zeros(1, dtype=torch.int64, device=dev)
+        pred_off = torch.cat([zero, torch.cumsum(e_cnt.to(torch.int64), 0)])
+        par_off = torch.cat([zero, torch.cumsum(r_cnt.to(torch.int64), 0)])
+        task_off = torch.arange(B + 1, dtype=torch.int64, device=dev) * n
+        node_off = torch.arange(B + 1, dtype=torch.int64, device=dev) * K
+        e_total, r_total = int(pred_off[-1].item()), int(par_off[-1].item())
+        e_max, r_max = int(e_cnt.max().item()), int(r_cnt.max().item())
+        t = {
+            "task_off": task_off, "pred_off": pred_off, "par_off": par_off, "pid_off": par_off, "node_off": node_off,
+            "pred_ptr": torch.empty(B * (n + 1), dtype=torch.int32, device=dev),
+            "pred_idx": torch.empty(max(e_total, 1), dtype=torch.int16, device=dev),
+            "par_ptr": torch.empty(B * (n + 1), dtype=torch.int32, device=dev),
+            "par_idx": torch.empty(max(r_total, 1), dtype=torch.int16, device=dev),
+            "rank": torch.empty(B * n, dtype=torch.int16, device=dev),
+            "mem": torch.empty(B * n, dtype=torch.float64, device=dev),
+            "dur": torch.empty(B * n, dtype=torch.float64, device=dev),
+            "cap": torch.empty(B * K, dtype=torch.float64, device=dev),
+            "spd": torch.empty(B * K, dtype=torch.float64, device=dev),
+        }
+        meta = DagBatch(
+            B=B, T=B, n_max=n, K_max=K, P_max=r_max, E_max=e_max, R_max=r_max, flags=0,
+            task_off=task_off.cpu().numpy(), pred_off=pred_off.cpu().numpy(), par_off=par_off.cpu().numpy(),
+            pid_off=par_off.cpu().numpy(), pred_ptr=None, pred_idx=None, par_ptr=None, par_idx=None, rank=None,
+            mem=None, dur=None, node_off=node_off.cpu().numpy(), cap=None, spd=None, dags=None)
+        db = DeviceBatch.from_tensors(meta, t, dev)
+        N.check(lib.dls_generate_fill(C.byref(g), C.byref(db.struct), stream))
+        db._keep = (rank_d, ppos_d)
+    return db

@@ -329,8 +329,15 @@ class DagBatch:
         s.nt_topo, s.nt_inst, s.e_total, s.r_total = self.nt_topo, self.nt_inst, self.e_total, self.r_total
         s.nk_inst, s.np_inst = self.nk_inst, self.np_inst
         for f in _FIELDS_ALL:
-            a = getattr(self, f)
+            a = getattr(self, f, None)
             setattr(s, f, None if a is None else ptr_of(f, a))
+        return s
+
+    def as_struct_present(self, ptr_of_name) -> N.DlsBatch:
+        """dls_batch_t from addresses looked up by field name (arrays need not exist on the host)."""
+        s = self.as_struct(lambda f, a: None)
+        for f in _FIELDS_ALL:
+            setattr(s, f, ptr_of_name(f))
         return s
 
     def host_struct(self):

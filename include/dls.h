@@ -207,6 +207,26 @@ int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, 
 #define DLS_STATIC_SCRATCH_BYTES (32u << 20)
 int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* cuda_stream);
 
+/*
+ * Device-side DAG builder: emits B random DAGs of n tasks straight into the CSR arrays of a
+ * dls_batch_t, with the distribution of DAGGenerator.generate_random_dag (simulation.py:91-114) and node sets from
+ * calculate_total_memory_needed / create_nodes_with_memory_regime (simulation.py:161-214). The random stream is a
+ * counter-based hash of (seed, instance, task, draw), so instances are reproducible but are not the reference's
+ * Mersenne-Twister instances. Two steps because CSR sizes are data dependent:
+ *   1. dls_generate_counts: e_count[b], r_count[b] = dependency / param-reference entries of instance b;
+ *   2. the caller prefix-sums them into pred_off/par_off/pid_off (pid_off == par_off: params are private), sets
+ *      task_off[b] = b*n and node_off[b] = b*K, allocates the arrays, and calls dls_generate_fill.
+ */
+typedef struct dls_gen {
+  int32_t B, n, K, max_deps; /* max_deps <= 8 (reference default 3) */
+  double regime;             /* memory regime, e.g. 0.9 */
+  uint64_t seed;
+  const uint16_t* rank;      /* [n]  device: pi of the task names 'task_0'..'task_{n-1}' (host hash order) */
+  const uint16_t* param_pos; /* [2n] device: position of 'param_{i}_{j}' (slot 2i+j) among all 2n names sorted */
+} dls_gen_t;
+int dls_generate_counts(const dls_gen_t* gen, int32_t* e_count, int32_t* r_count, void* cuda_stream);
+int dls_generate_fill(const dls_gen_t* gen, const dls_batch_t* out, void* cuda_stream);
+
 /* Test/measurement switch (no reference counterpart). Qualifying batches (K <= 8 nodes, small per-DAG state, no
  * extension outputs requested) normally run on the thread-per-DAG streamed kernels; 0 forces the general
  * warp-per-DAG kernels for everything, 1 restores the default. Returns the previous setting. */

@@ -82,15 +82,15 @@ def test_lowering_contract():
     assert sh.B == 1 and sh.K_max == 1 and sh.pred_ptr.tolist() == d.pred_ptr.tolist()
 
 
-def test_generator_matches_reference_distribution():
-    """gen.random_dag_batch follows generate_random_dag's shape (ref simulation.py:91-114): deps only on earlier
-    tasks, <=3 distinct deps, 1-2 private params, value ranges; ids are lexicographic ranks of param names."""
-    b = random_dag_batch(32, 300, 8, 0.9, seed=3)
-    n = 300
+def check_random_dag_structure(b, n):
+    """Invariants of generate_random_dag's shape (ref simulation.py:91-114): deps only on earlier tasks, <= 3 distinct
+    deps, 1-2 private params, value ranges; param ids are lexicographic ranks of the names 'param_{i}_{j}'; node
+    memory follows calculate_total_memory_needed / create_nodes_with_memory_regime (ref simulation.py:161-214)."""
     for i in range(b.B):
         pp = b.pred_ptr[i * (n + 1):(i + 1) * (n + 1)]
         pi = b.pred_idx[b.pred_off[i]:b.pred_off[i + 1]]
         deg = np.diff(pp)
+        assert pp[0] == 0 and pp[-1] == len(pi)
         assert deg.max() <= 3 and deg[0] == 0 and deg[1] <= 1
         child = np.repeat(np.arange(n), deg)
         assert (pi < child).all()
@@ -105,5 +105,15 @@ def test_generator_matches_reference_distribution():
         rank = {nm: r for r, nm in enumerate(sorted(names))}
         want = [sorted(rank[f"param_{t}_{j}"] for j in range(npar[t])) for t in range(n)]
         assert [qi[qp[t]:qp[t + 1]].tolist() for t in range(n)] == want
+        mem = b.mem[i * n:(i + 1) * n]
+        total = (mem + npar * 0.5).max() + len(qi) * 0.5
+        K = int(b.node_off[i + 1] - b.node_off[i])
+        cap = b.cap[b.node_off[i]:b.node_off[i + 1]]
+        if K not in (2, 4):
+            assert (cap == total * 0.9 / K).all() or np.allclose(cap, cap[0])
     assert 0.1 <= b.mem.min() and b.mem.max() <= 0.5 and 0.05 <= b.dur.min() and b.dur.max() <= 0.15
-    assert abs(np.diff(b.pred_ptr.reshape(32, n + 1), axis=1).mean() - 1.5) < 0.1
+    assert abs(np.diff(b.pred_ptr.reshape(b.B, n + 1), axis=1).mean() - 1.5) < 0.1
+
+
+def test_generator_matches_reference_distribution():
+    check_random_dag_structure(random_dag_batch(32, 300, 8, 0.9, seed=3), 300)

@@ -149,6 +149,27 @@ def test_streamed_path_is_taken_and_falls_back():
             assert_matches_expected(c.exp[a], mb, res, slot, b, f"mixed {c.label} algo={a}")
 
 
+def test_device_generator_parity_and_shape(oracle_mod):
+    """the device-side DAG builder emits valid CSR batches with generate_random_dag's shape, is
+    reproducible, and what it emits schedules identically on the GPU and in the oracle."""
+    from dls_b200.gen import random_dag_batch_device
+    from test_abi_cpu import check_random_dag_structure
+    for n, K, regime in ((300, 8, 0.9), (64, 4, 0.7), (1000, 2, 0.8)):
+        dev = random_dag_batch_device(96, n, K, regime, seed=5)
+        host = dev.to_host()
+        check_random_dag_structure(host, n)
+        again = random_dag_batch_device(96, n, K, regime, seed=5).to_host()
+        other = random_dag_batch_device(96, n, K, regime, seed=6).to_host()
+        for f in ("pred_ptr", "pred_idx", "par_idx", "mem", "dur", "cap", "spd"):
+            np.testing.assert_array_equal(getattr(host, f), getattr(again, f))
+        assert not np.array_equal(host.mem, other.mem)
+        want = oracle_mod.schedule_batch(host, N.MASK_ALL, nthreads=8)
+        got = schedule_batch(dev, N.MASK_ALL).host()          # straight from the device-resident batch
+        assert_results_equal(got, want, f"device-generated n={n} K={K}")
+        for path, res in run_both_paths(host, N.MASK_ALL):   # and through the host round trip
+            assert_results_equal(res, want, f"{path} device-generated n={n} K={K}")
+
+
 def test_error_codes():
     import ctypes as C
     lib = N.load()
