@@ -64,6 +64,7 @@ class BaseScheduler:
         self.pending_tasks = set()
         self._added: List[Task] = []
         self.last_summary = None  # dls_summary_t of the last schedule() as a numpy record
+        self.last_device_result = None
 
     def add_task(self, task: Task):
         """ref schedulers.py:43-48"""
@@ -109,13 +110,23 @@ class BaseScheduler:
                 self.failed_tasks.add(tid)
                 self.pending_tasks.discard(tid)
             return {}
-        dag = lower_tasks(tasks, pending=list(self.pending_tasks))
+        dag = lower_tasks(tasks, pending=self._pending_order())
         cap = np.asarray([float(x.available_memory) for x in node_list], np.float64)
         _, spd = lower_nodes(node_list)
         batch = DagBatch.from_instances([dag], [(cap, spd)])
         res = schedule_batch(batch, 1 << self.ALGO, peak=False, cached=True).host()
         self._lift(batch, res, dag, node_list)
-        return schedule_dict(batch, res, 0, 0, dag.names, [x.id for x in node_list])
+        sched = schedule_dict(batch, res, 0, 0, dag.names, [x.id for x in node_list])
+        # simulate_execution's outputs (ref simulation.py:216-278) came out of the same kernel; keep them for callers
+        self.last_device_result = {
+            "schedule": sched, "makespan": float(res.summary[0, 0]["makespan"]), "hits": int(res.summary[0, 0]["hits"]),
+            "misses": int(res.summary[0, 0]["misses"]),
+            "fin": {nd.id: float(res.fin[0, k]) for k, nd in enumerate(node_list)}}
+        return sched
+
+    def _pending_order(self) -> List[str]:
+        """Iteration order of the pending set = the reference's tie-break among ready tasks (ref schedulers.py:58)."""
+        return list(self.pending_tasks)
 
     def _lift(self, batch: DagBatch, res: ResultArrays, dag, node_list: List[Node]):
         summ = res.summary[0, 0]

@@ -31,7 +31,8 @@ from dls_b200.lowering import lower_nodes, lower_tasks  # noqa: E402
 
 IN_FIELDS = ("pred_ptr", "pred_idx", "par_ptr", "par_idx", "rank", "mem", "dur")
 EXP_ARR = ("node_of", "order", "fin", "cnt", "avail", "peak", "cached")
-EXP_SCALAR = ("completed", "failed", "pending", "makespan", "hits", "misses")
+EXP_SCALAR = ("completed", "failed", "pending", "makespan", "hits", "misses", "avg_node_utilization",
+              "load_balance_score", "completion_rate")
 
 
 def llm_dag_wide(sch, num_layers: int, heads: int):

@@ -9,7 +9,9 @@ from common import ROOT  # noqa: F401  (puts the repo root on sys.path)
 from dls_b200.lowering import DagBatch, LoweredDag
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-SCALARS = ("completed", "failed", "pending", "makespan", "hits", "misses")
+SCALARS = ("completed", "failed", "pending", "makespan", "hits", "misses", "avg_node_utilization",
+           "load_balance_score", "completion_rate")
+FLOAT_SCALARS = ("makespan", "avg_node_utilization", "load_balance_score", "completion_rate")
 
 
 class Case:
@@ -31,7 +33,7 @@ class Case:
             e = {f: z[f"c{c}_a{a}_{f}"] for f in ("node_of", "order", "fin", "cnt", "avail", "peak", "cached")}
             sc = z[f"c{c}_a{a}_scalars"]
             for f, v in zip(SCALARS, sc):
-                e[f] = float(v) if f == "makespan" else int(v)
+                e[f] = float(v) if f in FLOAT_SCALARS else int(v)
             lens = z[f"c{c}_a{a}_pernode_len"]
             flat = z[f"c{c}_a{a}_pernode"]
             offs = np.concatenate([[0], np.cumsum(lens)])

@@ -118,8 +118,12 @@ def run_reference(algo: int, tasks, nodes):
         sys.setrecursionlimit(lim)
     ev = sim.ImprovedSchedulerEvaluator({})
     makespan, stats = ev.simulate_execution(s, schedule)
+    util = list(stats["node_utilization"].values())
     return {"scheduler": s, "pi": pi, "schedule": schedule, "makespan": float(makespan), "stats": stats,
-            "tasks": task_copies, "nodes": node_copies, "evaluator": ev}
+            "tasks": task_copies, "nodes": node_copies, "evaluator": ev,
+            "avg_node_utilization": float(np.mean(util)) if util else 0.0,              # ref simulation.py:344-345
+            "load_balance_score": float(ev.calculate_load_balance(s, schedule)),       # ref simulation.py:347
+            "completion_rate": (len(s.completed_tasks) / len(tasks) * 100) if tasks else 0.0}
 
 
 def expected_arrays(run, dag):
@@ -159,4 +163,6 @@ def expected_arrays(run, dag):
             "per_node_seq": per_node_seq, "completed": len(s.completed_tasks), "failed": len(s.failed_tasks),
             "pending": len(s.pending_tasks), "makespan": run["makespan"],
             "hits": run["stats"]["param_cache_hits"], "misses": run["stats"]["param_cache_misses"],
-            "key_order": [kidx[k] for k in run["schedule"].keys()]}
+            "key_order": [kidx[k] for k in run["schedule"].keys()],
+            "avg_node_utilization": run["avg_node_utilization"], "load_balance_score": run["load_balance_score"],
+            "completion_rate": run["completion_rate"]}
