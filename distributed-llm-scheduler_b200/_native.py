@@ -84,7 +84,7 @@ EXPORTED_SYMBOLS = (
     "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path", "dls_generate_counts", "dls_generate_fill",
 )
 STATIC_SCRATCH_BYTES = 32 << 20
-NUM_KERNELS = 13
+NUM_KERNELS = 14
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

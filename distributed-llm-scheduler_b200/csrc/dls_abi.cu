@@ -21,7 +21,7 @@ const char* const kKernelNames[DLS_NUM_KERNELS] = {"priority_topology_kernel", "
                                                    "param_class_kernel", "stream_build_kernel",
                                                    "sched_stream_kernel<DFS>", "sched_stream_kernel<Greedy>",
                                                    "sched_stream_kernel<Critical>", "sched_stream_mru_kernel",
-                                                   "unpermute_kernel"};
+                                                   "unpermute_kernel", "prep_fused_kernel"};
 
 int fail(int code, const std::string& msg) {
   g_err = msg;
@@ -150,6 +150,7 @@ int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
 }
 
 bool g_stream_enabled = true;
+bool g_fused_enabled = false;  // measured slower than the separate kernels (profiles/r1d_*): 2 CTAs/SM cannot hide its barriers
 
 int cuda_fail(cudaError_t e, const char* why) {
   return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
@@ -209,8 +210,12 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
     e = cudaMemsetAsync(w.topo_status, 0, (size_t)batch->T * sizeof(int32_t), ctx.st);
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(built-in scratch)");
   }
-  e = dls::launch_priority(*batch, w, algo_mask, ctx);
-  if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
+  if (stream && g_fused_enabled && dls::prep_fused_possible(*batch, lim)) {
+    e = dls::launch_prep_fused(*batch, w, algo_mask, ctx);  // priorities, orders and streams in one shared-memory pass
+  } else {
+    e = dls::launch_priority(*batch, w, algo_mask, ctx);
+    if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
+  }
   if (e == cudaSuccess && stream) e = dls::launch_stream_sched(*batch, *result, w, algo_mask, ctx);
   if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
   g_launches += ctx.launches;
@@ -306,8 +311,9 @@ int dls_generate_fill(const dls_gen_t* gen, const dls_batch_t* out, void* cuda_s
 /* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
 int dls_set_stream_path(int enabled) {
-  const int old = g_stream_enabled ? 1 : 0;
+  const int old = !g_stream_enabled ? 0 : (g_fused_enabled ? 2 : 1);
   g_stream_enabled = enabled != 0;
+  g_fused_enabled = enabled == 2;
   return old;
 }
 

@@ -236,6 +236,8 @@ cudaError_t launch_schedule(const dls_batch_t& b, const dls_result_t& r, const W
                             LaunchCtx& ctx);
 cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_count, LaunchCtx& ctx);
 cudaError_t launch_gen_fill(const dls_gen_t& g, const dls_batch_t& out, LaunchCtx& ctx);
+cudaError_t launch_prep_fused(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
+bool prep_fused_possible(const dls_batch_t& b, int smem_limit);
 cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                 LaunchCtx& ctx);

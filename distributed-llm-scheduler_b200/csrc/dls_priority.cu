@@ -13,49 +13,13 @@
 // priority_critical_kernel: one CTA per instance. Upward rank level by level from the sinks, then the
 // within-level stable sort by rank-by-counting.
 #include "dls_common.cuh"
+#include "dls_sort.cuh"
 
 namespace dls {
 
 namespace {
 
-constexpr int kThreadsP = 128;
-
-__device__ __forceinline__ uint32_t lanemask_lt() {
-  uint32_t m;
-  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
-  return m;
-}
-
-// dst = src stably sorted by key(task) ascending, key in [0, nkeys). Histogram by all threads, placement by
-// warp 0 walking src in order, 32 at a time, with __match_any giving each lane its rank among equal keys.
-template <class KeyF>
-__device__ void stable_counting_sort(const uint16_t* src, uint16_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
-                                     uint32_t* s_part) {
-  for (int k = threadIdx.x; k <= nkeys; k += blockDim.x) s_hist[k] = 0;
-  __syncthreads();
-  for (int q = threadIdx.x; q < n; q += blockDim.x) atomicAdd(&s_hist[key(src[q])], 1u);
-  __syncthreads();
-  block_exclusive_scan(s_hist, nkeys, s_part);
-  if (threadIdx.x < 32) {
-    const int lane = threadIdx.x;
-    for (int base = 0; base < n; base += 32) {
-      const int q = base + lane;
-      const bool valid = q < n;
-      const unsigned vm = __ballot_sync(DLS_FULL_MASK, valid);
-      if (valid) {
-        const int i = src[q];
-        const uint32_t k = key(i);
-        const unsigned peers = __match_any_sync(vm, k);
-        const uint32_t pos = s_hist[k] + __popc(peers & lanemask_lt());
-        dst[pos] = (uint16_t)i;
-        __syncwarp(vm);
-        if (lane == __ffs(peers) - 1) s_hist[k] += __popc(peers);
-        __syncwarp(vm);
-      }
-    }
-  }
-  __syncthreads();
-}
+constexpr int kThreadsP = 128;   // measured r1d: 64 and 256 threads per CTA are both slower for the topology kernel
 
 __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru, int stage) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -200,7 +164,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   __syncthreads();
   const int maxd = s_maxd, maxdeg = s_maxdeg;
   // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
-  stable_counting_sort(s_ord, s_tmp, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, s_part);
+  stable_counting_sort(s_ord, s_tmp, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, n + 2, s_part);
   for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = s_tmp[q];
   __syncthreads();
   if (want_mru) {
@@ -208,8 +172,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     uint32_t* s_deg = s_cnt;  // reuse: out-degree per task
     for (int i = tid; i < n; i += blockDim.x) s_deg[i] = g_outdeg[i];
     __syncthreads();
-    stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, s_part);
-    stable_counting_sort(s_tmp, s_ord, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, s_part);
+    stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, n + 2, s_part);
+    stable_counting_sort(s_tmp, s_ord, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, n + 2, s_part);
     for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_ord[q];
   }
 }
@@ -262,7 +226,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   atomicMax(&s_maxd, md);
   for (int p = tid; p < P; p += blockDim.x) s_src[p] = (uint16_t)p;
   __syncthreads();
-  stable_counting_sort(s_src, s_dst, P, s_maxd + 1, [&](int p) { return (uint32_t)s_ownd[p]; }, s_hist, s_part);
+  stable_counting_sort(s_src, s_dst, P, s_maxd + 1, [&](int p) { return (uint32_t)s_ownd[p]; }, s_hist, n + 2, s_part);
   for (int q = tid; q < P; q += blockDim.x) g_erank[s_dst[q]] = (uint16_t)q;
 }
 
@@ -278,8 +242,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   const int n_al = (n + 3) & ~3;
   double* s_up = reinterpret_cast<double*>(smem_raw);             // [n]
   // sort scratch: counting with keys (use_key): s_key[n]; bitonic (m_sort = power of two >= n): s_key[m], s_lq[m]
-  double* s_key = s_up + n;
-  const int nkey = m_sort ? m_sort : (use_key ? n : 0);
+  double* s_key = s_up + ((n + 1) & ~1);  // 16-byte aligned: read as double2
+  const int nkey = m_sort ? m_sort : (use_key ? ((n + 1) & ~1) : 0);
   uint32_t* s_lq = reinterpret_cast<uint32_t*>(s_key + nkey);      // [m_sort] (level << 16 | position)
   uint32_t* s_lvl = s_lq + m_sort;                                 // [n+2] first position of each level
   uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
@@ -335,8 +299,23 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     const double u = s_up[i];
     int ahead = 0;
     if (use_key) {
-      for (int q2 = ls; q2 < q; ++q2) ahead += s_key[q2] >= u;
-      for (int q2 = q + 1; q2 < le; ++q2) ahead += s_key[q2] > u;
+      // keys are read as aligned pairs (one 16-byte shared load, broadcast across the warp) and the loops unrolled
+      int q2 = ls;
+      if ((q2 & 1) && q2 < q) { ahead += s_key[q2] >= u; ++q2; }
+#pragma unroll 4
+      for (; q2 + 1 < q; q2 += 2) {
+        const double2 kk = *reinterpret_cast<const double2*>(s_key + q2);
+        ahead += (kk.x >= u) + (kk.y >= u);
+      }
+      for (; q2 < q; ++q2) ahead += s_key[q2] >= u;
+      q2 = q + 1;
+      if ((q2 & 1) && q2 < le) { ahead += s_key[q2] > u; ++q2; }
+#pragma unroll 4
+      for (; q2 + 1 < le; q2 += 2) {
+        const double2 kk = *reinterpret_cast<const double2*>(s_key + q2);
+        ahead += (kk.x > u) + (kk.y > u);
+      }
+      for (; q2 < le; ++q2) ahead += s_key[q2] > u;
     } else {  // very large DAGs: no room for the second key array
       for (int q2 = ls; q2 < q; ++q2) ahead += s_up[s_ord[q2]] >= u;
       for (int q2 = q + 1; q2 < le; ++q2) ahead += s_up[s_ord[q2]] > u;
@@ -366,14 +345,14 @@ static int bitonic_size(int) { return 0; }
 size_t priority_smem_inst(int n_max, bool with_key) {
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
   const size_t m = with_key ? (size_t)bitonic_size(n_max) : 0;
-  const size_t nkey = m ? m : (with_key ? n : 0);
-  return (n + nkey) * sizeof(double) + (m + n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
+  const size_t nkey = m ? m : (with_key ? ((n + 1) & ~(size_t)1) : 0);
+  return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (m + n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
 }
 
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
   cudaError_t e;
   size_t sm1 = priority_smem_topo(b.n_max, b.E_max);
-  const int stage = sm1 <= 64 * 1024;  // staging pays while several CTAs still fit an SM
+  const int stage = 0;  // measured (r1c): with the in-order depth pass the CSR is read once; staging only costs occupancy
   if (!stage) sm1 = priority_smem_topo(b.n_max, -1);
   ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
   e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);

@@ -1,0 +1,56 @@
+// dls_sort.cuh — CTA-level stable counting sort shared by the priority kernels.
+#pragma once
+
+#include "dls_common.cuh"
+
+namespace dls {
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// dst = src stably sorted by key(task) ascending, key in [0, nkeys). s_hist has hist_cap words.
+// When nkeys * (warps per CTA) counters fit, every warp owns a contiguous chunk of src: it counts its keys, one
+// block-wide scan over the [key][warp] table turns the counts into start offsets, and each warp then places its own
+// chunk, 32 elements at a time, with __match_any giving each lane its rank among equal keys (stable). Otherwise the
+// histogram is shared and warp 0 places everything.
+template <class KeyF>
+__device__ inline void stable_counting_sort(const uint16_t* src, uint16_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
+                                     int hist_cap, uint32_t* s_part) {
+  const int nwarp = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool split = nkeys * nwarp + 1 <= hist_cap;
+  const int stride = split ? nwarp : 1, col = split ? wid : 0;
+  const int per = split ? (((n + nwarp - 1) / nwarp + 31) & ~31) : n;
+  const int lo = split ? min(wid * per, n) : 0, hi = split ? min(lo + per, n) : n;
+  for (int k = threadIdx.x; k <= nkeys * stride; k += blockDim.x) s_hist[k] = 0;
+  __syncthreads();
+  if (split) {
+    for (int q = lo + lane; q < hi; q += 32) atomicAdd(&s_hist[key(src[q]) * stride + col], 1u);
+  } else {
+    for (int q = threadIdx.x; q < n; q += blockDim.x) atomicAdd(&s_hist[key(src[q])], 1u);
+  }
+  __syncthreads();
+  block_exclusive_scan(s_hist, nkeys * stride, s_part);
+  if (split || wid == 0) {
+    for (int base = lo; base < hi; base += 32) {
+      const int q = base + lane;
+      const bool valid = q < hi;
+      const unsigned vm = __ballot_sync(DLS_FULL_MASK, valid);
+      if (valid) {
+        const int i = src[q];
+        const uint32_t k = key(i) * stride + col;
+        const unsigned peers = __match_any_sync(vm, k);
+        const uint32_t pos = s_hist[k] + __popc(peers & lanemask_lt());
+        dst[pos] = (uint16_t)i;
+        __syncwarp(vm);
+        if (lane == __ffs(peers) - 1) s_hist[k] += __popc(peers);
+        __syncwarp(vm);
+      }
+    }
+  }
+  __syncthreads();
+}
+
+}  // namespace dls

@@ -71,5 +71,11 @@ def run_both_paths(batch, mask):
     produce the peak/cached extensions) and the thread-per-DAG streamed kernels (taken when no extension output is
     requested and the batch qualifies; otherwise the library falls back to the general ones by itself)."""
     from dls_b200.batch import schedule_batch
+    from dls_b200 import _native as N
     yield "general", schedule_batch(batch, mask, peak=True, cached=True).host()
     yield "streamed", schedule_batch(batch, mask, peak=False, cached=False).host()
+    old = N.load().dls_set_stream_path(2)  # streamed kernels fed by the fused preparation kernel
+    try:
+        yield "streamed+fused-prep", schedule_batch(batch, mask, peak=False, cached=False).host()
+    finally:
+        N.load().dls_set_stream_path(old)
