@@ -263,3 +263,95 @@ def priorities(batch, device=None):
         a = t.cpu().numpy()
         res[k] = a.view(np.uint16) if a.dtype == np.int16 else a
     return res
+
+
+class PipelinedScheduler:
+    """End-to-end path for HOST batches: instances are cut into chunks and pushed through `nstreams` CUDA streams so
+    that the host->device copy of chunk i+1, the kernels of chunk i and the device->host copy of chunk i-1 overlap
+    (PCIe is full duplex; the kernels need neither direction). Inputs are staged in pinned memory once per batch
+    object; results land in pinned host arrays (`.out`, same layout as ResultArrays).
+    """
+
+    def __init__(self, host: DagBatch, algo_mask: int = N.MASK_ALL, device=None, chunks: int = 8, nstreams: int = 3):
+        torch = _torch()
+        if host.T != host.B:
+            raise ValueError("pipelining shards by instance: needs one topology per instance (T == B)")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.mask, self.algos = algo_mask, algos_of(algo_mask)
+        A = len(self.algos)
+        # pinned copies of the inputs; the chunks below are numpy views into them
+        pinned = {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL if getattr(host, f) is not None}
+        import dataclasses
+        views = {f: t.numpy().view(getattr(host, f).dtype) for f, t in pinned.items()}
+        self._pinned = pinned
+        self.host = dataclasses.replace(host, **views)
+        chunks = max(1, min(chunks, host.B))
+        bounds = [(c * host.B) // chunks for c in range(chunks + 1)]
+        self.parts = [(lo, hi, self.host.shard(lo, hi)) for lo, hi in zip(bounds[:-1], bounds[1:]) if hi > lo]
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(min(nstreams, len(self.parts)))]
+        big = max(self.parts, key=lambda p: p[2].nt_inst)[2]
+        with torch.cuda.device(self.device):
+            self._res = [BatchResult(big, algo_mask, self.device, False, False) for _ in self.streams]
+            probe = DeviceBatch(big, self.device)
+            need = int(N.load().dls_workspace_bytes(C.byref(probe.struct), algo_mask))
+            self._ws = [torch.empty(need, dtype=torch.uint8, device=self.device) for _ in self.streams]
+        pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
+        self.out = {"node_of": pin((A, host.nt_inst), torch.int8), "seq_pos": pin((A, host.nt_inst), torch.int16),
+                    "summary": pin((A, host.B, N.SUMMARY_BYTES), torch.uint8), "fin": pin((A, host.nk_inst), torch.float64),
+                    "cnt": pin((A, host.nk_inst), torch.int32), "avail": pin((A, host.nk_inst), torch.float64)}
+        self.h2d_bytes = sum(t.numel() * t.element_size() for t in pinned.values())
+        self.d2h_bytes = sum(t.numel() * t.element_size() for t in self.out.values())
+
+    def run(self):
+        """One pass over the whole batch. Returns after everything has been ENQUEUED; call `.synchronize()`."""
+        torch = _torch()
+        keep = []
+        for c, (lo, hi, part) in enumerate(self.parts):
+            slot = c % len(self.streams)
+            st = self.streams[slot]
+            with torch.cuda.stream(st):
+                dev = DeviceBatch(part, self.device, non_blocking=True)
+                res = self._res[slot]
+                # result buffers are sized for the largest chunk; point the call at the leading part
+                sub = BatchResult.__new__(BatchResult)
+                sub.batch, sub.mask, sub.algos = part, self.mask, self.algos
+                A = len(self.algos)
+                views = {"node_of": res.node_of.view(-1)[:A * part.nt_inst].view(A, part.nt_inst),
+                         "seq_pos": res.seq_pos.view(-1)[:A * part.nt_inst].view(A, part.nt_inst),
+                         "summary": res.summary.view(-1)[:A * part.B * N.SUMMARY_BYTES].view(A, part.B, N.SUMMARY_BYTES),
+                         "fin": res.fin.view(-1)[:A * part.nk_inst].view(A, part.nk_inst),
+                         "cnt": res.cnt.view(-1)[:A * part.nk_inst].view(A, part.nk_inst),
+                         "avail": res.avail.view(-1)[:A * part.nk_inst].view(A, part.nk_inst)}
+                r = N.DlsResult()
+                for f, t in views.items():
+                    setattr(sub, f, t)
+                    setattr(r, f, t.data_ptr())
+                sub.peak = sub.cached = None
+                sub.struct = r
+                schedule_batch(dev, self.mask, workspace=self._ws[slot], result=sub)
+                t0, t1 = int(self.host.task_off[lo]), int(self.host.task_off[hi])
+                k0, k1 = (int(self.host.node_off[lo]), int(self.host.node_off[hi])) if self.host.node_off is not None else (
+                    lo * self.host.K_max, hi * self.host.K_max)
+                for a in range(A):  # one contiguous async copy per array and algorithm slot (strided copies would be staged)
+                    self.out["node_of"][a, t0:t1].copy_(views["node_of"][a], non_blocking=True)
+                    self.out["seq_pos"][a, t0:t1].copy_(views["seq_pos"][a], non_blocking=True)
+                    self.out["summary"][a, lo:hi].copy_(views["summary"][a], non_blocking=True)
+                    self.out["fin"][a, k0:k1].copy_(views["fin"][a], non_blocking=True)
+                    self.out["cnt"][a, k0:k1].copy_(views["cnt"][a], non_blocking=True)
+                    self.out["avail"][a, k0:k1].copy_(views["avail"][a], non_blocking=True)
+                keep.append(dev)
+        self._keep = keep
+        return self
+
+    def synchronize(self):
+        for st in self.streams:
+            st.synchronize()
+        return self
+
+    def result(self) -> ResultArrays:
+        self.synchronize()
+        o = self.out
+        return ResultArrays(
+            algos=self.algos, node_of=o["node_of"].numpy(), seq_pos=o["seq_pos"].numpy().view(np.uint16),
+            summary=o["summary"].numpy().view(np.dtype(N.SUMMARY_DTYPE)).reshape(len(self.algos), self.host.B),
+            fin=o["fin"].numpy(), cnt=o["cnt"].numpy(), avail=o["avail"].numpy(), peak=None, cached=None)

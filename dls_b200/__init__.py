@@ -9,7 +9,7 @@ __path__.insert(0, _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.absp
 
 from . import _native  # noqa: E402
 from .lowering import DagBatch, LoweredDag, lower_nodes, lower_tasks, set_order  # noqa: E402,F401
-from .batch import (BatchResult, DeviceBatch, ResultArrays, algos_of, pin_batch, priorities,  # noqa: E402,F401
+from .batch import (BatchResult, DeviceBatch, PipelinedScheduler, ResultArrays, algos_of, pin_batch, priorities,  # noqa: E402,F401
                     schedule_batch, schedule_dict, sequence_of)
 from .schedulers import (SCHEDULERS, BaseScheduler, CriticalPathScheduler, DFSScheduler,  # noqa: E402,F401
                          GreedyScheduler, MRUScheduler, Node, Task)

@@ -171,6 +171,18 @@ def test_device_generator_parity_and_shape(oracle_mod):
             assert_results_equal(res, want, f"{path} device-generated n={n} K={K}")
 
 
+def test_pipelined_host_path_matches_single_call(oracle_mod):
+    """The chunked, multi-stream end-to-end path (host in, host out) returns exactly what one call returns."""
+    from dls_b200.batch import PipelinedScheduler
+    batch = random_dag_batch(150, 120, 8, 0.8, seed=31)
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    pipe = PipelinedScheduler(batch, N.MASK_ALL, chunks=7, nstreams=3)
+    for _ in range(2):  # buffers are reused across runs
+        got = pipe.run().result()
+        want.peak = want.cached = None
+        assert_results_equal(got, want, "pipelined")
+
+
 def test_error_codes():
     import ctypes as C
     lib = N.load()
