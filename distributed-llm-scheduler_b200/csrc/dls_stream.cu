@@ -533,62 +533,54 @@ __device__ __forceinline__ uint32_t nibble_eq_mask(uint32_t word, uint32_t k) {
   return ~(((x & 0x77777777u) + 0x77777777u) | x) & 0x88888888u;
 }
 
-// evict_params_for_task (ref schedulers.py:404-442) on node k. Returns the reference's bool; updates avail_k, pnode
-// and the cursor. Candidates are visited in slot order (== sorted (score, name) order, see param_class_kernel).
-__device__ bool evict_private(const Slab& sl, int PN, int nslots, int k, double need, double& avail_k, uint32_t& cursor) {
+// evict_params_for_task (ref schedulers.py:404-442) on one node, split in two so that the 32 DAGs of a warp stay
+// converged (measured r1e: ~1.2 evictions per DAG-step under pressure, on different nodes in different lanes; run
+// inline in the node loop, every lane's eviction serialised the whole warp).
+//
+// plan_evict — arithmetic only. The candidates are the node's `ncached` cached params (none belongs to the task:
+// its params are private and not loaded yet), each frees exactly 0.5, and the reference walks them until
+// `freed >= shortage`: it needs j = ceil(shortage / 0.5) of them and succeeds iff j <= ncached. On success the
+// node's available memory goes up by 0.5, j times (ref :429); on failure all ncached are evicted and rolled back,
+// which leaves only the +0.5 / -0.5 rounding trace (ref :438-441). Returns the reference's bool, `j` slots to clear.
+__device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_t& ncached, uint32_t& j) {
+  j = 0;
   const double shortage = __dsub_rn(need, avail_k);
   if (shortage <= 0.0) return true;
-  double freed = 0.0;
-  int nev = 0;
-  uint32_t pos = cursor;       // first slot not yet examined
-  uint32_t hit[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};  // first evicted slots (commit without rescanning)
+  const double want = ceil(__dmul_rn(shortage, 2.0));  // exact: power-of-two scaling, then ceil
+  if (want <= (double)ncached) {
+    j = (uint32_t)want;
+    for (uint32_t q = 0; q < j; ++q) avail_k = __dadd_rn(avail_k, 0.5);
+    ncached -= j;
+    return true;
+  }
+  for (uint32_t q = 0; q < ncached; ++q) avail_k = __dadd_rn(avail_k, 0.5);
+  for (uint32_t q = 0; q < ncached; ++q) avail_k = __dsub_rn(avail_k, 0.5);
+  return false;
+}
+
+// apply_evict — node.cached_params.remove(param) for the `count` lowest slots of node k at or after `cursor`
+// (slot order == sorted (score, name) order, see param_class_kernel). Returns the new cursor.
+__device__ __forceinline__ uint32_t apply_evict(const Slab& sl, int PN, int nslots, uint32_t k, uint32_t count, uint32_t cursor) {
   const uint32_t nwords = (uint32_t)(nslots + 7) >> 3;
-  bool ok = false;
-  uint32_t wd = pos >> 3;
-  uint32_t hits = wd < nwords ? (nibble_eq_mask(sl.w(PN + wd), (uint32_t)k) & (0xffffffffu << ((pos & 7) * 4))) : 0;
-  while (true) {
-    if (freed >= shortage) { ok = true; break; }
-    while (hits == 0 && ++wd < nwords) hits = nibble_eq_mask(sl.w(PN + wd), (uint32_t)k);
-    if (wd >= nwords) break;  // candidates exhausted
-    const uint32_t bit = __ffs(hits) - 1;
-    hits &= hits - 1;
-    const uint32_t slot = (wd << 3) + (bit >> 2);
-    if (nev == 0) hit[0] = slot;
-    else if (nev == 1) hit[1] = slot;
-    else if (nev == 2) hit[2] = slot;
-    else if (nev == 3) hit[3] = slot;
-    pos = slot + 1;
-    avail_k = __dadd_rn(avail_k, 0.5);  // ref :429
-    freed = __dadd_rn(freed, 0.5);      // ref :431
-    ++nev;
-  }
-  if (ok) {
-    // commit: node.cached_params.remove(param) for the nev lowest slots of node k
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-      if (q < nev) sl.w(PN + (hit[q] >> 3)) |= 0xFu << ((hit[q] & 7) * 4);
-    if (nev > 4) {  // rare: more than four params evicted at once; walk on from the fourth
-      uint32_t w2 = (hit[3] + 1) >> 3;
-      int left = nev - 4;
-      uint32_t h2 = nibble_eq_mask(sl.w(PN + w2), (uint32_t)k) & (0xffffffffu << (((hit[3] + 1) & 7) * 4));
-      while (left > 0) {
-        while (h2 == 0) h2 = nibble_eq_mask(sl.w(PN + (++w2)), (uint32_t)k);
-        uint32_t word = sl.w(PN + w2);
-        while (h2 && left > 0) {
-          const uint32_t bit = __ffs(h2) - 1;
-          h2 &= h2 - 1;
-          word |= 0xFu << (bit - 3);
-          --left;
-        }
-        sl.w(PN + w2) = word;
-      }
+  uint32_t wd = cursor >> 3, pos = cursor;
+  uint32_t mask = 0xffffffffu << ((cursor & 7) * 4);
+  while (count > 0 && wd < nwords) {
+    uint32_t word = sl.w(PN + wd);
+    uint32_t hits = nibble_eq_mask(word, k) & mask;
+    mask = 0xffffffffu;
+    if (hits) {
+      do {
+        const uint32_t bit = __ffs(hits) - 1;
+        hits &= hits - 1;
+        word |= 0xFu << (bit - 3);
+        pos = (wd << 3) + (bit >> 2) + 1;
+        --count;
+      } while (hits && count > 0);
+      sl.w(PN + wd) = word;
     }
-    cursor = pos;
-  } else {
-    for (int q = 0; q < nev; ++q) avail_k = __dsub_rn(avail_k, 0.5);  // rollback (ref :438-441); nothing was cleared
-    cursor = hit[0] == 0xffffffffu ? (uint32_t)nslots : hit[0];
+    ++wd;
   }
-  return ok;
+  return pos;
 }
 
 template <int KMAX>
@@ -633,7 +625,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
     sl.f(SPD + k) = on ? v.spd[k] : 1.0;
     sl.f(HCNT + k) = 0.0;
     sl.w(CNT + k) = 0;
-    sl.w(CURS + k) = (uint32_t)nslots;  // nothing cached yet
+    sl.w(CURS + k) = (uint32_t)nslots;  // low half: lower bound of the node's first cached slot; high half: #cached
   }
   for (int x = 0; x < nw_done; ++x) sl.w(DONE + x) = 0;
   for (int x = 0; x < nw_pn; ++x) sl.w(PN + x) = 0xffffffffu;
@@ -684,6 +676,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
           for (int k = 0; k < KMAX; ++k) all_fit = all_fit && (k >= K || need <= avail[k]);
           int best = -1;
           double best_score = -INFINITY;
+          unsigned long long pend = 0;  // slots to clear per node (one byte each), filled by the node loop
           if (all_fit) {
             // no memory pressure: score = 0.0 + cached*20 + available_memory - len(completed_tasks)*0.5 with cached == 0
             double hc[KMAX];
@@ -703,9 +696,18 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
                 if (need <= avail[k]) {
                   score = __dadd_rn(score, avail[k]);  // ref :490-491
                 } else {
-                  uint32_t cu = sl.w(CURS + k);
-                  const bool ok = evict_private(sl, PN, nslots, k, need, avail[k], cu);  // mutates the node (ref :492)
-                  sl.w(CURS + k) = cu;
+                  // evict_params_for_task mutates the node even if another node wins (ref :492): decide and
+                  // account now, clear the slots after the node loop
+                  const uint32_t cw = sl.w(CURS + k);
+                  uint32_t nc = cw >> 16, jk;
+                  const bool ok = plan_evict(need, avail[k], nc, jk);
+                  sl.w(CURS + k) = (cw & 0xffffu) | (nc << 16);
+                  if (jk > 255u) {  // cannot be queued in a byte: clear right away (never seen; keeps the code total)
+                    const uint32_t cu = apply_evict(sl, PN, nslots, k, jk, cw & 0xffffu);
+                    sl.w(CURS + k) = cu | (nc << 16);
+                  } else {
+                    pend |= (unsigned long long)jk << (8 * k);
+                  }
                   if (ok) score = __dadd_rn(score, 5.0);
                   else cand = false;
                 }
@@ -714,13 +716,34 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
               }
             }
           }
+          double a = 0.0;
           if (best >= 0) {
-            double a = pick<KMAX>(avail, best);
-            if (!(need <= a)) {  // ref :506-507
-              uint32_t cu = sl.w(CURS + best);
-              evict_private(sl, PN, nslots, best, need, a, cu);
-              sl.w(CURS + best) = cu;
+            a = pick<KMAX>(avail, best);
+            if (!(need <= a)) {  // ref :506-507 (only after a rounding mishap in the first eviction)
+              const uint32_t cw = sl.w(CURS + best);
+              uint32_t nc = cw >> 16, jk;
+              plan_evict(need, a, nc, jk);
+              sl.w(CURS + best) = (cw & 0xffffu) | (nc << 16);
+              const uint32_t queued = (uint32_t)(pend >> (8 * best)) & 0xffu;
+              if (queued + jk > 255u) {
+                const uint32_t cu = apply_evict(sl, PN, nslots, (uint32_t)best, queued + jk, cw & 0xffffu);
+                sl.w(CURS + best) = cu | (nc << 16);
+                pend &= ~(0xffull << (8 * best));
+              } else {
+                pend += (unsigned long long)jk << (8 * best);
+              }
             }
+          }
+          // clear the evicted slots: each lane works through its own queue, all lanes run the same scan code
+          while (pend != 0) {
+            const uint32_t k = (uint32_t)(__ffsll((long long)pend) - 1) >> 3;
+            const uint32_t cnt = (uint32_t)(pend >> (8 * k)) & 0xffu;
+            pend &= ~(0xffull << (8 * k));
+            const uint32_t cw = sl.w(CURS + k);
+            const uint32_t cu = apply_evict(sl, PN, nslots, k, cnt, cw & 0xffffu);
+            sl.w(CURS + k) = cu | (cw & 0xffff0000u);
+          }
+          if (best >= 0) {
             if (need > a) {
               // assign_task_to_node refuses (ref :82-83): the reference retries next round; flagged, not replayed
               to.status |= DLS_ST_CARRY;
@@ -739,7 +762,8 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
               sl.f(HCNT + best) = __dadd_rn(sl.f(HCNT + best), 0.5);
               sl.w(CNT + best) += 1;
               to.misses += npar;
-              uint32_t cu = sl.w(CURS + best);
+              const uint32_t cw = sl.w(CURS + best);
+              uint32_t cu = cw & 0xffffu;
               for (int j = 0; j < npar; ++j) {
                 const uint32_t sd = j == 0 ? (cur.hi.z & 0xffff) : j == 1 ? (cur.hi.z >> 16) : (uint32_t)ext[x_par + j - 2];
                 const uint32_t sh = (sd & 7) * 4;
@@ -747,7 +771,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
                 word = (word & ~(0xFu << sh)) | ((uint32_t)best << sh);  // node.cached_params.add(param)
                 cu = min(cu, sd);
               }
-              sl.w(CURS + best) = cu;
+              sl.w(CURS + best) = cu | (((cw >> 16) + (uint32_t)npar) << 16);  // cursor | params cached on the node
               curw |= 1u << (t & 31);
               sl.w(DONE + (t >> 5)) = curw;
               verdict = best;

@@ -1,0 +1,26 @@
+import sys, time, ctypes as C
+sys.path.insert(0, '/root/repo')
+import numpy as np, torch
+from dls_b200 import _native as N
+from dls_b200.batch import schedule_batch
+from dls_b200.gen import random_dag_batch_device
+lib = N.load()
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 131072
+dev = random_dag_batch_device(B, 1000, 8, 0.9, seed=1000)
+res = schedule_batch(dev, 0xF)
+torch.cuda.synchronize()
+lib.dls_profile_enable(1)
+ms = (C.c_double * N.NUM_KERNELS)(); cnt = (C.c_int64 * N.NUM_KERNELS)()
+lib.dls_profile_read(ms, cnt)
+for i in range(N.NUM_KERNELS): ms[i]=0; cnt[i]=0
+for it in range(3):
+    res = schedule_batch(dev, 0xF, workspace=res.workspace, result=res)
+torch.cuda.synchronize()
+lib.dls_profile_read(ms, cnt)
+for k in range(N.NUM_KERNELS):
+    if cnt[k] and ms[k]/cnt[k] > 0.2:
+        print(f"{lib.dls_kernel_name(k).decode():34s} avg ms {ms[k]/cnt[k]:9.3f}  -> inst/s {B/(ms[k]/cnt[k])*1e3:14.0f}")
+tot = sum(ms) / 3
+print("total ms/step", tot, "schedules/s", 4 * B / tot * 1e3)
+s = res.summary_host()
+print("completed mean per algo", s["completed"].mean(1), "status any", s["status"].any())
