@@ -250,8 +250,21 @@ __global__ void __launch_bounds__(kPrepThreads) prep_fused_kernel(dls_batch_t b,
   stable_counting_sort(s_ord, s_odg, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, hist_cap, s_part);
   for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = s_odg[q];
   if (want_mru) {
-    stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - min(s_cnt[i], 65535u); }, s_hist,
-                         hist_cap, s_part);
+    if (maxdeg + 2 <= hist_cap) {
+      stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - min(s_cnt[i], 65535u); }, s_hist,
+                           hist_cap, s_part);
+    } else {  // out-degrees beyond the histogram (duplicate dependency entries): place by counting
+      for (int q = tid; q < n; q += blockDim.x) {
+        const uint32_t dq = min(s_cnt[s_ord[q]], 65535u);
+        int ahead = 0;
+        for (int q2 = 0; q2 < n; ++q2) {
+          const uint32_t d2 = min(s_cnt[s_ord[q2]], 65535u);
+          ahead += (d2 > dq) || (d2 == dq && q2 < q);
+        }
+        s_tmp[ahead] = s_ord[q];
+      }
+      __syncthreads();
+    }
     stable_counting_sort(s_tmp, s_omru, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, hist_cap, s_part);
     for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_omru[q];
   }

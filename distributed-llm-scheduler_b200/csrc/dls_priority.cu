@@ -30,14 +30,18 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   bind_topology(b, t, v);
   const int n = v.n;
   const int n_al = (n + 3) & ~3;
-  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw);  // [n+2]
-  uint32_t* s_hist = s_cnt + (n + 2);                       // [n+2]
-  uint16_t* s_depth = reinterpret_cast<uint16_t*>(s_hist + (n + 2));  // [n_al]
-  uint16_t* s_ord = s_depth + n_al;                                     // [n_al]
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw);              // [n+2]
+  uint16_t* s_depth = reinterpret_cast<uint16_t*>(s_cnt + (n + 2));     // [n_al]
+  uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_depth + n_al);       // [n+2]
+  uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_hist + (n + 2));      // [n_al]
   uint16_t* s_tmp = s_ord + n_al;                                       // [n_al]
-  // with `stage`: dependency CSR copied to shared memory (it is walked once per relaxation sweep)
-  uint32_t* s_pptr = reinterpret_cast<uint32_t*>(s_tmp + n_al);         // [n+1]
-  uint16_t* s_pidx = reinterpret_cast<uint16_t*>(s_pptr + (n + 1));     // [E]
+  // Until the orders are built (which is when s_hist / s_ord / s_tmp are first needed) the same bytes hold a copy of
+  // the dependency CSR: row pointers over s_hist, indices over s_ord + s_tmp (if they fit: E <= 2 n). The depth pass
+  // walks the CSR with dependent loads, one 32-task chunk after the other; from global memory that chain cost 48 %
+  // of this kernel (measured with clock64 per phase, round 1e).
+  uint32_t* s_pptr = s_hist;                                            // [n+1]
+  uint16_t* s_pidx = s_ord;                                             // [E]
+  stage = stage && v.E <= (uint32_t)(2 * n_al);
   const uint32_t* pptr = stage ? s_pptr : v.pred_ptr;
   const uint16_t* pidx = stage ? s_pidx : v.pred_idx;
 
@@ -56,12 +60,22 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
       return;
     }
     if (n > 0 && (v.pred_ptr[0] != 0 || v.par_ptr[0] != 0 || v.pred_ptr[n] != v.E || v.par_ptr[n] != v.R)) bad = 1;
+    // every load below is independent of the others: unrolled so that a thread has them all in flight at once
+#pragma unroll 8
     for (int i = tid; i < n; i += blockDim.x) {
-      if (v.pred_ptr[i] > v.pred_ptr[i + 1] || v.par_ptr[i] > v.par_ptr[i + 1]) bad = 1;
+      const uint32_t p0 = v.pred_ptr[i], p1 = v.pred_ptr[i + 1], q0 = v.par_ptr[i], q1 = v.par_ptr[i + 1];
+      if (p0 > p1 || q0 > q1 || p1 > v.E) bad = 1;
       if (v.rank[i] >= n) bad = 1;
+      if (stage) s_pptr[i] = p0;
     }
-    for (uint32_t e = tid; e < v.E; e += blockDim.x)
-      if (v.pred_idx[e] >= n) bad = 1;
+    if (stage && tid == 0) s_pptr[n] = v.E;
+#pragma unroll 8
+    for (uint32_t e = tid; e < v.E; e += blockDim.x) {
+      const uint16_t p = v.pred_idx[e];
+      if (p >= n) bad = 1;
+      if (stage) s_pidx[e] = p;
+    }
+#pragma unroll 8
     for (uint32_t e = tid; e < v.R; e += blockDim.x)
       if (v.par_idx[e] >= v.P) bad = 1;
     if (__syncthreads_or(bad)) {
@@ -72,10 +86,6 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   // ---- depth: relax until a fixed point (<= levels+1 sweeps; more than n+1 sweeps means a cycle) ----
   // The dependency CSR is staged in shared memory once: every sweep walks it again.
   for (int i = tid; i < n; i += blockDim.x) s_depth[i] = 0;
-  if (stage) {
-    for (int i = tid; i <= n; i += blockDim.x) s_pptr[i] = v.pred_ptr[i];
-    for (uint32_t e = tid; e < v.E; e += blockDim.x) s_pidx[e] = v.pred_idx[e];
-  }
   __syncthreads();
   // Tasks are usually listed in a topological order already (every dependency has a smaller index: all of the
   // reference's generators emit them that way). Then one in-order pass by a single warp is exact: a chunk of 32
@@ -160,6 +170,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
       g_succ_idx[pos] = (uint16_t)i;
     }
   // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
+  __syncthreads();  // the staged CSR (aliased with s_hist / s_ord / s_tmp) is dead from here on
+#pragma unroll 8
   for (int i = tid; i < n; i += blockDim.x) s_ord[v.rank[i]] = (uint16_t)i;
   __syncthreads();
   const int maxd = s_maxd, maxdeg = s_maxdeg;
@@ -172,7 +184,22 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     uint32_t* s_deg = s_cnt;  // reuse: out-degree per task
     for (int i = tid; i < n; i += blockDim.x) s_deg[i] = g_outdeg[i];
     __syncthreads();
-    stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, n + 2, s_part);
+    if (maxdeg + 2 <= n + 2) {
+      stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, n + 2, s_part);
+    } else {
+      // duplicate dependency entries can push an out-degree beyond n: more keys than the histogram holds.
+      // Rare, so place by counting: position = #(larger degree) + #(equal degree earlier in pi order).
+      for (int q = tid; q < n; q += blockDim.x) {
+        const uint32_t dq = s_deg[s_ord[q]];
+        int ahead = 0;
+        for (int q2 = 0; q2 < n; ++q2) {
+          const uint32_t d2 = s_deg[s_ord[q2]];
+          ahead += (d2 > dq) || (d2 == dq && q2 < q);
+        }
+        s_tmp[ahead] = s_ord[q];
+      }
+      __syncthreads();
+    }
     stable_counting_sort(s_tmp, s_ord, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, n + 2, s_part);
     for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_ord[q];
   }
@@ -326,11 +353,9 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
 
 }  // namespace
 
-size_t priority_smem_topo(int n_max, int E_max) {  // E_max < 0: without the staged dependency CSR
+size_t priority_smem_topo(int n_max, int /*E_max*/) {  // the staged dependency CSR aliases the sort scratch
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
-  size_t base = 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
-  if (E_max < 0) return base;
-  return base + (n + 1) * sizeof(uint32_t) + (((size_t)E_max + 1) & ~(size_t)1) * sizeof(uint16_t);
+  return 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
 }
 
 size_t priority_smem_param(int n_max, int P_max) {
@@ -352,8 +377,7 @@ size_t priority_smem_inst(int n_max, bool with_key) {
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
   cudaError_t e;
   size_t sm1 = priority_smem_topo(b.n_max, b.E_max);
-  const int stage = 0;  // measured (r1c): with the in-order depth pass the CSR is read once; staging only costs occupancy
-  if (!stage) sm1 = priority_smem_topo(b.n_max, -1);
+  const int stage = 1;
   ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
   e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   if (e != cudaSuccess) return e;
