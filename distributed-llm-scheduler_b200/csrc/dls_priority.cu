@@ -280,10 +280,28 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   const uint16_t* succ_idx = w.succ_idx + b.pred_off[v.topo];
   const int64_t cp_off = w.cp_per_instance ? v.t_inst : v.t_topo;
 
+  // One coalesced pass brings in everything the level loop touches: durations land in s_up (a task's slot holds its
+  // own duration until its level is processed), and the reverse adjacency is copied over the key array, which is not
+  // needed before the sort (if it fits: 4(n+1) + 2E bytes in 8n). From global memory the dependent loads of the level
+  // loop were 53 % of this kernel (clock64 per phase, round 1e).
+  const uint32_t E = (uint32_t)(b.pred_off[v.topo + 1] - b.pred_off[v.topo]);
+  const bool staged = (use_key || m_sort) && (size_t)4 * (n + 1) + (size_t)2 * E <= (size_t)8 * ((n + 1) & ~1);
+  uint32_t* s_sptr = reinterpret_cast<uint32_t*>(s_key);
+  uint16_t* s_sidx = reinterpret_cast<uint16_t*>(s_sptr + (n + 1));
+#pragma unroll 8
   for (int q = tid; q < n; q += blockDim.x) {
     s_ord[q] = w.order_dg[v.t_topo + q];
     s_depth[q] = g_depth[q];
+    s_up[q] = v.dur[q];
   }
+  if (staged) {
+#pragma unroll 8
+    for (int i = tid; i <= n; i += blockDim.x) s_sptr[i] = succ_ptr[i];
+#pragma unroll 8
+    for (uint32_t e = tid; e < E; e += blockDim.x) s_sidx[e] = succ_idx[e];
+  }
+  const uint32_t* sptr = staged ? s_sptr : succ_ptr;
+  const uint16_t* sidx = staged ? s_sidx : succ_idx;
   __syncthreads();
   if (tid == 0) s_maxd = s_depth[s_ord[n - 1]];
   for (int q = tid; q < n; q += blockDim.x) {
@@ -298,12 +316,12 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   for (int d = maxd; d >= 0; --d) {
     for (int q = s_lvl[d] + tid; q < (int)s_lvl[d + 1]; q += blockDim.x) {
       const int i = s_ord[q];
-      const uint32_t sb = succ_ptr[i], se = succ_ptr[i + 1];
-      double path = v.dur[i];
+      const uint32_t sb = sptr[i], se = sptr[i + 1];
+      double path = s_up[i];  // == dur[i]
       if (se > sb) {
-        double mx = s_up[succ_idx[sb]];
+        double mx = s_up[sidx[sb]];
         for (uint32_t e = sb + 1; e < se; ++e) {
-          double u = s_up[succ_idx[e]];
+          double u = s_up[sidx[e]];
           if (u > mx) mx = u;
         }
         path = __dadd_rn(path, mx);  // task.compute_time + max(...)  ref schedulers.py:314
@@ -312,6 +330,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     }
     __syncthreads();
   }
+  // (the last level's barrier separates the staged adjacency from the keys that now overwrite it)
   for (int i = tid; i < n; i += blockDim.x) {
     w.up[cp_off + i] = s_up[i];
     if (use_key || m_sort) s_key[i] = s_up[s_ord[i]];  // keys in pi order inside each level
