@@ -146,27 +146,37 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
   TaskRec* s_task = reinterpret_cast<TaskRec*>(smem_raw);                    // [n]
   uint32_t* s_extoff = reinterpret_cast<uint32_t*>(s_task + n);              // [n+1]
   uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));         // [n]
+  uint16_t* s_order = s_pos + ((n + 1) & ~1);                                // [3][n] the processing orders, staged
   const uint16_t* depth = w.depth + v.t_topo;
   const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
   const uint16_t* erank = w.erank + b.pid_off[v.topo];
   if (tid == 0) s_any_ext = 0;
   __syncthreads();
-  // ---- phase 1: task-order gather ----
+  // ---- phase 1: task-order gather (read-only loads, unrolled: a thread keeps several tasks' loads in flight) ----
   int any_ext = 0;
+  for (int kind = 0; kind < 3; ++kind) {
+    if (!((kind_mask >> kind) & 1)) continue;
+    const uint16_t* g_order = kind == kStreamDG ? w.order_dg + v.t_topo
+                            : kind == kStreamMRU ? w.order_mru + v.t_topo
+                                                 : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
+#pragma unroll 4
+    for (int t = tid; t < n; t += blockDim.x) s_order[kind * n + t] = __ldg(g_order + t);
+  }
+#pragma unroll 4
   for (int i = tid; i < n; i += blockDim.x) {
     TaskRec tr;
-    tr.m = v.mem[i];
-    tr.c = v.dur[i];
-    const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
-    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+    tr.m = __ldg(v.mem + i);
+    tr.c = __ldg(v.dur + i);
+    const uint32_t pb = __ldg(v.pred_ptr + i), pe = __ldg(v.pred_ptr + i + 1);
+    const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
     tr.npred = (uint16_t)min(pe - pb, 65535u);
     tr.npar = (uint16_t)min(qe - qb, 65535u);
-    tr.pred[0] = pe - pb > 0 ? v.pred_idx[pb] : 0;
-    tr.pred[1] = pe - pb > 1 ? v.pred_idx[pb + 1] : 0;
-    tr.pred[2] = pe - pb > 2 ? v.pred_idx[pb + 2] : 0;
-    tr.p0 = qe - qb > 0 ? v.par_idx[qb] : 0;
-    tr.p1 = qe - qb > 1 ? v.par_idx[qb + 1] : 0;
-    tr.depth = depth[i];
+    tr.pred[0] = pe - pb > 0 ? __ldg(v.pred_idx + pb) : 0;
+    tr.pred[1] = pe - pb > 1 ? __ldg(v.pred_idx + pb + 1) : 0;
+    tr.pred[2] = pe - pb > 2 ? __ldg(v.pred_idx + pb + 2) : 0;
+    tr.p0 = qe - qb > 0 ? __ldg(v.par_idx + qb) : 0;
+    tr.p1 = qe - qb > 1 ? __ldg(v.par_idx + qb + 1) : 0;
+    tr.depth = __ldg(depth + i);
     s_task[i] = tr;
     any_ext |= (pe - pb > 3) || (qe - qb > 2);
   }
@@ -177,9 +187,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
   for (int kind = 0; kind < 3; ++kind) {
     if (!((kind_mask >> kind) & 1)) continue;
     if (kind == kStreamMRU ? nsh_topo != 0 : nsh_topo > kSharedCap) continue;  // routed to the general kernels
-    const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
-                          : kind == kStreamMRU ? w.order_mru + v.t_topo
-                                               : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
+    const uint16_t* order = s_order + kind * n;
     Rec* out = w.stream[kind] + v.t_inst;
     uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
     __syncthreads();  // previous pass is done with s_pos / s_extoff
@@ -887,7 +895,7 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
   if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
   const size_t staged = (size_t)b.n_max * 32 + ((size_t)b.n_max + 1) * sizeof(uint32_t) +
-                        (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
+                        (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t) + (size_t)3 * b.n_max * sizeof(uint16_t) + 16;
   if (staged <= 180 * 1024)
     return launch_fast(stream_build_staged_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B), kBuildThreads, staged, ctx, b, w, kinds);
   const size_t smem = ((size_t)b.n_max + 1) * sizeof(uint32_t) + (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
