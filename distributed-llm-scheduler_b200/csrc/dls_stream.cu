@@ -22,7 +22,8 @@ namespace dls {
 
 namespace {
 
-constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG kernels
+constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG DFS/Greedy/Critical kernels
+constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp CTAs, 7 instead of 6 warps/SM, are slower)
 constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
 
 __device__ __forceinline__ int64_t ext_offset(const dls_batch_t& b, int inst, const Inst& v) {
@@ -336,15 +337,15 @@ template <int ALGO, int KMAX>
 __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int nw_done) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab layout per warp: doubles fin[KMAX], spd[KMAX]; words done[nw_done], smask[kSharedCap/4], cnt[KMAX]
+  // slab layout per warp: doubles fin[KMAX], spd[KMAX]; words smask[kSharedCap/4], cnt[KMAX]
   constexpr int kD = 2 * KMAX;
-  const int kW = nw_done + kSharedCap / 4 + KMAX;
+  const int kW = kSharedCap / 4 + KMAX;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
   sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
-  const int FIN = 0, SPD = KMAX, DONE = 0, SMASK = nw_done, CNT = nw_done + kSharedCap / 4;
+  const int FIN = 0, SPD = KMAX, SMASK = 0, CNT = kSharedCap / 4;
 
   const int inst = blockIdx.x * kTPB + threadIdx.x;
   const bool have = inst < b.B;
@@ -391,14 +392,14 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       ckey[k] = (k < K && sk > 0.0) ? rank * KMAX + k : 0x7fffffff;
     }
   }
-  for (int x = 0; x < nw_done + kSharedCap / 4; ++x) sl.w(x) = 0;
+  for (int x = 0; x < kSharedCap / 4; ++x) sl.w(SMASK + x) = 0;
 
   ThreadOut to;
   to.completed = to.failed = to.hits = to.misses = to.rounds = 0;
   to.status = DLS_ST_OK;
   to.fail_rest = false;
   bool running = elig, any_ready = false, any_assigned = false;
-  uint32_t curw = 0;
+  uint32_t first_nd = 0xffffffffu;  // smallest order position whose task is not completed (none so far)
   uint32_t xpos = 0;
   RecRegs cur;
   cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
@@ -412,7 +413,6 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
       const int npred = cur.hi.y >> 16, npriv = cur.hi.w & 0xffff, nsh = (cur.hi.w >> 16) & 0xff;
       const int flags = cur.hi.w >> 24;
-      if ((t & 31) == 0) curw = 0;
       if (flags & kRecFirst) {
         if (t > 0 && running) {
           if (!any_ready) running = false;                       // ready list empty (ref schedulers.py:172-174)
@@ -426,12 +426,21 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       if (running) {
         // is_task_ready (ref :50-53). The done word of the current 32-group is written through on every assignment,
         // so shared memory is always current; unused dependency slots hold position 0 and are masked by the count.
-        auto done_bit = [&](uint32_t p) -> uint32_t { return (sl.w(DONE + (p >> 5)) >> (p & 31)) & 1u; };
-        const uint32_t b0 = done_bit(cur.hi.x & 0xffff) | (npred < 1);
-        const uint32_t b1 = done_bit(cur.hi.x >> 16) | (npred < 2);
-        const uint32_t b2 = done_bit(cur.hi.y & 0xffff) | (npred < 3);
-        bool ready = (b0 & b1 & b2) != 0;
-        for (int j = 3; j < npred; ++j) ready = ready && done_bit(ext[x_pred + j - 3]);
+        // is_task_ready (ref :50-53) without a done-bitmap: every position below `first_nd` is done, so a task
+        // whose dependencies all sit below it is ready with no memory access at all; only after the first failed or
+        // blocked task do the (few) later dependencies get looked up in this thread's own verdict bytes.
+        bool ready = true;
+        if (npred > 0) {
+          const uint32_t p0 = cur.hi.x & 0xffff, p1 = cur.hi.x >> 16, p2 = cur.hi.y & 0xffff;
+          uint32_t pm = p0;
+          if (npred > 1) pm = max(pm, p1);
+          if (npred > 2) pm = max(pm, p2);
+          if (pm >= first_nd || npred > 3) {
+            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || __ldcg(npos + p) >= 0; };
+            ready = done_at(p0) && (npred < 2 || done_at(p1)) && (npred < 3 || done_at(p2));
+            for (int j = 3; j < npred; ++j) ready = ready && done_at(ext[x_pred + j - 3]);
+          }
+        }
         if (ready) {
           any_ready = true;
           int best = -1, lbest = npriv;
@@ -501,8 +510,6 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
               const int sd = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
               sl.w(SMASK + (sd >> 2)) |= (1u << best) << ((sd & 3) * 8);
             }
-            curw |= 1u << (t & 31);
-            sl.w(DONE + (t >> 5)) = curw;
             verdict = best;
             ++to.completed;
             any_assigned = true;
@@ -512,6 +519,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
           }
         }
       }
+      if (verdict < 0) first_nd = min(first_nd, (uint32_t)t);
       npos[t] = (int8_t)verdict;
     }
     cur = nxt;
@@ -592,22 +600,22 @@ __device__ __forceinline__ uint32_t apply_evict(const Slab& sl, int PN, int nslo
 }
 
 template <int KMAX>
-__global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+__global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
                                                                 int nw_done, int nw_pn) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX]; words done[nw_done], pnode[nw_pn], cnt[KMAX], curs[KMAX]
+  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX]; words pnode[nw_pn], cnt[KMAX], curs[KMAX]
   constexpr int kD = 3 * KMAX;
-  const int kW = nw_done + nw_pn + 2 * KMAX;
+  const int kW = nw_pn + 2 * KMAX;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
   sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
   // HCNT[k] = len(node.completed_tasks) * 0.5 kept as a double: every += 0.5 is exact (ref schedulers.py:498)
-  const int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, DONE = 0, PN = nw_done, CNT = nw_done + nw_pn, CURS = CNT + KMAX;
+  const int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, PN = 0, CNT = nw_pn, CURS = CNT + KMAX;
 
-  const int inst = blockIdx.x * kTPB + threadIdx.x;
+  const int inst = blockIdx.x * kTPBM + threadIdx.x;
   const bool have = inst < b.B;
   Inst v;
   v.n = 0; v.K = 0; v.topo = 0; v.P = 0; v.t_inst = 0;
@@ -635,7 +643,6 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
     sl.w(CNT + k) = 0;
     sl.w(CURS + k) = (uint32_t)nslots;  // low half: lower bound of the node's first cached slot; high half: #cached
   }
-  for (int x = 0; x < nw_done; ++x) sl.w(DONE + x) = 0;
   for (int x = 0; x < nw_pn; ++x) sl.w(PN + x) = 0xffffffffu;
 
   ThreadOut to;
@@ -644,7 +651,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
   to.fail_rest = false;
   int carried = 0;
   bool running = elig, any_ready = false, any_assigned = false;
-  uint32_t curw = 0, xpos = 0;
+  uint32_t first_nd = 0xffffffffu, xpos = 0;
   RecRegs cur;
   cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
   if (n > 0) cur = load_rec(rec);
@@ -657,7 +664,6 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
       const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
       const int npred = cur.hi.y >> 16, npar = cur.hi.w & 0xffff;
       const int flags = cur.hi.w >> 24;
-      if ((t & 31) == 0) curw = 0;
       if (flags & kRecFirst) {
         if (t > 0 && running) {
           if (!any_ready) running = false;
@@ -669,12 +675,21 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
       const uint32_t x_pred = xpos, x_par = xpos + (uint32_t)max(0, npred - 3);
       xpos = x_par + (uint32_t)max(0, npar - 2);
       if (running) {
-        auto done_bit = [&](uint32_t p) -> uint32_t { return (sl.w(DONE + (p >> 5)) >> (p & 31)) & 1u; };
-        const uint32_t b0 = done_bit(cur.hi.x & 0xffff) | (npred < 1);
-        const uint32_t b1 = done_bit(cur.hi.x >> 16) | (npred < 2);
-        const uint32_t b2 = done_bit(cur.hi.y & 0xffff) | (npred < 3);
-        bool ready = (b0 & b1 & b2) != 0;
-        for (int j = 3; j < npred; ++j) ready = ready && done_bit(ext[x_pred + j - 3]);
+        // is_task_ready (ref :50-53) without a done-bitmap: every position below `first_nd` is done, so a task
+        // whose dependencies all sit below it is ready with no memory access at all; only after the first failed or
+        // blocked task do the (few) later dependencies get looked up in this thread's own verdict bytes.
+        bool ready = true;
+        if (npred > 0) {
+          const uint32_t p0 = cur.hi.x & 0xffff, p1 = cur.hi.x >> 16, p2 = cur.hi.y & 0xffff;
+          uint32_t pm = p0;
+          if (npred > 1) pm = max(pm, p1);
+          if (npred > 2) pm = max(pm, p2);
+          if (pm >= first_nd || npred > 3) {
+            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || __ldcg(npos + p) >= 0; };
+            ready = done_at(p0) && (npred < 2 || done_at(p1)) && (npred < 3 || done_at(p2));
+            for (int j = 3; j < npred; ++j) ready = ready && done_at(ext[x_pred + j - 3]);
+          }
+        }
         if (ready) {
           any_ready = true;
           // none of the task's (private) params is cached anywhere: params_to_load = npar on every node
@@ -780,8 +795,6 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
                 cu = min(cu, sd);
               }
               sl.w(CURS + best) = cu | (((cw >> 16) + (uint32_t)npar) << 16);  // cursor | params cached on the node
-              curw |= 1u << (t & 31);
-              sl.w(DONE + (t >> 5)) = curw;
               verdict = best;
               ++to.completed;
               any_assigned = true;
@@ -792,6 +805,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_mru_kernel(dls_batch_t b, d
           }
         }
       }
+      if (verdict < 0) first_nd = min(first_nd, (uint32_t)t);
       npos[t] = (int8_t)verdict;
     }
     cur = nxt;
@@ -857,12 +871,12 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
 }
 
 template <int KMAX>
-size_t smem_simple(int nw_done) {
-  return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(nw_done + kSharedCap / 4 + KMAX) * 32 * 4);
+size_t smem_simple(int /*nw_done*/) {
+  return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX) * 32 * 4);
 }
 template <int KMAX>
-size_t smem_mru(int nw_done, int nw_pn) {
-  return (size_t)(kTPB / 32) * ((size_t)3 * KMAX * 32 * 8 + (size_t)(nw_done + nw_pn + 2 * KMAX) * 32 * 4);
+size_t smem_mru(int /*nw_done*/, int nw_pn) {
+  return (size_t)(kTPBM / 32) * ((size_t)3 * KMAX * 32 * 8 + (size_t)(nw_pn + 2 * KMAX) * 32 * 4);
 }
 
 }  // namespace
@@ -929,8 +943,8 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
     sk.kind[slot++] = kStreamCP;
   }
   if (algo_mask & (1 << DLS_ALGO_MRU)) {
-    e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, grid, kTPB, smem_mru<KMAX>(nw_done, nw_pn), ctx, b,
-                    r, w, slot, nw_done, nw_pn);
+    e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, dim3((b.B + kTPBM - 1) / kTPBM), kTPBM,
+                    smem_mru<KMAX>(nw_done, nw_pn), ctx, b, r, w, slot, nw_done, nw_pn);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamMRU;
   }
