@@ -885,9 +885,13 @@ size_t smem_mru(int /*nw_done*/, int nw_pn) {
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit) {
   if (b.K_max > 8) return false;
   if (r && (r->peak || r->cached)) return false;  // extension outputs are produced by the general kernels only
-  const int nw_done = (b.n_max + 31) / 32, nw_pn = (b.P_max + 7) / 8;
-  const size_t need = std::max(smem_simple<8>(nw_done), smem_mru<8>(nw_done, nw_pn));
-  return need <= (size_t)smem_limit / 2 && b.n_max >= 1;  // at least two CTAs (4 warps) per SM
+  return smem_simple<8>(0) <= (size_t)smem_limit / 2 && b.n_max >= 1;
+}
+
+// The streamed MRU kernel keeps 4 bits per param in shared memory: only when a useful number of warps still fits.
+// Otherwise (e.g. the ~10k-param DAGs of config 4) MRU alone stays on the general kernel.
+static bool stream_mru_possible(const dls_batch_t& b) {
+  return smem_mru<8>(0, (b.P_max + 7) / 8) <= (size_t)110 * 1024;
 }
 
 template <class Kern, class... Args>
@@ -907,7 +911,7 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
   int kinds = 0;
   if (algo_mask & 3) kinds |= 1 << kStreamDG;
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
-  if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
+  if ((algo_mask & (1 << DLS_ALGO_MRU)) && stream_mru_possible(b)) kinds |= 1 << kStreamMRU;
   const size_t staged = (size_t)b.n_max * 32 + ((size_t)b.n_max + 1) * sizeof(uint32_t) +
                         (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t) + (size_t)3 * b.n_max * sizeof(uint16_t) + 16;
   if (staged <= 180 * 1024)
@@ -942,7 +946,13 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamCP;
   }
-  if (algo_mask & (1 << DLS_ALGO_MRU)) {
+  if ((algo_mask & (1 << DLS_ALGO_MRU)) && !stream_mru_possible(b)) {
+    // every instance of this slot goes to the general MRU kernel
+    ctx.why = "cudaMemsetAsync(route)";
+    e = cudaMemsetAsync(w.route + (size_t)slot * b.B, 1, (size_t)b.B, ctx.st);
+    if (e != cudaSuccess) return e;
+    sk.kind[slot++] = kStreamMRU;
+  } else if (algo_mask & (1 << DLS_ALGO_MRU)) {
     e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, dim3((b.B + kTPBM - 1) / kTPBM), kTPBM,
                     smem_mru<KMAX>(nw_done, nw_pn), ctx, b, r, w, slot, nw_done, nw_pn);
     if (e != cudaSuccess) return e;
