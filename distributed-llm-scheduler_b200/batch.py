@@ -232,6 +232,33 @@ def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool =
     return result
 
 
+def aggregate(result: BatchResult, group_of=None, n_groups: int = 1) -> Dict[str, np.ndarray]:
+    """Group means of the sweep on the device (ref analyze_results' groupby tables, simulation.py:518-524): returns
+    {field: [A, G] array}. `group_of` is an int array [B] (host or device); makespan and load balance are averaged over
+    instances that completed at least one task, like the reference (`df[df.completed_tasks > 0]`)."""
+    torch = _torch()
+    lib = N.load()
+    dev_batch = result.dev_batch
+    device = dev_batch.device
+    A = len(result.algos)
+    with torch.cuda.device(device):
+        g = None
+        if group_of is not None:
+            g = torch.as_tensor(np.asarray(group_of, np.int32) if not torch.is_tensor(group_of) else group_of,
+                                dtype=torch.int32, device=device)
+        out = torch.empty((A, n_groups, N.AGG_FIELDS), dtype=torch.float64, device=device)
+        stream = torch.cuda.current_stream(device).cuda_stream
+        N.check(lib.dls_aggregate(C.byref(dev_batch.struct), C.byref(result.struct), result.mask,
+                                  None if g is None else g.data_ptr(), n_groups, out.data_ptr(), C.c_void_p(stream)))
+        sums = out.cpu().numpy()
+    cnt = np.maximum(sums[..., 0], 1.0)
+    with_c = np.maximum(sums[..., 7], 1.0)
+    return {"count": sums[..., 0], "completion_rate": sums[..., 1] / cnt, "makespan_all": sums[..., 2] / cnt,
+            "makespan": sums[..., 2] / with_c, "avg_node_utilization": sums[..., 3] / cnt,
+            "load_balance_score": sums[..., 4] / with_c, "param_cache_hits": sums[..., 5],
+            "param_cache_misses": sums[..., 6]}
+
+
 def priorities(batch, device=None):
     """Kernel P alone: returns dict of numpy arrays depth/outdeg/up/order_dg/order_mru/order_cp."""
     torch = _torch()

@@ -308,6 +308,21 @@ int dls_generate_fill(const dls_gen_t* gen, const dls_batch_t* out, void* cuda_s
   return DLS_OK;
 }
 
+int dls_aggregate(const dls_batch_t* batch, const dls_result_t* result, int algo_mask, const int32_t* group_of,
+                  int32_t n_groups, double* out, void* cuda_stream) {
+  int rc = validate(batch, algo_mask, false);
+  if (rc != DLS_OK) return rc;
+  if (!result || !result->summary || !result->fin || !result->cnt || !out || n_groups <= 0)
+    return fail(DLS_ERR_BAD_ARG, "NULL or empty argument in dls_aggregate");
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  cudaError_t e = dls::launch_aggregate(*batch, *result, count_bits(algo_mask & DLS_MASK_ALL), group_of, n_groups, out, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
 /* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
 int dls_set_stream_path(int enabled) {

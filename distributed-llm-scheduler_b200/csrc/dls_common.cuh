@@ -234,6 +234,8 @@ struct LaunchCtx {
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_schedule(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                             LaunchCtx& ctx);
+cudaError_t launch_aggregate(const dls_batch_t& b, const dls_result_t& r, int nslots, const int32_t* group_of, int n_groups,
+                             double* out, LaunchCtx& ctx);
 cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_count, LaunchCtx& ctx);
 cudaError_t launch_gen_fill(const dls_gen_t& g, const dls_batch_t& out, LaunchCtx& ctx);
 cudaError_t launch_prep_fused(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);

@@ -227,6 +227,18 @@ typedef struct dls_gen {
 int dls_generate_counts(const dls_gen_t* gen, int32_t* e_count, int32_t* r_count, void* cuda_stream);
 int dls_generate_fill(const dls_gen_t* gen, const dls_batch_t* out, void* cuda_stream);
 
+/*
+ * Sweep-level aggregation on the device (replaces the groupby(...).mean() tables of
+ * analyze_results, simulation.py:452,518-524,552-563). group_of[b] in [0, n_groups) assigns every instance to a group
+ * (e.g. its memory regime); NULL puts all instances in group 0. out[slot][group][DLS_AGG_FIELDS] receives SUMS:
+ *   0 count, 1 completion_rate, 2 makespan, 3 avg_node_utilization, 4 load_balance_score, 5 param_cache_hits,
+ *   6 param_cache_misses, 7 instances with completed_tasks > 0 (the reference averages makespan over those only).
+ * `result` is the device result of a finished or enqueued dls_schedule_batch on the same stream.
+ */
+#define DLS_AGG_FIELDS 8
+int dls_aggregate(const dls_batch_t* batch, const dls_result_t* result, int algo_mask, const int32_t* group_of,
+                  int32_t n_groups, double* out, void* cuda_stream);
+
 /* Test/measurement switch (no reference counterpart). Qualifying batches (K <= 8 nodes, small per-DAG state, no
  * extension outputs requested) normally run on the thread-per-DAG streamed kernels, fed by the priority and
  * stream-build kernels. 0 forces the general warp-per-DAG kernels for everything; 1 restores the default; 2 feeds the

@@ -99,3 +99,35 @@ def test_run_single_test_and_run_experiments_on_gpu():
     # MRU completes every LLM DAG at every regime (ref PDF 5.2.2; hash-order independent: level width <= 4 ties aside)
     llm_mru = df[(df["dag_type"].str.startswith("LLM")) & (df["scheduler_name"] == "MRU_spec")]
     assert (llm_mru["completion_rate"] == 100.0).all()
+
+
+@pytest.mark.gpu
+def test_device_aggregation_matches_groupby():
+    """the per-(scheduler, regime) mean tables of analyze_results computed on the device equal a
+    pandas groupby over the reference's own TestResult metrics (fixture), to 1e-9."""
+    import pandas as pd
+    from dls_b200.batch import aggregate, schedule_batch
+    cases = golden_io.load("cfg2_sweep_seed0.npz")
+    batch = golden_io.batch_of(cases)
+    regimes = [float(c.label.split("|")[2][1:]) for c in cases]
+    levels = sorted(set(regimes))
+    group = np.array([levels.index(x) for x in regimes], np.int32)
+    res = schedule_batch(batch, N.MASK_ALL)
+    agg = aggregate(res, group, len(levels))
+    rows = []
+    for a in range(4):
+        for c, g in zip(cases, group):
+            e = c.exp[a]
+            rows.append({"a": a, "g": int(g), "completion_rate": e["completion_rate"], "makespan": e["makespan"],
+                         "avg_node_utilization": e["avg_node_utilization"], "load_balance_score": e["load_balance_score"],
+                         "completed": e["completed"]})
+    df = pd.DataFrame(rows)
+    m_all = df.groupby(["a", "g"])[["completion_rate", "avg_node_utilization"]].mean()
+    m_done = df[df["completed"] > 0].groupby(["a", "g"])[["makespan", "load_balance_score"]].mean()
+    for a in range(4):
+        for g in range(len(levels)):
+            assert agg["count"][a, g] == (group == g).sum()
+            for f in ("completion_rate", "avg_node_utilization"):
+                np.testing.assert_allclose(agg[f][a, g], m_all.loc[(a, g), f], rtol=1e-9, err_msg=f)
+            for f in ("makespan", "load_balance_score"):
+                np.testing.assert_allclose(agg[f][a, g], m_done.loc[(a, g), f], rtol=1e-9, err_msg=f)
