@@ -114,6 +114,92 @@ def perturbed_durations(dag: LoweredDag, B: int, eps: float = 0.1, seed: int = 0
     return dag.dur[None, :] * (1.0 + rng.uniform(-eps, eps, (B, dag.n)))
 
 
+def lower_arrays(names, deps, params, mem, dur) -> LoweredDag:
+    """Array-level lowering: task names, dependency index lists, param-name sets, memory and time -> LoweredDag.
+    The tie-break order pi is this process's set order of `names` (as add_task would produce it)."""
+    n = len(names)
+    pos = {nm: r for r, nm in enumerate(set_order(names))}
+    pnames = sorted({p for ps in params for p in ps})
+    pid = {p: i for i, p in enumerate(pnames)}
+    pred_ptr = np.zeros(n + 1, np.uint32)
+    par_ptr = np.zeros(n + 1, np.uint32)
+    pred_ptr[1:] = np.cumsum([len(d) for d in deps])
+    par_ptr[1:] = np.cumsum([len(p) for p in params])
+    return LoweredDag(
+        names=list(names), param_names=pnames, pred_ptr=pred_ptr,
+        pred_idx=np.asarray([j for d in deps for j in d], np.uint16), par_ptr=par_ptr,
+        par_idx=np.asarray([i for ps in params for i in sorted(pid[p] for p in ps)], np.uint16),
+        rank=np.asarray([pos[nm] for nm in names], np.uint16), mem=np.asarray(mem, np.float64),
+        dur=np.asarray(dur, np.float64))
+
+
+def llm_dag(num_layers: int, attention_heads: int = 8, head_cap: int = 4) -> LoweredDag:
+    """generate_llm_dag (ref simulation.py:36-88) straight to arrays; head_cap=4 is the reference's fixed cap (:52),
+    head_cap=205 with 48 layers gives config 4's 9,986-task DAG."""
+    names, deps, params, mem, dur = ["embedding"], [[]], [{"embedding_weights"}], [0.5], [0.1]
+    prev = 0
+    for layer in range(num_layers):
+        heads = []
+        for h in range(min(attention_heads, head_cap)):
+            nm = f"layer_{layer}_attention_head_{h}"
+            heads.append(len(names))
+            names.append(nm); deps.append([prev]); params.append({f"{nm}_weights"}); mem.append(0.2); dur.append(0.05)
+        names.append(f"layer_{layer}_attention_output"); deps.append(heads)
+        params.append({f"layer_{layer}_attention_output_weights"}); mem.append(0.3); dur.append(0.05)
+        names.append(f"layer_{layer}_ffn"); deps.append([len(names) - 2])
+        params.append({f"layer_{layer}_ffn_weights"}); mem.append(0.5); dur.append(0.1)
+        names.append(f"layer_{layer}_output"); deps.append([len(names) - 2]); params.append(set()); mem.append(0.1); dur.append(0.02)
+        prev = len(names) - 1
+    names.append("output"); deps.append([prev]); params.append({"output_weights"}); mem.append(0.3); dur.append(0.05)
+    return lower_arrays(names, deps, params, mem, dur)
+
+
+def pipeline_dag(num_stages: int, width: int = 3) -> LoweredDag:
+    """generate_pipeline_dag (ref simulation.py:117-151) straight to arrays."""
+    names, deps, params, mem, dur = [], [], [], [], []
+    for stage in range(num_stages):
+        prev = [] if stage == 0 else list(range((stage - 1) * width, stage * width))
+        for wk in range(width):
+            names.append(f"stage_{stage}_worker_{wk}"); deps.append(list(prev)); params.append({f"stage_{stage}_params"})
+            mem.append(0.3); dur.append(0.1)
+    names.append("final_output"); deps.append(list(range((num_stages - 1) * width, num_stages * width)))
+    params.append({"output_params"}); mem.append(0.2); dur.append(0.05)
+    return lower_arrays(names, deps, params, mem, dur)
+
+
+def gpt2_dag(n_layer: int = 12, n_embd: int = 768, vocab_size: int = 50257) -> LoweredDag:
+    """The GPT-2 DAG of LLMDAGExtractor.extract_gpt2_dag (ref test_gpt2.py:45-168) from the model's SHAPES alone (no
+    torch module is instantiated): estimate_memory_gb (ref :18-31) is parameter bytes / 1e9 plus, for a module with a
+    `.weight`, prod(weight.shape) * batch * 4 / 1e9, else 0.1. Defaults = gpt2-small: 99 tasks, 75 params."""
+    emb_numel = vocab_size * n_embd
+    embedding_memory = emb_numel * 4 / 1e9 + float(np.prod((vocab_size, n_embd))) * 1 * 4 / 1e9          # model.wte
+    attn_numel = (n_embd * 3 * n_embd + 3 * n_embd) + (n_embd * n_embd + n_embd)                          # c_attn + c_proj
+    attn_memory = attn_numel * 4 / 1e9 + 0.1                                                              # no .weight
+    fc_numel = n_embd * 4 * n_embd + 4 * n_embd
+    ffn_memory = fc_numel * 4 / 1e9 + float(np.prod((n_embd, 4 * n_embd))) * 1 * 4 / 1e9                 # mlp.c_fc (Conv1D)
+    names, deps, params, mem, dur = ["embedding"], [[]], [{"embedding_weights", "position_weights"}], [embedding_memory], [0.1]
+    prev = 0
+    for L in range(n_layer):
+        base = len(names)
+        rows = [
+            (f"layer_{L}_ln1", [prev], {f"layer_{L}_ln1_weights"}, 0.01, 0.01),
+            (f"layer_{L}_attention", [base], {f"layer_{L}_attn_qkv_weights", f"layer_{L}_attn_proj_weights"}, attn_memory, 0.05),
+            (f"layer_{L}_attn_residual", [base + 1, prev], set(), 0.01, 0.01),
+            (f"layer_{L}_ln2", [base + 2], {f"layer_{L}_ln2_weights"}, 0.01, 0.01),
+            (f"layer_{L}_ffn_expand", [base + 3], {f"layer_{L}_ffn_expand_weights"}, ffn_memory, 0.08),
+            (f"layer_{L}_ffn_activation", [base + 4], set(), 0.01, 0.01),
+            (f"layer_{L}_ffn_contract", [base + 5], {f"layer_{L}_ffn_contract_weights"}, ffn_memory, 0.08),
+            (f"layer_{L}_output", [base + 6, base + 2], set(), 0.01, 0.01),
+        ]
+        for nm, d, p, m, c in rows:
+            names.append(nm); deps.append(d); params.append(p); mem.append(m); dur.append(c)
+        prev = base + 7
+    names.append("final_ln"); deps.append([prev]); params.append({"final_ln_weights"}); mem.append(0.01); dur.append(0.01)
+    names.append("output_projection"); deps.append([len(names) - 2]); params.append({"embedding_weights"})
+    mem.append(embedding_memory); dur.append(0.1)
+    return lower_arrays(names, deps, params, mem, dur)
+
+
 def random_dag_batch_device(B: int, n: int, K: int = 8, regime: float = 0.9, seed: int = 0, max_deps: int = 3,
                             device=None, rank: Optional[np.ndarray] = None):
     """Config-5 sweep inputs built ON the GPU by the library's generator kernels (dls_generate_counts/_fill).

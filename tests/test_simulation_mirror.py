@@ -31,6 +31,28 @@ def test_sweep_instances_equal_the_reference_sweep_fixture():
         np.testing.assert_array_equal(spd, c.spd)
 
 
+def test_array_level_builders_equal_object_lowering():
+    """llm / pipeline / GPT-2 builders that emit arrays directly give exactly what lowering the
+    reference-style Task objects gives; the analytic GPT-2 DAG equals the fixture extracted from the real model."""
+    from dls_b200.gen import gpt2_dag, llm_dag, pipeline_dag
+    pairs = [(llm_dag(6, attention_heads=8), lower_tasks(DAGGenerator.generate_llm_dag(6, attention_heads=8))),
+             (llm_dag(3, attention_heads=7, head_cap=7), lower_tasks(DAGGenerator.generate_llm_dag(3, attention_heads=7, head_cap=7))),
+             (pipeline_dag(5, 3), lower_tasks(DAGGenerator.generate_pipeline_dag(5, 3)))]
+    for a, b in pairs:
+        assert a.names == b.names and a.param_names == b.param_names
+        for f in ("pred_ptr", "pred_idx", "par_ptr", "par_idx", "rank", "mem", "dur"):
+            np.testing.assert_array_equal(getattr(a, f), getattr(b, f), err_msg=f)
+    g = gpt2_dag()
+    fx = [c for c in golden_io.load("cfg3_gpt2.npz") if c.label == "gpt2|4laptops"][0].dag
+    assert g.n == 99 and g.P == 75 and g.names == fx.names and g.param_names == fx.param_names
+    for f in ("pred_ptr", "pred_idx", "par_ptr", "par_idx"):
+        np.testing.assert_array_equal(getattr(g, f), getattr(fx, f), err_msg=f)
+    np.testing.assert_array_equal(g.dur, fx.dur)
+    np.testing.assert_array_equal(g.mem.view(np.uint64), fx.mem.view(np.uint64))  # bit-identical memory estimates
+    big = llm_dag(48, attention_heads=205, head_cap=205)
+    assert big.n == 9986 and big.E == 19777
+
+
 @pytest.mark.skipif(not rh.available(), reason="/root/reference not present")
 def test_generators_match_live_reference():
     _, sim = rh.ref_modules()
