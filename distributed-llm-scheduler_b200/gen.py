@@ -108,6 +108,36 @@ def random_dag_batch(B: int, n: int, K: int = 8, regime: float = 0.9, seed: int 
         node_off=off(np.full(B, K, np.int64)), cap=cap.reshape(-1), spd=spd.reshape(-1), dags=None)
 
 
+def random_shared_param_batch(B: int, n: int, K: int, pool: int, regime: float = 0.7, seed: int = 0,
+                              max_deps: int = 4, max_params: int = 3) -> DagBatch:
+    """Random DAGs whose tasks draw 0..max_params params from a pool of `pool` names, so params are SHARED between
+    tasks (pipeline-like pressure: cache hits, evictions with live readiness, rollbacks). Not a reference generator —
+    a fuzzing input for the parity tests; instances are built task by task (small sizes)."""
+    rng = np.random.default_rng(seed)
+    dags, nodes = [], []
+    for _ in range(B):
+        names = [f"task_{i}" for i in range(n)]
+        deps, params = [], []
+        for i in range(n):
+            nd = int(rng.integers(0, min(max_deps, i) + 1))
+            d = rng.choice(i, size=nd, replace=False).tolist() if nd else []
+            if d and rng.random() < 0.15:
+                d.append(d[0])  # duplicate dependency entry (kept with multiplicity, ref schedulers.py:47-48)
+            deps.append(d)
+            npar = int(rng.integers(0, max_params + 1))
+            params.append({f"w{int(x):03d}" for x in rng.choice(pool, size=min(npar, pool), replace=False)})
+        mem = rng.uniform(0.05, 0.6, n)
+        mem[rng.random(n) < 0.05] = 0.0
+        dur = rng.uniform(0.01, 0.2, n)
+        dag = lower_arrays(names, deps, params, mem, dur)
+        total = float((mem + np.array([len(p) for p in params]) * 0.5).max() + dag.P * 0.5)
+        cap = rng.uniform(0.3, 1.7, K) * total * regime / K
+        spd = rng.choice([0.5, 0.8, 1.0, 1.0, 1.2, 1.3], K)  # repeated speeds: ties between nodes
+        dags.append(dag)
+        nodes.append((cap.astype(np.float64), spd.astype(np.float64)))
+    return DagBatch.from_instances(dags, nodes)
+
+
 def perturbed_durations(dag: LoweredDag, B: int, eps: float = 0.1, seed: int = 0) -> np.ndarray:
     """Config 3: dur_i * (1 + e), e ~ U(-eps, eps), one row per instance."""
     rng = np.random.default_rng(seed)

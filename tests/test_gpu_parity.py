@@ -37,6 +37,19 @@ def test_cuda_matches_oracle_random_dags(oracle_mod, n, K, regime, B):
         assert_results_equal(got, want, f"{path} random n={n} K={K} r={regime}")
 
 
+@pytest.mark.parametrize("n,K,pool,regime", [(40, 3, 6, 1.2), (60, 8, 12, 1.5), (30, 2, 3, 1.0), (80, 8, 40, 1.0),
+                                             (50, 17, 10, 2.5), (24, 32, 8, 6.0), (120, 5, 16, 0.9), (60, 8, 12, 0.6)])
+def test_cuda_matches_oracle_shared_params_fuzz(oracle_mod, n, K, pool, regime):
+    """Shared params (cache hits, MRU eviction scores with live readiness, rollbacks), duplicate dependency entries,
+    zero-memory tasks, tied node speeds, up to 32 nodes: every device path against the oracle, bit for bit."""
+    from dls_b200.gen import random_shared_param_batch
+    batch = random_shared_param_batch(96, n, K, pool, regime, seed=n * 7 + K)
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    assert want.summary["failed"].sum() > 0 and want.summary["completed"].sum() > 0   # pressure, but not only failures
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} shared-param fuzz n={n} K={K} pool={pool}")
+
+
 def test_single_algorithm_masks_and_slots(oracle_mod):
     batch = random_dag_batch(16, 200, 8, 0.8, seed=5)
     full = schedule_batch(batch, N.MASK_ALL).host()
