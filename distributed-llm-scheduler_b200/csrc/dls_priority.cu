@@ -60,24 +60,23 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
       return;
     }
     if (n > 0 && (v.pred_ptr[0] != 0 || v.par_ptr[0] != 0 || v.pred_ptr[n] != v.E || v.par_ptr[n] != v.R)) bad = 1;
-    // every load below is independent of the others: unrolled so that a thread has them all in flight at once
-#pragma unroll 8
-    for (int i = tid; i < n; i += blockDim.x) {
-      const uint32_t p0 = v.pred_ptr[i], p1 = v.pred_ptr[i + 1], q0 = v.par_ptr[i], q1 = v.par_ptr[i + 1];
+    // every load below is independent of the others: a thread keeps 8 iterations' worth in flight at once
+    strided_for<8>(n, [&](int i) {
+      const uint32_t p0 = __ldg(v.pred_ptr + i), p1 = __ldg(v.pred_ptr + i + 1);
+      const uint32_t q0 = __ldg(v.par_ptr + i), q1 = __ldg(v.par_ptr + i + 1);
       if (p0 > p1 || q0 > q1 || p1 > v.E) bad = 1;
-      if (v.rank[i] >= n) bad = 1;
+      if (__ldg(v.rank + i) >= n) bad = 1;
       if (stage) s_pptr[i] = p0;
-    }
+    });
     if (stage && tid == 0) s_pptr[n] = v.E;
-#pragma unroll 8
-    for (uint32_t e = tid; e < v.E; e += blockDim.x) {
-      const uint16_t p = v.pred_idx[e];
+    strided_for<8>((int)v.E, [&](int e) {
+      const uint16_t p = __ldg(v.pred_idx + e);
       if (p >= n) bad = 1;
       if (stage) s_pidx[e] = p;
-    }
-#pragma unroll 8
-    for (uint32_t e = tid; e < v.R; e += blockDim.x)
-      if (v.par_idx[e] >= v.P) bad = 1;
+    });
+    strided_for<8>((int)v.R, [&](int e) {
+      if (__ldg(v.par_idx + e) >= v.P) bad = 1;
+    });
     if (__syncthreads_or(bad)) {
       if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
       return;
@@ -97,23 +96,37 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   int sweeps = 0, changed = 0;
   if (!unsorted) {
     if (tid < 32) {
+      // The dependency ids of a chunk do not depend on any depth: they are fetched one chunk ahead into registers,
+      // so the per-chunk critical path is a single round of shared-memory reads of the dependencies' depths.
+      uint32_t nb = 0, q0 = 0, q1 = 0, q2 = 0, neb = 0, nee = 0;
+      auto fetch = [&](int base) {
+        const int i = base + tid;
+        neb = i < n ? pptr[i] : 0;
+        nee = i < n ? pptr[i + 1] : 0;
+        nb = nee - neb;
+        q0 = nb > 0 ? pidx[neb] : 0;
+        q1 = nb > 1 ? pidx[neb + 1] : 0;
+        q2 = nb > 2 ? pidx[neb + 2] : 0;
+      };
+      fetch(0);
       for (int base = 0; base < n; base += 32) {
         const int i = base + tid;
-        const uint32_t eb = i < n ? pptr[i] : 0, ee = i < n ? pptr[i + 1] : 0;
+        const uint32_t np = nb, p0 = q0, p1 = q1, p2 = q2, eb = neb, ee = nee;
+        if (base + 32 < n) fetch(base + 32);
+        const bool inside = (np > 0 && (int)p0 >= base) || (np > 1 && (int)p1 >= base) || (np > 2 && (int)p2 >= base) || np > 3;
+        const bool any_inside = __any_sync(DLS_FULL_MASK, inside);
         bool again;
         do {
           int d = 0;
-          bool inside = false;  // depends on a task of this chunk whose depth may still move
-          for (uint32_t e = eb; e < ee; ++e) {
-            const int p = pidx[e];
-            d = max(d, (int)s_depth[p] + 1);
-            inside |= p >= base;
-          }
+          if (np > 0) d = (int)s_depth[p0] + 1;
+          if (np > 1) d = max(d, (int)s_depth[p1] + 1);
+          if (np > 2) d = max(d, (int)s_depth[p2] + 1);
+          for (uint32_t e = eb + 3; e < ee; ++e) d = max(d, (int)s_depth[pidx[e]] + 1);
           d = min(d, 65535);
           const bool moved = i < n && d != s_depth[i];
           if (moved) s_depth[i] = (uint16_t)d;
           __syncwarp();
-          again = __any_sync(DLS_FULL_MASK, moved && true) && __any_sync(DLS_FULL_MASK, inside);
+          again = any_inside && __any_sync(DLS_FULL_MASK, moved);
         } while (again);
       }
     }
@@ -171,8 +184,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     }
   // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
   __syncthreads();  // the staged CSR (aliased with s_hist / s_ord / s_tmp) is dead from here on
-#pragma unroll 8
-  for (int i = tid; i < n; i += blockDim.x) s_ord[v.rank[i]] = (uint16_t)i;
+  strided_for<8>(n, [&](int i) { s_ord[__ldg(v.rank + i)] = (uint16_t)i; });
   __syncthreads();
   const int maxd = s_maxd, maxdeg = s_maxdeg;
   // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
@@ -235,7 +247,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   if (tid == 0) s_maxd = 0;
   for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
   __syncthreads();
-  for (uint32_t e = tid; e < v.R; e += blockDim.x) atomicAdd(&s_rc[v.par_idx[e]], 1u);
+  strided_for<8>((int)v.R, [&](int e) { atomicAdd(&s_rc[__ldg(v.par_idx + e)], 1u); });
   __syncthreads();
   for (int p = tid; p < P; p += blockDim.x) s_rc[p] = s_rc[p] >= 2 ? 1u : 0u;
   __syncthreads();
@@ -245,11 +257,12 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   if (tid == 0) w.nshared[t] = (int)nsh;
   if (nsh != 0) return;
   int md = 0;
-  for (int i = tid; i < n; i += blockDim.x) {
-    const int d = g_depth[i];
+  strided_for<8>(n, [&](int i) {
+    const int d = __ldg(g_depth + i);
     md = max(md, d);
-    for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) s_ownd[v.par_idx[e]] = (uint16_t)d;
-  }
+    const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
+    for (uint32_t e = qb; e < qe; ++e) s_ownd[__ldg(v.par_idx + e)] = (uint16_t)d;
+  });
   atomicMax(&s_maxd, md);
   for (int p = tid; p < P; p += blockDim.x) s_src[p] = (uint16_t)p;
   __syncthreads();
@@ -288,17 +301,14 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   const bool staged = (use_key || m_sort) && (size_t)4 * (n + 1) + (size_t)2 * E <= (size_t)8 * ((n + 1) & ~1);
   uint32_t* s_sptr = reinterpret_cast<uint32_t*>(s_key);
   uint16_t* s_sidx = reinterpret_cast<uint16_t*>(s_sptr + (n + 1));
-#pragma unroll 8
-  for (int q = tid; q < n; q += blockDim.x) {
-    s_ord[q] = w.order_dg[v.t_topo + q];
-    s_depth[q] = g_depth[q];
-    s_up[q] = v.dur[q];
-  }
+  strided_for<8>(n, [&](int q) {
+    s_ord[q] = __ldg(w.order_dg + v.t_topo + q);
+    s_depth[q] = __ldg(g_depth + q);
+    s_up[q] = __ldg(v.dur + q);
+  });
   if (staged) {
-#pragma unroll 8
-    for (int i = tid; i <= n; i += blockDim.x) s_sptr[i] = succ_ptr[i];
-#pragma unroll 8
-    for (uint32_t e = tid; e < E; e += blockDim.x) s_sidx[e] = succ_idx[e];
+    strided_for<8>(n + 1, [&](int i) { s_sptr[i] = __ldg(succ_ptr + i); });
+    strided_for<8>((int)E, [&](int e) { s_sidx[e] = __ldg(succ_idx + e); });
   }
   const uint32_t* sptr = staged ? s_sptr : succ_ptr;
   const uint16_t* sidx = staged ? s_sidx : succ_idx;
