@@ -95,40 +95,27 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   unsorted = __syncthreads_or(unsorted);
   int sweeps = 0, changed = 0;
   if (!unsorted) {
-    if (tid < 32) {
-      // The dependency ids of a chunk do not depend on any depth: they are fetched one chunk ahead into registers,
-      // so the per-chunk critical path is a single round of shared-memory reads of the dependencies' depths.
-      uint32_t nb = 0, q0 = 0, q1 = 0, q2 = 0, neb = 0, nee = 0;
-      auto fetch = [&](int base) {
-        const int i = base + tid;
-        neb = i < n ? pptr[i] : 0;
-        nee = i < n ? pptr[i + 1] : 0;
-        nb = nee - neb;
-        q0 = nb > 0 ? pidx[neb] : 0;
-        q1 = nb > 1 ? pidx[neb + 1] : 0;
-        q2 = nb > 2 ? pidx[neb + 2] : 0;
-      };
-      fetch(0);
-      for (int base = 0; base < n; base += 32) {
-        const int i = base + tid;
-        const uint32_t np = nb, p0 = q0, p1 = q1, p2 = q2, eb = neb, ee = nee;
-        if (base + 32 < n) fetch(base + 32);
-        const bool inside = (np > 0 && (int)p0 >= base) || (np > 1 && (int)p1 >= base) || (np > 2 && (int)p2 >= base) || np > 3;
-        const bool any_inside = __any_sync(DLS_FULL_MASK, inside);
-        bool again;
-        do {
-          int d = 0;
-          if (np > 0) d = (int)s_depth[p0] + 1;
-          if (np > 1) d = max(d, (int)s_depth[p1] + 1);
-          if (np > 2) d = max(d, (int)s_depth[p2] + 1);
-          for (uint32_t e = eb + 3; e < ee; ++e) d = max(d, (int)s_depth[pidx[e]] + 1);
-          d = min(d, 65535);
-          const bool moved = i < n && d != s_depth[i];
-          if (moved) s_depth[i] = (uint16_t)d;
-          __syncwarp();
-          again = any_inside && __any_sync(DLS_FULL_MASK, moved);
-        } while (again);
-      }
+    // One in-order pass, a CTA-wide chunk of tasks at a time: dependencies below the chunk are final, so a chunk is
+    // repeated only while one of its tasks still depends on another task of the same chunk whose depth moved.
+    for (int base = 0; base < n; base += blockDim.x) {
+      const int i = base + tid;
+      const uint32_t eb = i < n ? pptr[i] : 0, ee = i < n ? pptr[i + 1] : 0, np = ee - eb;
+      const uint32_t p0 = np > 0 ? pidx[eb] : 0, p1 = np > 1 ? pidx[eb + 1] : 0, p2 = np > 2 ? pidx[eb + 2] : 0;
+      const bool inside = (np > 0 && (int)p0 >= base) || (np > 1 && (int)p1 >= base) || (np > 2 && (int)p2 >= base) || np > 3;
+      const int any_inside = __syncthreads_or(inside);
+      int again;
+      do {
+        int d = 0;
+        if (np > 0) d = (int)s_depth[p0] + 1;
+        if (np > 1) d = max(d, (int)s_depth[p1] + 1);
+        if (np > 2) d = max(d, (int)s_depth[p2] + 1);
+        for (uint32_t e = eb + 3; e < ee; ++e) d = max(d, (int)s_depth[pidx[e]] + 1);
+        d = min(d, 65535);
+        const bool moved = i < n && d != s_depth[i];
+        __syncthreads();  // everybody has read this round's depths
+        if (moved) s_depth[i] = (uint16_t)d;
+        again = __syncthreads_or(moved) && any_inside;
+      } while (again);
     }
     __syncthreads();
   } else {
