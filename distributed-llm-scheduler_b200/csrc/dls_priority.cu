@@ -260,6 +260,8 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
 __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key, int m_sort) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
+  __shared__ uint32_t s_part[33];
+  __shared__ double s_red[2 * (kThreadsP / 32)];
   const int inst = blockIdx.x, tid = threadIdx.x;
   Inst v;
   bind_instance(b, inst, v);
@@ -275,6 +277,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   uint32_t* s_lvl = s_lq + m_sort;                                 // [n+2] first position of each level
   uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
   uint16_t* s_depth = s_ord + n_al;                               // [n_al]
+  uint16_t* s_pq = s_depth + n_al;                                // [n_al] (use_key) pi position of each bucketed key
   const uint16_t* g_depth = w.depth + v.t_topo;
   const uint32_t* succ_ptr = w.succ_ptr + v.t_topo + v.topo;
   const uint16_t* succ_idx = w.succ_idx + b.pred_off[v.topo];
@@ -328,38 +331,76 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     __syncthreads();
   }
   // (the last level's barrier separates the staged adjacency from the keys that now overwrite it)
-  for (int i = tid; i < n; i += blockDim.x) {
-    w.up[cp_off + i] = s_up[i];
-    if (use_key || m_sort) s_key[i] = s_up[s_ord[i]];  // keys in pi order inside each level
+  // Within-level stable sort by up desc: ready_tasks.sort(key=critical_path, reverse=True), ref schedulers.py:343.
+  // Position of q inside its level = #{q2: key[q2] > key[q]} + #{q2 < q: key[q2] == key[q]}.
+  if (use_key) {
+    // Counting all pairs of a level costs sum(level^2) compares (a random 1k-task DAG has levels of 250 tasks) and was
+    // half of this kernel. So the levels are first cut into NB value buckets by a monotone function of the key
+    // (an unstable counting sort by (level, bucket): pi positions travel with the keys), and pairs are counted
+    // inside a bucket only. Monotone: a <= b implies bucket(a) <= bucket(b), so buckets never reorder keys.
+    double lo = INFINITY, hi = -INFINITY;
+    for (int i = tid; i < n; i += blockDim.x) {
+      const double u = s_up[i];
+      w.up[cp_off + i] = u;
+      lo = fmin(lo, u);
+      hi = fmax(hi, u);
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      lo = fmin(lo, __shfl_xor_sync(DLS_FULL_MASK, lo, off));
+      hi = fmax(hi, __shfl_xor_sync(DLS_FULL_MASK, hi, off));
+    }
+    if ((tid & 31) == 0) { s_red[2 * (tid >> 5)] = lo; s_red[2 * (tid >> 5) + 1] = hi; }
+    uint32_t* s_hist = s_lvl;  // the level starts are not needed any more: [nlev * NB + 1] <= [n + 2]
+    __syncthreads();
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) { lo = fmin(lo, s_red[2 * k]); hi = fmax(hi, s_red[2 * k + 1]); }
+    const int nlev = maxd + 1;
+    const int NB = max(1, min(64, (n + 1) / nlev));
+    const double scale = hi > lo ? (double)NB / (hi - lo) : 0.0;
+    auto group_of = [&](int d, double u) {
+      const int bk = max(0, min(NB - 1, (int)((u - lo) * scale)));
+      return d * NB + (NB - 1 - bk);  // deeper levels later, larger keys first
+    };
+    const int ngroups = nlev * NB;
+    __syncthreads();  // every warp has read the level starts (maxd) before the histogram reuses them
+    for (int k = tid; k <= ngroups; k += blockDim.x) s_hist[k] = 0;
+    __syncthreads();
+    for (int q = tid; q < n; q += blockDim.x) {
+      const int i = s_ord[q];
+      atomicAdd(&s_hist[group_of(s_depth[i], s_up[i])], 1u);
+    }
+    __syncthreads();
+    block_exclusive_scan(s_hist, ngroups + 1, s_part);
+    for (int q = tid; q < n; q += blockDim.x) {
+      const int i = s_ord[q];
+      const double u = s_up[i];
+      const uint32_t pos = atomicAdd(&s_hist[group_of(s_depth[i], u)], 1u);  // afterwards s_hist[g] = end of group g
+      s_key[pos] = u;
+      s_pq[pos] = (uint16_t)q;
+    }
+    __syncthreads();
+    for (int p = tid; p < n; p += blockDim.x) {
+      const double u = s_key[p];
+      const int q = s_pq[p], i = s_ord[q];
+      const int g = group_of(s_depth[i], u);
+      const int gs = g ? (int)s_hist[g - 1] : 0, ge = (int)s_hist[g];
+      int ahead = 0;
+      for (int p2 = gs; p2 < ge; ++p2) {
+        const double u2 = s_key[p2];
+        ahead += (u2 > u) || (u2 == u && s_pq[p2] < q);
+      }
+      w.order_cp[cp_off + gs + ahead] = (uint16_t)i;
+    }
+    return;
   }
+  for (int i = tid; i < n; i += blockDim.x) w.up[cp_off + i] = s_up[i];
   __syncthreads();
-  // within-level stable sort by up desc: ready_tasks.sort(key=critical_path, reverse=True), ref schedulers.py:343.
-  // Position of q = #{q2 in level: key[q2] > key[q]} + #{q2 < q in level: key[q2] == key[q]}.
   for (int q = tid; q < n; q += blockDim.x) {
     const int i = s_ord[q];
     const int d = s_depth[i];
     const int ls = s_lvl[d], le = s_lvl[d + 1];
     const double u = s_up[i];
     int ahead = 0;
-    if (use_key) {
-      // keys are read as aligned pairs (one 16-byte shared load, broadcast across the warp) and the loops unrolled
-      int q2 = ls;
-      if ((q2 & 1) && q2 < q) { ahead += s_key[q2] >= u; ++q2; }
-#pragma unroll 4
-      for (; q2 + 1 < q; q2 += 2) {
-        const double2 kk = *reinterpret_cast<const double2*>(s_key + q2);
-        ahead += (kk.x >= u) + (kk.y >= u);
-      }
-      for (; q2 < q; ++q2) ahead += s_key[q2] >= u;
-      q2 = q + 1;
-      if ((q2 & 1) && q2 < le) { ahead += s_key[q2] > u; ++q2; }
-#pragma unroll 4
-      for (; q2 + 1 < le; q2 += 2) {
-        const double2 kk = *reinterpret_cast<const double2*>(s_key + q2);
-        ahead += (kk.x > u) + (kk.y > u);
-      }
-      for (; q2 < le; ++q2) ahead += s_key[q2] > u;
-    } else {  // very large DAGs: no room for the second key array
+    {  // very large DAGs: no room for a key array
       for (int q2 = ls; q2 < q; ++q2) ahead += s_up[s_ord[q2]] >= u;
       for (int q2 = q + 1; q2 < le; ++q2) ahead += s_up[s_ord[q2]] > u;
     }
@@ -387,7 +428,7 @@ size_t priority_smem_inst(int n_max, bool with_key) {
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
   const size_t m = with_key ? (size_t)bitonic_size(n_max) : 0;
   const size_t nkey = m ? m : (with_key ? ((n + 1) & ~(size_t)1) : 0);
-  return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (m + n + 2) * sizeof(uint32_t) + 2 * n_al * sizeof(uint16_t);
+  return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (m + n + 2) * sizeof(uint32_t) + (with_key ? 3 : 2) * n_al * sizeof(uint16_t);
 }
 
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
