@@ -338,6 +338,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     // half of this kernel. So the levels are first cut into NB value buckets by a monotone function of the key
     // (an unstable counting sort by (level, bucket): pi positions travel with the keys), and pairs are counted
     // inside a bucket only. Monotone: a <= b implies bucket(a) <= bucket(b), so buckets never reorder keys.
+    // (NaN keys land in some valid bucket; the reference's own order is undefined for them.)
     double lo = INFINITY, hi = -INFINITY;
     for (int i = tid; i < n; i += blockDim.x) {
       const double u = s_up[i];
@@ -355,9 +356,18 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     for (int k = 0; k < (int)(blockDim.x >> 5); ++k) { lo = fmin(lo, s_red[2 * k]); hi = fmax(hi, s_red[2 * k + 1]); }
     const int nlev = maxd + 1;
     const int NB = max(1, min(64, (n + 1) / nlev));
-    const double scale = hi > lo ? (double)NB / (hi - lo) : 0.0;
+    // Buckets are linear in the bit pattern of the key (sign-corrected so that it orders like the value), i.e. roughly
+    // logarithmic in the value: 40 % of the tasks of a random DAG are sinks whose key is just their duration, and a
+    // scale linear in the value put all of them into the lowest three buckets of every level.
+    auto mono = [](double u) -> uint32_t {
+      const long long bits = __double_as_longlong(u + 0.0);  // -0.0 -> +0.0: equal keys must share a bucket
+      const unsigned long long m = bits < 0 ? ~(unsigned long long)bits : ((unsigned long long)bits | 0x8000000000000000ull);
+      return (uint32_t)(m >> 32);
+    };
+    const uint32_t mlo = mono(lo), mhi = mono(hi);
+    const float scale = (float)NB / ((float)(mhi - mlo) + 1.0f);
     auto group_of = [&](int d, double u) {
-      const int bk = max(0, min(NB - 1, (int)((u - lo) * scale)));
+      const int bk = max(0, min(NB - 1, (int)((float)(mono(u) - mlo) * scale)));
       return d * NB + (NB - 1 - bk);  // deeper levels later, larger keys first
     };
     const int ngroups = nlev * NB;
