@@ -22,6 +22,10 @@ namespace dls {
 
 namespace {
 
+// route byte of an (algorithm slot, instance): 0 done here, 1 left to the warp-per-DAG kernel, kRouteFailRest = done and
+// every still-pending task counts as failed, kRouteTwin = done by the DFS launch, whose verdict bytes are the ones to
+// read, kRouteOpen = the DFS launch could not vouch for Greedy, which therefore runs this instance itself.
+constexpr int kRouteGeneral = 1, kRouteFailRest = 2, kRouteTwin = 4, kRouteOpen = 0xFF;
 constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG DFS/Greedy/Critical kernels
 constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp CTAs, 7 instead of 6 warps/SM, are slower)
 constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
@@ -155,16 +159,13 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
   __syncthreads();
   // ---- phase 1: task-order gather (read-only loads, unrolled: a thread keeps several tasks' loads in flight) ----
   int any_ext = 0;
-  for (int kind = 0; kind < 3; ++kind) {
-    if (!((kind_mask >> kind) & 1)) continue;
-    const uint16_t* g_order = kind == kStreamDG ? w.order_dg + v.t_topo
-                            : kind == kStreamMRU ? w.order_mru + v.t_topo
-                                                 : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
-#pragma unroll 4
-    for (int t = tid; t < n; t += blockDim.x) s_order[kind * n + t] = __ldg(g_order + t);
-  }
-#pragma unroll 4
-  for (int i = tid; i < n; i += blockDim.x) {
+  const uint16_t* g_order[3] = {w.order_dg + v.t_topo, w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo),
+                                w.order_mru + v.t_topo};
+  static_assert(kStreamDG == 0 && kStreamCP == 1 && kStreamMRU == 2, "order table follows the stream kinds");
+  strided_for<4>(n, [&](int i) {
+#pragma unroll
+    for (int kind = 0; kind < 3; ++kind)
+      if ((kind_mask >> kind) & 1) s_order[kind * n + i] = __ldg(g_order[kind] + i);
     TaskRec tr;
     tr.m = __ldg(v.mem + i);
     tr.c = __ldg(v.dur + i);
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
     tr.depth = __ldg(depth + i);
     s_task[i] = tr;
     any_ext |= (pe - pb > 3) || (qe - qb > 2);
-  }
+  });
   if (any_ext) s_any_ext = 1;
   __syncthreads();
   const bool ext_needed = s_any_ext != 0;
@@ -301,7 +302,7 @@ struct ThreadOut {
 template <int KMAX>
 __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int slot,
                                               int inst, const Inst& v, const double (&avail)[KMAX], const Slab& sl,
-                                              int fin_base, int cnt_base, const ThreadOut& to) {
+                                              int fin_base, int cnt_base, const ThreadOut& to, int route_or = 0) {
   const int64_t ko = (int64_t)slot * b.nk_inst + v.k_out;
   double mk = 0.0;
   bool any = false;
@@ -327,14 +328,15 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
   s.status = to.status;
   s.reserved = 0;
   r.summary[(int64_t)slot * b.B + inst] = s;
-  w.route[(int64_t)slot * b.B + inst] = to.fail_rest ? 2 : 0;
+  w.route[(int64_t)slot * b.B + inst] = (uint8_t)((to.fail_rest ? kRouteFailRest : 0) | route_or);
 }
 
 // -------------------------------------------------------------------------------------------------------------------
 // DFS / Greedy / Critical, one thread per DAG
 // -------------------------------------------------------------------------------------------------------------------
 template <int ALGO, int KMAX>
-__global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int nw_done) {
+__global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int nw_done,
+                                                       int twin_mode, int twin_slot) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   // slab layout per warp: doubles fin[KMAX], spd[KMAX]; words smask[kSharedCap/4], cnt[KMAX]
@@ -351,15 +353,29 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
   const bool have = inst < b.B;
   Inst v;
   v.n = 0; v.K = 0; v.topo = 0; v.t_inst = 0;
-  bool elig = false;
+  // DFS and Greedy walk the same order, and on a DAG without shared params they are the same function: every param
+  // must be loaded whichever node is taken, so Greedy's (fewest loads, then most memory) is DFS's (most memory), see
+  // the node choice below. The DFS launch (twin_mode 1) then stores its result in Greedy's slot as well, and the Greedy
+  // launch (twin_mode 2) leaves those instances alone. The one case where the two differ even so (no node has more
+  // than -1 available: DFS starts from max_memory = -1, Greedy from the first fitting node) withdraws the offer.
+  bool elig = false, twin_ok = false;
   if (have) {
     bind_instance(b, inst, v);
-    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] <= kSharedCap;
-    if (!elig) w.route[(int64_t)slot * b.B + inst] = 1;
+    bool taken = false;
+    if (twin_mode == 2) {
+      const int rt = w.route[(int64_t)slot * b.B + inst];
+      taken = rt != kRouteOpen && (rt & kRouteTwin);
+    }
+    elig = !taken && w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] <= kSharedCap;
+    if (!elig && !taken) w.route[(int64_t)slot * b.B + inst] = kRouteGeneral;
+    twin_ok = ALGO == DLS_ALGO_DFS && twin_mode == 1 && elig && w.nshared[v.topo] == 0;
   }
   const int n = elig ? v.n : 0, K = v.K;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
-  if (n_warp == 0) return;
+  if (n_warp == 0) {
+    if (have && twin_mode == 1) w.route[(int64_t)twin_slot * b.B + inst] = kRouteOpen;
+    return;
+  }
   constexpr int kind = ALGO == DLS_ALGO_CRITICAL ? kStreamCP : kStreamDG;
   const Rec* rec = w.stream[kind] + v.t_inst;
   const uint16_t* ext = w.ext[kind] + (elig ? ext_offset(b, inst, v) : 0);
@@ -461,6 +477,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
 #pragma unroll
               for (int k = 0; k < KMAX; ++k)
                 if (avail[k] > bv) { bv = avail[k]; best = k; }
+              if constexpr (ALGO == DLS_ALGO_DFS) { if (best < 0) twin_ok = false; }
               if (!(need <= bv)) best = -1;
               a = bv;
             }
@@ -530,7 +547,9 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       else if (any_ready && to.completed + to.failed < n) ++to.rounds;  // one more iteration finds nothing ready
     }
     finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, to);
+    if (twin_ok) finish_thread<KMAX>(b, r, w, twin_slot, inst, v, avail, sl, FIN, CNT, to, kRouteTwin);
   }
+  if (have && twin_mode == 1 && !twin_ok) w.route[(int64_t)twin_slot * b.B + inst] = kRouteOpen;
 }
 
 // -------------------------------------------------------------------------------------------------------------------
@@ -623,7 +642,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   if (have) {
     bind_instance(b, inst, v);
     elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] == 0 && v.P <= nw_pn * 8;
-    if (!elig) w.route[(int64_t)slot * b.B + inst] = 1;
+    if (!elig) w.route[(int64_t)slot * b.B + inst] = kRouteGeneral;
   }
   const int n = elig ? v.n : 0, K = v.K, nslots = v.P;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
@@ -824,6 +843,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
 // -------------------------------------------------------------------------------------------------------------------
 struct SlotKinds {
   int kind[4];
+  int twin[4];  // slot whose verdict bytes a kRouteTwin instance of this slot reads
 };
 
 // grid (ceil(B/4), A): one warp per (instance, algorithm slot). With `staged`, verdicts are scattered into shared
@@ -834,14 +854,15 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   const int inst = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, slot = blockIdx.y;
   if (inst >= b.B) return;
   const int route = w.route[(int64_t)slot * b.B + inst];
-  if (route == 1) return;  // the warp-per-DAG kernel writes this instance
+  if (route == kRouteGeneral) return;  // the warp-per-DAG kernel writes this instance
+  const int src_slot = (route & kRouteTwin) ? sk.twin[slot] : slot;
   const int kind = sk.kind[slot];
   Inst v;
   bind_instance(b, inst, v);
   const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
                         : kind == kStreamMRU ? w.order_mru + v.t_topo
                                              : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
-  const int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  const int8_t* npos = w.node_pos + (int64_t)src_slot * b.nt_inst + v.t_inst;
   int8_t* node_of = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
   uint16_t* seq_pos = r.seq_pos + (int64_t)slot * b.nt_inst + v.t_inst;
   int8_t* s_node = reinterpret_cast<int8_t*>(smem_raw) + (size_t)(threadIdx.x >> 5) * 3 * n_al;
@@ -854,7 +875,7 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
     const unsigned asg = __ballot_sync(DLS_FULL_MASK, verdict >= 0);
     if (t < v.n) {
       const int i = order[t];
-      if (route == 2 && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
+      if ((route & kRouteFailRest) && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
       const uint16_t sq = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
       if (staged) { s_node[i] = (int8_t)verdict; s_seq[i] = sq; }
       else { node_of[i] = (int8_t)verdict; seq_pos[i] = sq; }
@@ -926,23 +947,25 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
   const int nw_done = (b.n_max + 31) / 32, nw_pn = (b.P_max + 7) / 8;
   const dim3 grid((b.B + kTPB - 1) / kTPB);
   int slot = 0;
-  SlotKinds sk = {{0, 0, 0, 0}};
+  SlotKinds sk = {{0, 0, 0, 0}, {0, 1, 2, 3}};
   cudaError_t e = cudaSuccess;
+  const bool twins = (algo_mask & 3) == 3;  // DFS and Greedy both asked for: slots 0 and 1
   if (algo_mask & (1 << DLS_ALGO_DFS)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX>, DLS_KERNEL_STREAM_DFS, grid, kTPB, smem_simple<KMAX>(nw_done),
-                    ctx, b, r, w, slot, nw_done);
+                    ctx, b, r, w, slot, nw_done, twins ? 1 : 0, slot + 1);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_GREEDY)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
-                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done);
+                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done, twins ? 2 : 0, slot - 1);
     if (e != cudaSuccess) return e;
+    sk.twin[slot] = twins ? slot - 1 : slot;
     sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
-                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done);
+                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done, 0, 0);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamCP;
   }

@@ -50,6 +50,28 @@ def test_cuda_matches_oracle_shared_params_fuzz(oracle_mod, n, K, pool, regime):
         assert_results_equal(got, want, f"{path} shared-param fuzz n={n} K={K} pool={pool}")
 
 
+def test_dfs_result_shared_with_greedy_only_where_they_agree(oracle_mod):
+    """On DAGs without shared params the DFS launch stores its result for Greedy too. The one input class where the
+    two differ even there (no node above DFS's max_memory = -1 start, requirements negative enough to "fit":
+    ref schedulers.py:187 vs :267-281) must still come out as the reference's, next to ordinary instances."""
+    batch = random_dag_batch(64, 60, 4, 0.9, seed=3)
+    odd = np.repeat(np.arange(64) % 2 == 1, 4)
+    batch.cap[odd] = -2.0 - (np.arange(odd.sum()) % 3)
+    odd_t = np.repeat(np.arange(64) % 2 == 1, 60)
+    batch.mem[odd_t] -= 6.0
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=4)
+    dfs, greedy = want.summary[N.ALGO_DFS], want.summary[N.ALGO_GREEDY]
+    assert (dfs["completed"][1::2] != greedy["completed"][1::2]).any()      # they do differ here
+    assert (dfs["completed"][0::2] == greedy["completed"][0::2]).all()
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} dfs/greedy twins")
+    for mask in (3, 2, 1, 11):
+        got = schedule_batch(batch, mask).host()
+        for slot, a in enumerate(got.algos):
+            np.testing.assert_array_equal(got.node_of[slot], want.node_of[a])
+            np.testing.assert_array_equal(got.summary[slot], want.summary[a])
+
+
 def test_single_algorithm_masks_and_slots(oracle_mod):
     batch = random_dag_batch(16, 200, 8, 0.8, seed=5)
     full = schedule_batch(batch, N.MASK_ALL).host()
