@@ -87,7 +87,7 @@ STATIC_SCRATCH_BYTES = 32 << 20
 AGG_FIELDS = 8
 AGG_NAMES = ("count", "completion_rate", "makespan", "avg_node_utilization", "load_balance_score",
              "param_cache_hits", "param_cache_misses", "with_completed")
-NUM_KERNELS = 14
+NUM_KERNELS = 13
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -21,7 +21,7 @@ const char* const kKernelNames[DLS_NUM_KERNELS] = {"priority_topology_kernel", "
                                                    "param_class_kernel", "stream_build_kernel",
                                                    "sched_stream_kernel<DFS>", "sched_stream_kernel<Greedy>",
                                                    "sched_stream_kernel<Critical>", "sched_stream_mru_kernel",
-                                                   "unpermute_kernel", "prep_fused_kernel"};
+                                                   "unpermute_kernel"};
 
 int fail(int code, const std::string& msg) {
   g_err = msg;
@@ -35,7 +35,7 @@ struct Layout {
   size_t off_depth, off_outdeg, off_order_dg, off_order_mru, off_order_cp, off_up, off_succ_ptr, off_succ_idx,
       off_status, total;
   // streamed path (present when `stream` is set)
-  size_t off_sid, off_erank, off_nshared, off_stream[3], off_ext[3], off_node_pos, off_route;
+  size_t off_sid, off_nshared, off_stream[3], off_ext[3], off_node_pos, off_route;
   bool stream;
   int cp_per_instance;
 };
@@ -58,13 +58,12 @@ Layout layout_of(const dls_batch_t& b, int algo_mask = DLS_MASK_ALL, bool stream
   L.off_succ_idx = o;  o = align_up(o + (size_t)b.e_total * sizeof(uint16_t));
   L.off_status = o;    o = align_up(o + (size_t)b.T * sizeof(int32_t));
   for (int k = 0; k < 3; ++k) L.off_stream[k] = L.off_ext[k] = 0;
-  L.off_sid = L.off_erank = L.off_nshared = L.off_node_pos = L.off_route = 0;
+  L.off_sid = L.off_nshared = L.off_node_pos = L.off_route = 0;
   if (stream) {
     const size_t np = (size_t)(b.T == 1 ? b.P_max : b.np_inst);
     const size_t next = (size_t)(b.e_total + b.r_total) * (size_t)(b.T == 1 ? b.B : 1);
     const int A = count_bits(algo_mask & DLS_MASK_ALL);
     L.off_sid = o;     o = align_up(o + np * sizeof(uint16_t));
-    L.off_erank = o;   o = align_up(o + np * sizeof(uint16_t));
     L.off_nshared = o; o = align_up(o + (size_t)b.T * sizeof(int32_t));
     const bool need[3] = {(algo_mask & 3) != 0, (algo_mask & (1 << DLS_ALGO_CRITICAL)) != 0,
                           (algo_mask & (1 << DLS_ALGO_MRU)) != 0};
@@ -93,11 +92,10 @@ dls::Workspace carve(void* base, const Layout& L) {
   w.succ_idx = reinterpret_cast<uint16_t*>(p + L.off_succ_idx);
   w.topo_status = reinterpret_cast<int32_t*>(p + L.off_status);
   w.cp_per_instance = L.cp_per_instance;
-  w.par_sid = nullptr; w.erank = nullptr; w.nshared = nullptr; w.node_pos = nullptr; w.route = nullptr;
+  w.par_sid = nullptr; w.nshared = nullptr; w.node_pos = nullptr; w.route = nullptr;
   for (int k = 0; k < 3; ++k) { w.stream[k] = nullptr; w.ext[k] = nullptr; }
   if (L.stream) {
     w.par_sid = reinterpret_cast<uint16_t*>(p + L.off_sid);
-    w.erank = reinterpret_cast<uint16_t*>(p + L.off_erank);
     w.nshared = reinterpret_cast<int32_t*>(p + L.off_nshared);
     for (int k = 0; k < 3; ++k) {
       if (!L.off_stream[k]) continue;
@@ -150,7 +148,6 @@ int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
 }
 
 bool g_stream_enabled = true;
-bool g_fused_enabled = false;  // measured slower than the separate kernels (profiles/r1d_*): 2 CTAs/SM cannot hide its barriers
 
 int cuda_fail(cudaError_t e, const char* why) {
   return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
@@ -210,12 +207,8 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
     e = cudaMemsetAsync(w.topo_status, 0, (size_t)batch->T * sizeof(int32_t), ctx.st);
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(built-in scratch)");
   }
-  if (stream && g_fused_enabled && dls::prep_fused_possible(*batch, lim)) {
-    e = dls::launch_prep_fused(*batch, w, algo_mask, ctx);  // priorities, orders and streams in one shared-memory pass
-  } else {
-    e = dls::launch_priority(*batch, w, algo_mask, ctx);
-    if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
-  }
+  e = dls::launch_priority(*batch, w, algo_mask, ctx);
+  if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
   if (e == cudaSuccess && stream) e = dls::launch_stream_sched(*batch, *result, w, algo_mask, ctx);
   if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
   g_launches += ctx.launches;
@@ -326,9 +319,8 @@ int dls_aggregate(const dls_batch_t* batch, const dls_result_t* result, int algo
 /* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
 int dls_set_stream_path(int enabled) {
-  const int old = !g_stream_enabled ? 0 : (g_fused_enabled ? 2 : 1);
+  const int old = g_stream_enabled ? 1 : 0;
   g_stream_enabled = enabled != 0;
-  g_fused_enabled = enabled == 2;
   return old;
 }
 

@@ -29,7 +29,6 @@ struct Workspace {
   int cp_per_instance;  // order_cp/up indexed per instance (T==B or per-instance durations) or per topology
   // ---- streamed (thread-per-DAG) path; all null when that path is not used ----
   uint16_t* par_sid;    // [np_topo]   dense id of a param shared by >= 2 tasks, 0xFFFF if private to one task
-  uint16_t* erank;      // [np_topo]   MRU eviction order of private params (valid when nshared == 0)
   int32_t* nshared;     // [T]
   struct Rec* stream[3];   // [nt_inst] task records in processing order: 0 DFS/Greedy, 1 Critical, 2 MRU
   uint16_t* ext[3];        // overflow lists (dependencies beyond 3, params beyond 2), e+r entries per instance
@@ -253,8 +252,6 @@ cudaError_t launch_aggregate(const dls_batch_t& b, const dls_result_t& r, int ns
                              double* out, LaunchCtx& ctx);
 cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_count, LaunchCtx& ctx);
 cudaError_t launch_gen_fill(const dls_gen_t& g, const dls_batch_t& out, LaunchCtx& ctx);
-cudaError_t launch_prep_fused(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
-bool prep_fused_possible(const dls_batch_t& b, int smem_limit);
 cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                 LaunchCtx& ctx);

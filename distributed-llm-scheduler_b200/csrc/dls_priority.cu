@@ -206,32 +206,19 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
 
 // Classify params of one topology (one CTA each):
 //   par_sid[p] = dense id among params referenced by >= 2 tasks ("shared"), 0xFFFF for params private to one task;
-//   nshared[t] = number of shared params;
-//   erank[p]   = (only when nshared == 0) position of p in the order (depth of its owner task asc, param id asc).
-// For a private param cached after its owner ran, MRU's eviction score is 0.0 + 1*10 + 100.0/(step - last + 1) with
-// last = owner's round = depth+1 (ref schedulers.py:385-393,514-516) and never a +1000 (its only user is done), so
-// `evictable.sort()` over (score, name) (ref :420) visits such params exactly in erank order: older rounds first
-// (the score is strictly decreasing in step-last for any reachable step count), equal rounds by param id.
+//   nshared[t] = number of shared params.
+// Tasks whose params are all private cost the same on every node (nothing of theirs is ever cached when they are
+// looked at), which is what the thread-per-DAG kernels build their short cuts on.
 __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, Workspace w) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_part[33];
-  __shared__ int s_maxd;
   const int t = blockIdx.x, tid = threadIdx.x;
   Inst v;
   bind_topology(b, t, v);
   if (w.topo_status[t] != DLS_ST_OK) return;
-  const int n = v.n, P = v.P;
-  const int P_al = (P + 3) & ~3;
+  const int P = v.P;
   uint32_t* s_rc = reinterpret_cast<uint32_t*>(smem_raw);             // [P+2]
-  uint32_t* s_hist = s_rc + (P + 2);                                  // [n+2]
-  uint16_t* s_ownd = reinterpret_cast<uint16_t*>(s_hist + (n + 2));   // [P_al]
-  uint16_t* s_src = s_ownd + P_al;                                    // [P_al]
-  uint16_t* s_dst = s_src + P_al;                                     // [P_al]
-  const int64_t p_topo = b.pid_off[t];
-  uint16_t* g_sid = w.par_sid + p_topo;
-  uint16_t* g_erank = w.erank + p_topo;
-  const uint16_t* g_depth = w.depth + v.t_topo;
-  if (tid == 0) s_maxd = 0;
+  uint16_t* g_sid = w.par_sid + b.pid_off[t];
   for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
   __syncthreads();
   strided_for<8>((int)v.R, [&](int e) { atomicAdd(&s_rc[__ldg(v.par_idx + e)], 1u); });
@@ -242,19 +229,6 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   const uint32_t nsh = block_exclusive_scan(s_rc, P + 1, s_part);
   for (int p = tid; p < P; p += blockDim.x) g_sid[p] = (s_rc[p + 1] != s_rc[p]) ? (uint16_t)s_rc[p] : (uint16_t)0xFFFF;
   if (tid == 0) w.nshared[t] = (int)nsh;
-  if (nsh != 0) return;
-  int md = 0;
-  strided_for<8>(n, [&](int i) {
-    const int d = __ldg(g_depth + i);
-    md = max(md, d);
-    const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
-    for (uint32_t e = qb; e < qe; ++e) s_ownd[__ldg(v.par_idx + e)] = (uint16_t)d;
-  });
-  atomicMax(&s_maxd, md);
-  for (int p = tid; p < P; p += blockDim.x) s_src[p] = (uint16_t)p;
-  __syncthreads();
-  stable_counting_sort(s_src, s_dst, P, s_maxd + 1, [&](int p) { return (uint32_t)s_ownd[p]; }, s_hist, n + 2, s_part);
-  for (int q = tid; q < P; q += blockDim.x) g_erank[s_dst[q]] = (uint16_t)q;
 }
 
 __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key, int m_sort) {
@@ -425,9 +399,8 @@ size_t priority_smem_topo(int n_max, int /*E_max*/) {  // the staged dependency 
   return 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
 }
 
-size_t priority_smem_param(int n_max, int P_max) {
-  size_t n = (size_t)n_max, P = (size_t)P_max, P_al = (P + 3) & ~(size_t)3;
-  return (P + 2 + n + 2) * sizeof(uint32_t) + 3 * P_al * sizeof(uint16_t);
+size_t priority_smem_param(int /*n_max*/, int P_max) {
+  return ((size_t)P_max + 2) * sizeof(uint32_t);
 }
 
 // A block-wide bitonic network over (level, up, position) was tried for the Critical order (round 1c): with its

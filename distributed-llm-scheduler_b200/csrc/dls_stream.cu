@@ -56,7 +56,6 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
                                              : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
   const uint16_t* depth = w.depth + v.t_topo;
   const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
-  const uint16_t* erank = w.erank + b.pid_off[v.topo];
   Rec* out = w.stream[kind] + v.t_inst;
   uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
 
@@ -66,9 +65,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
     const int npred = (int)(v.pred_ptr[i + 1] - v.pred_ptr[i]);
     int extra = max(0, npred - 3);
     const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-    if (kind == kStreamMRU) {
-      extra += max(0, (int)(qe - qb) - 2);
-    } else {
+    if (kind != kStreamMRU) {  // (the MRU stream only ever holds DAGs without shared params)
       int nsh = 0;
       for (uint32_t e = qb; e < qe; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
       extra += max(0, nsh - 2);
@@ -95,14 +92,8 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
     const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
     rc.a0 = rc.a1 = 0;
     if (kind == kStreamMRU) {
-      rc.npriv = (uint16_t)(qe - qb);
+      rc.npriv = (uint16_t)(qe - qb);  // all private: the count is all the MRU kernel needs
       rc.nsh = 0;
-      for (uint32_t e = qb; e < qe; ++e) {
-        const uint16_t slot = erank[v.par_idx[e]];
-        if (e - qb == 0) rc.a0 = slot;
-        else if (e - qb == 1) rc.a1 = slot;
-        else ext[xo++] = slot;
-      }
     } else {
       int nsh = 0, npriv = 0;
       for (uint32_t e = qb; e < qe; ++e) {
@@ -131,7 +122,7 @@ struct __align__(16) TaskRec {   // like Rec, but dependencies/params still as t
   double m, c;
   uint16_t pred[3];
   uint16_t npred;
-  uint16_t p0, p1;   // first two param ids
+  uint16_t p0, p1;   // (unused: padding to 32 bytes)
   uint16_t npar;
   uint16_t depth;
 };
@@ -154,7 +145,6 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
   uint16_t* s_order = s_pos + ((n + 1) & ~1);                                // [3][n] the processing orders, staged
   const uint16_t* depth = w.depth + v.t_topo;
   const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
-  const uint16_t* erank = w.erank + b.pid_off[v.topo];
   if (tid == 0) s_any_ext = 0;
   __syncthreads();
   // ---- phase 1: task-order gather (read-only loads, unrolled: a thread keeps several tasks' loads in flight) ----
@@ -176,11 +166,10 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
     tr.pred[0] = pe - pb > 0 ? __ldg(v.pred_idx + pb) : 0;
     tr.pred[1] = pe - pb > 1 ? __ldg(v.pred_idx + pb + 1) : 0;
     tr.pred[2] = pe - pb > 2 ? __ldg(v.pred_idx + pb + 2) : 0;
-    tr.p0 = qe - qb > 0 ? __ldg(v.par_idx + qb) : 0;
-    tr.p1 = qe - qb > 1 ? __ldg(v.par_idx + qb + 1) : 0;
+    tr.p0 = tr.p1 = 0;
     tr.depth = __ldg(depth + i);
     s_task[i] = tr;
-    any_ext |= (pe - pb > 3) || (qe - qb > 2);
+    any_ext |= (pe - pb > 3) || (nsh_topo > 0 && qe - qb > 2);
   });
   if (any_ext) s_any_ext = 1;
   __syncthreads();
@@ -199,9 +188,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
         const int i = order[t];
         const TaskRec& tr = s_task[i];
         int extra = max(0, (int)tr.npred - 3);
-        if (kind == kStreamMRU) {
-          extra += max(0, (int)tr.npar - 2);
-        } else if (nsh_topo > 0) {
+        if (kind != kStreamMRU && nsh_topo > 0) {
           int nsh = 0;
           for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
           extra += max(0, nsh - 2);
@@ -230,16 +217,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
         for (uint32_t e = pb + 3; e < pe; ++e) ext[xo++] = s_pos[v.pred_idx[e]];
       }
       rc.a0 = rc.a1 = 0;
-      if (kind == kStreamMRU) {
-        rc.npriv = tr.npar;
-        rc.nsh = 0;
-        if (tr.npar > 0) rc.a0 = erank[tr.p0];
-        if (tr.npar > 1) rc.a1 = erank[tr.p1];
-        if (tr.npar > 2) {
-          const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-          for (uint32_t e = qb + 2; e < qe; ++e) ext[xo++] = erank[v.par_idx[e]];
-        }
-      } else if (nsh_topo == 0) {
+      if (kind == kStreamMRU || nsh_topo == 0) {
         rc.npriv = tr.npar;
         rc.nsh = 0;
       } else {
@@ -554,36 +532,27 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
 
 // -------------------------------------------------------------------------------------------------------------------
 // MRU for DAGs whose params are all private to one task, one thread per DAG.
-// Node k's cached params are the slots of `pnode` holding k (4 bits per slot, slots in eviction order, 0xF = not
-// cached); evicting = taking the lowest slots that hold k. curs[k] is a lower bound of the first such slot.
-// -------------------------------------------------------------------------------------------------------------------
-template <int KMAX>
-struct MruNodes {
-  double avail[KMAX];
-};
-
-__device__ __forceinline__ uint32_t nibble_eq_mask(uint32_t word, uint32_t k) {
-  // bit 4j+3 set iff nibble j of `word` equals k
-  const uint32_t x = word ^ (k * 0x11111111u);
-  return ~(((x & 0x77777777u) + 0x77777777u) | x) & 0x88888888u;
-}
-
-// evict_params_for_task (ref schedulers.py:404-442) on one node, split in two so that the 32 DAGs of a warp stay
-// converged (measured r1e: ~1.2 evictions per DAG-step under pressure, on different nodes in different lanes; run
-// inline in the node loop, every lane's eviction serialised the whole warp).
 //
-// plan_evict — arithmetic only. The candidates are the node's `ncached` cached params (none belongs to the task:
-// its params are private and not loaded yet), each frees exactly 0.5, and the reference walks them until
-// `freed >= shortage`: it needs j = ceil(shortage / 0.5) of them and succeeds iff j <= ncached. On success the
-// node's available memory goes up by 0.5, j times (ref :429); on failure all ncached are evicted and rolled back,
-// which leaves only the +0.5 / -0.5 rounding trace (ref :438-441). Returns the reference's bool, `j` slots to clear.
-__device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_t& ncached, uint32_t& j) {
-  j = 0;
+// A private param is loaded when its only user is assigned and is never asked for again, so no task ever finds it
+// cached: what MRU's cache does for such a DAG is hold memory until evict_params_for_task frees it, 0.5 per param.
+// Every cached param of the node is a candidate (none is in the task's params_needed), so WHICH ones the
+// (score, name) sort of ref schedulers.py:420 puts first changes node.cached_params but none of the outputs this
+// path produces (verdicts, counters, finish times, available memory): those depend on HOW MANY are cached per node.
+// The kernel therefore keeps one count per node and nothing per param. (The `cached` extension output needs the
+// identities; asking for it selects the warp-per-DAG kernel, which keeps them.) Rounds 1b-1f kept 4 bits per param in
+// shared memory to replay the eviction order: 24 KB per warp, 6 warps per SM, 7 ms per 131k instances.
+// -------------------------------------------------------------------------------------------------------------------
+
+// evict_params_for_task (ref schedulers.py:404-442) on one node, as arithmetic. Each of the node's `ncached` params
+// frees exactly 0.5 and the reference walks them until `freed >= shortage`: it needs j = ceil(shortage / 0.5) of
+// them and succeeds iff j <= ncached. On success the node's available memory goes up by 0.5, j times (ref :429); on
+// failure all ncached are evicted and rolled back, which leaves only the +0.5 / -0.5 rounding trace (ref :438-441).
+__device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_t& ncached) {
   const double shortage = __dsub_rn(need, avail_k);
   if (shortage <= 0.0) return true;
   const double want = ceil(__dmul_rn(shortage, 2.0));  // exact: power-of-two scaling, then ceil
   if (want <= (double)ncached) {
-    j = (uint32_t)want;
+    const uint32_t j = (uint32_t)want;
     for (uint32_t q = 0; q < j; ++q) avail_k = __dadd_rn(avail_k, 0.5);
     ncached -= j;
     return true;
@@ -593,46 +562,20 @@ __device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_
   return false;
 }
 
-// apply_evict — node.cached_params.remove(param) for the `count` lowest slots of node k at or after `cursor`
-// (slot order == sorted (score, name) order, see param_class_kernel). Returns the new cursor.
-__device__ __forceinline__ uint32_t apply_evict(const Slab& sl, int PN, int nslots, uint32_t k, uint32_t count, uint32_t cursor) {
-  const uint32_t nwords = (uint32_t)(nslots + 7) >> 3;
-  uint32_t wd = cursor >> 3, pos = cursor;
-  uint32_t mask = 0xffffffffu << ((cursor & 7) * 4);
-  while (count > 0 && wd < nwords) {
-    uint32_t word = sl.w(PN + wd);
-    uint32_t hits = nibble_eq_mask(word, k) & mask;
-    mask = 0xffffffffu;
-    if (hits) {
-      do {
-        const uint32_t bit = __ffs(hits) - 1;
-        hits &= hits - 1;
-        word |= 0xFu << (bit - 3);
-        pos = (wd << 3) + (bit >> 2) + 1;
-        --count;
-      } while (hits && count > 0);
-      sl.w(PN + wd) = word;
-    }
-    ++wd;
-  }
-  return pos;
-}
-
 template <int KMAX>
-__global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
-                                                                int nw_done, int nw_pn) {
+__global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX]; words pnode[nw_pn], cnt[KMAX], curs[KMAX]
+  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX]; words cnt[KMAX], ncached[KMAX]
   constexpr int kD = 3 * KMAX;
-  const int kW = nw_pn + 2 * KMAX;
+  constexpr int kW = 2 * KMAX;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
   sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
   // HCNT[k] = len(node.completed_tasks) * 0.5 kept as a double: every += 0.5 is exact (ref schedulers.py:498)
-  const int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, PN = 0, CNT = nw_pn, CURS = CNT + KMAX;
+  const int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, CNT = 0, NC = KMAX;
 
   const int inst = blockIdx.x * kTPBM + threadIdx.x;
   const bool have = inst < b.B;
@@ -641,10 +584,10 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   bool elig = false;
   if (have) {
     bind_instance(b, inst, v);
-    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] == 0 && v.P <= nw_pn * 8;
+    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] == 0;
     if (!elig) w.route[(int64_t)slot * b.B + inst] = kRouteGeneral;
   }
-  const int n = elig ? v.n : 0, K = v.K, nslots = v.P;
+  const int n = elig ? v.n : 0, K = v.K;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
   if (n_warp == 0) return;
   const Rec* rec = w.stream[kStreamMRU] + v.t_inst;
@@ -660,9 +603,8 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
     sl.f(SPD + k) = on ? v.spd[k] : 1.0;
     sl.f(HCNT + k) = 0.0;
     sl.w(CNT + k) = 0;
-    sl.w(CURS + k) = (uint32_t)nslots;  // low half: lower bound of the node's first cached slot; high half: #cached
+    sl.w(NC + k) = 0;  // len(node.cached_params)
   }
-  for (int x = 0; x < nw_pn; ++x) sl.w(PN + x) = 0xffffffffu;
 
   ThreadOut to;
   to.completed = to.failed = to.hits = to.misses = to.rounds = 0;
@@ -691,8 +633,8 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
         if (running) { ++to.rounds; any_ready = any_assigned = false; }  // self.time_step += 1 (ref :453)
       }
       int verdict = DLS_TASK_PENDING;
-      const uint32_t x_pred = xpos, x_par = xpos + (uint32_t)max(0, npred - 3);
-      xpos = x_par + (uint32_t)max(0, npar - 2);
+      const uint32_t x_pred = xpos;
+      xpos += (uint32_t)max(0, npred - 3);
       if (running) {
         // is_task_ready (ref :50-53) without a done-bitmap: every position below `first_nd` is done, so a task
         // whose dependencies all sit below it is ready with no memory access at all; only after the first failed or
@@ -718,7 +660,6 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
           for (int k = 0; k < KMAX; ++k) all_fit = all_fit && (k >= K || need <= avail[k]);
           int best = -1;
           double best_score = -INFINITY;
-          unsigned long long pend = 0;  // slots to clear per node (one byte each), filled by the node loop
           if (all_fit) {
             // no memory pressure: score = 0.0 + cached*20 + available_memory - len(completed_tasks)*0.5 with cached == 0
             double hc[KMAX];
@@ -738,18 +679,10 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
                 if (need <= avail[k]) {
                   score = __dadd_rn(score, avail[k]);  // ref :490-491
                 } else {
-                  // evict_params_for_task mutates the node even if another node wins (ref :492): decide and
-                  // account now, clear the slots after the node loop
-                  const uint32_t cw = sl.w(CURS + k);
-                  uint32_t nc = cw >> 16, jk;
-                  const bool ok = plan_evict(need, avail[k], nc, jk);
-                  sl.w(CURS + k) = (cw & 0xffffu) | (nc << 16);
-                  if (jk > 255u) {  // cannot be queued in a byte: clear right away (never seen; keeps the code total)
-                    const uint32_t cu = apply_evict(sl, PN, nslots, k, jk, cw & 0xffffu);
-                    sl.w(CURS + k) = cu | (nc << 16);
-                  } else {
-                    pend |= (unsigned long long)jk << (8 * k);
-                  }
+                  // evict_params_for_task mutates the node even if another node wins (ref :492)
+                  uint32_t nc = sl.w(NC + k);
+                  const bool ok = plan_evict(need, avail[k], nc);
+                  sl.w(NC + k) = nc;
                   if (ok) score = __dadd_rn(score, 5.0);
                   else cand = false;
                 }
@@ -762,28 +695,10 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
           if (best >= 0) {
             a = pick<KMAX>(avail, best);
             if (!(need <= a)) {  // ref :506-507 (only after a rounding mishap in the first eviction)
-              const uint32_t cw = sl.w(CURS + best);
-              uint32_t nc = cw >> 16, jk;
-              plan_evict(need, a, nc, jk);
-              sl.w(CURS + best) = (cw & 0xffffu) | (nc << 16);
-              const uint32_t queued = (uint32_t)(pend >> (8 * best)) & 0xffu;
-              if (queued + jk > 255u) {
-                const uint32_t cu = apply_evict(sl, PN, nslots, (uint32_t)best, queued + jk, cw & 0xffffu);
-                sl.w(CURS + best) = cu | (nc << 16);
-                pend &= ~(0xffull << (8 * best));
-              } else {
-                pend += (unsigned long long)jk << (8 * best);
-              }
+              uint32_t nc = sl.w(NC + best);
+              plan_evict(need, a, nc);
+              sl.w(NC + best) = nc;
             }
-          }
-          // clear the evicted slots: each lane works through its own queue, all lanes run the same scan code
-          while (pend != 0) {
-            const uint32_t k = (uint32_t)(__ffsll((long long)pend) - 1) >> 3;
-            const uint32_t cnt = (uint32_t)(pend >> (8 * k)) & 0xffu;
-            pend &= ~(0xffull << (8 * k));
-            const uint32_t cw = sl.w(CURS + k);
-            const uint32_t cu = apply_evict(sl, PN, nslots, k, cnt, cw & 0xffffu);
-            sl.w(CURS + k) = cu | (cw & 0xffff0000u);
           }
           if (best >= 0) {
             if (need > a) {
@@ -804,16 +719,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
               sl.f(HCNT + best) = __dadd_rn(sl.f(HCNT + best), 0.5);
               sl.w(CNT + best) += 1;
               to.misses += npar;
-              const uint32_t cw = sl.w(CURS + best);
-              uint32_t cu = cw & 0xffffu;
-              for (int j = 0; j < npar; ++j) {
-                const uint32_t sd = j == 0 ? (cur.hi.z & 0xffff) : j == 1 ? (cur.hi.z >> 16) : (uint32_t)ext[x_par + j - 2];
-                const uint32_t sh = (sd & 7) * 4;
-                uint32_t& word = sl.w(PN + (sd >> 3));
-                word = (word & ~(0xFu << sh)) | ((uint32_t)best << sh);  // node.cached_params.add(param)
-                cu = min(cu, sd);
-              }
-              sl.w(CURS + best) = cu | (((cw >> 16) + (uint32_t)npar) << 16);  // cursor | params cached on the node
+              sl.w(NC + best) += (uint32_t)npar;  // node.cached_params.add(param) for each loaded param (ref :90)
               verdict = best;
               ++to.completed;
               any_assigned = true;
@@ -896,8 +802,8 @@ size_t smem_simple(int /*nw_done*/) {
   return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX) * 32 * 4);
 }
 template <int KMAX>
-size_t smem_mru(int /*nw_done*/, int nw_pn) {
-  return (size_t)(kTPBM / 32) * ((size_t)3 * KMAX * 32 * 8 + (size_t)(nw_pn + 2 * KMAX) * 32 * 4);
+size_t smem_mru() {
+  return (size_t)(kTPBM / 32) * ((size_t)3 * KMAX * 32 * 8 + (size_t)(2 * KMAX) * 32 * 4);
 }
 
 }  // namespace
@@ -907,12 +813,6 @@ bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_
   if (b.K_max > 8) return false;
   if (r && (r->peak || r->cached)) return false;  // extension outputs are produced by the general kernels only
   return smem_simple<8>(0) <= (size_t)smem_limit / 2 && b.n_max >= 1;
-}
-
-// The streamed MRU kernel keeps 4 bits per param in shared memory: only when a useful number of warps still fits.
-// Otherwise (e.g. the ~10k-param DAGs of config 4) MRU alone stays on the general kernel.
-static bool stream_mru_possible(const dls_batch_t& b) {
-  return smem_mru<8>(0, (b.P_max + 7) / 8) <= (size_t)110 * 1024;
 }
 
 template <class Kern, class... Args>
@@ -932,7 +832,7 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
   int kinds = 0;
   if (algo_mask & 3) kinds |= 1 << kStreamDG;
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
-  if ((algo_mask & (1 << DLS_ALGO_MRU)) && stream_mru_possible(b)) kinds |= 1 << kStreamMRU;
+  if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
   const size_t staged = (size_t)b.n_max * 32 + ((size_t)b.n_max + 1) * sizeof(uint32_t) +
                         (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t) + (size_t)3 * b.n_max * sizeof(uint16_t) + 16;
   if (staged <= 180 * 1024)
@@ -944,7 +844,7 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
 template <int KMAX>
 static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                          LaunchCtx& ctx) {
-  const int nw_done = (b.n_max + 31) / 32, nw_pn = (b.P_max + 7) / 8;
+  const int nw_done = (b.n_max + 31) / 32;
   const dim3 grid((b.B + kTPB - 1) / kTPB);
   int slot = 0;
   SlotKinds sk = {{0, 0, 0, 0}, {0, 1, 2, 3}};
@@ -969,15 +869,9 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamCP;
   }
-  if ((algo_mask & (1 << DLS_ALGO_MRU)) && !stream_mru_possible(b)) {
-    // every instance of this slot goes to the general MRU kernel
-    ctx.why = "cudaMemsetAsync(route)";
-    e = cudaMemsetAsync(w.route + (size_t)slot * b.B, 1, (size_t)b.B, ctx.st);
-    if (e != cudaSuccess) return e;
-    sk.kind[slot++] = kStreamMRU;
-  } else if (algo_mask & (1 << DLS_ALGO_MRU)) {
+  if (algo_mask & (1 << DLS_ALGO_MRU)) {
     e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, dim3((b.B + kTPBM - 1) / kTPBM), kTPBM,
-                    smem_mru<KMAX>(nw_done, nw_pn), ctx, b, r, w, slot, nw_done, nw_pn);
+                    smem_mru<KMAX>(), ctx, b, r, w, slot);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamMRU;
   }

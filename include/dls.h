@@ -241,9 +241,8 @@ int dls_aggregate(const dls_batch_t* batch, const dls_result_t* result, int algo
 
 /* Test/measurement switch (no reference counterpart). Qualifying batches (K <= 8 nodes, small per-DAG state, no
  * extension outputs requested) normally run on the thread-per-DAG streamed kernels, fed by the priority and
- * stream-build kernels. 0 forces the general warp-per-DAG kernels for everything; 1 restores the default; 2 feeds the
- * streamed kernels from the single fused preparation kernel instead (same results; measured slower on B200, kept
- * for comparison). Returns the previous setting (0, 1 or 2). */
+ * stream-build kernels. 0 forces the general warp-per-DAG kernels for everything; any other value restores the
+ * default. Returns the previous setting (0 or 1). */
 int dls_set_stream_path(int enabled);
 
 /* Number of kernel launches the library has enqueued since load (for bench accounting). */
@@ -266,8 +265,7 @@ int64_t dls_launch_count(void);
 #define DLS_KERNEL_STREAM_CRITICAL 10
 #define DLS_KERNEL_STREAM_MRU 11
 #define DLS_KERNEL_UNPERMUTE 12
-#define DLS_KERNEL_PREP_FUSED 13
-#define DLS_NUM_KERNELS 14
+#define DLS_NUM_KERNELS 13
 int dls_profile_enable(int on);
 int dls_profile_read(double* ms_per_kernel, int64_t* launches_per_kernel);
 const char* dls_kernel_name(int kernel_id);
