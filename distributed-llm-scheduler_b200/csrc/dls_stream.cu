@@ -174,6 +174,17 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
   if (any_ext) s_any_ext = 1;
   __syncthreads();
   const bool ext_needed = s_any_ext != 0;
+  // Where each round starts is the same in all three orders (each sorts by depth first). Without ext lists the offset
+  // array is free to hold those starts, which turns "is this the first task of a round" into one lookup.
+  uint16_t* s_lvl = reinterpret_cast<uint16_t*>(s_extoff);
+  if (!ext_needed) {
+    const uint16_t* odg = w.order_dg + v.t_topo;
+    strided_for<4>(n, [&](int t) {
+      const int d = s_task[__ldg(odg + t)].depth;
+      const int dprev = t > 0 ? (int)s_task[__ldg(odg + t - 1)].depth : -1;
+      if (d != dprev) s_lvl[d] = (uint16_t)t;
+    });
+  }
   // ---- phase 2: one pass per processing order ----
   for (int kind = 0; kind < 3; ++kind) {
     if (!((kind_mask >> kind) & 1)) continue;
@@ -234,7 +245,8 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
         rc.npriv = (uint16_t)npriv;
         rc.nsh = (uint8_t)min(nsh, 255);
       }
-      rc.flags = (t == 0 || s_task[order[t - 1]].depth != tr.depth) ? kRecFirst : 0;
+      if (ext_needed) rc.flags = (t == 0 || s_task[order[t - 1]].depth != tr.depth) ? kRecFirst : 0;
+      else rc.flags = t == (int)s_lvl[tr.depth] ? kRecFirst : 0;
       out[t] = rc;
     }
   }
