@@ -261,11 +261,46 @@ struct RecRegs {
 __device__ __forceinline__ RecRegs load_rec(const Rec* p) {
   RecRegs r;
   const uint4* q = reinterpret_cast<const uint4*>(p);
-  r.lo = __ldg(q);
-  r.hi = __ldg(q + 1);
+  // L2::128B: a miss in L2 brings in the whole 128-byte line, i.e. this DAG's next three records as well
+  asm volatile("ld.global.nc.L2::128B.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w) : "l"(q));
+  asm volatile("ld.global.nc.L2::128B.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(q + 1));
   return r;
 }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// A thread's verdict bytes (node or DLS_TASK_*) by order position. They leave in aligned words: 32 lanes storing one
+// byte each to 32 different lines cost the L1-to-L2 request path — what bounds these kernels — as much as a record
+// load. The (up to three) positions not yet stored are answered from the register.
+struct VerdictOut {
+  int8_t* base;
+  uint32_t mis, acc;
+  int flushed;  // positions below are in global memory
+  __device__ __forceinline__ void init(int8_t* p) {
+    base = p;
+    mis = (uint32_t)(uintptr_t)p & 3u;
+    acc = 0;
+    flushed = 0;
+  }
+  __device__ __forceinline__ void put(int t, int verdict, bool last) {
+    const uint32_t q = ((uint32_t)t + mis) & 3u;
+    acc |= (uint32_t)(uint8_t)verdict << (8 * q);
+    if (q == 3 || last) {
+      if (q == 3 && t - flushed == 3) {
+        *reinterpret_cast<uint32_t*>(base + t - 3) = acc;
+      } else {
+        for (int p = flushed; p <= t; ++p) base[p] = (int8_t)(acc >> (8 * (((uint32_t)p + mis) & 3u)));
+      }
+      flushed = t + 1;
+      acc = 0;
+    }
+  }
+  __device__ __forceinline__ int get(uint32_t p) const {  // p below the position being decided
+    if ((int)p >= flushed) return (int8_t)(acc >> (8 * ((p + mis) & 3u)));
+    return __ldcg(base + p);
+  }
+};
 
 // Per-warp shared-memory slab: word `wd` of the calling lane.
 struct Slab {
@@ -369,7 +404,8 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
   constexpr int kind = ALGO == DLS_ALGO_CRITICAL ? kStreamCP : kStreamDG;
   const Rec* rec = w.stream[kind] + v.t_inst;
   const uint16_t* ext = w.ext[kind] + (elig ? ext_offset(b, inst, v) : 0);
-  int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  VerdictOut vout;
+  vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
 
   // Node state. avail[k] of a node that does not exist is -inf: it never fits and never wins a max.
   double avail[KMAX];
@@ -413,7 +449,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
   for (int t = 0; t < n_warp; ++t) {
     RecRegs nxt = cur;
     if (t + 1 < n) nxt = load_rec(rec + t + 1);
-    if (t + 8 < n) prefetch_l2(rec + t + 8);
+    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);
     if (t < n) {
       const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
       const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
@@ -442,7 +478,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
           if (npred > 1) pm = max(pm, p1);
           if (npred > 2) pm = max(pm, p2);
           if (pm >= first_nd || npred > 3) {
-            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || __ldcg(npos + p) >= 0; };
+            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || vout.get(p) >= 0; };
             ready = done_at(p0) && (npred < 2 || done_at(p1)) && (npred < 3 || done_at(p2));
             for (int j = 3; j < npred; ++j) ready = ready && done_at(ext[x_pred + j - 3]);
           }
@@ -527,7 +563,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
         }
       }
       if (verdict < 0) first_nd = min(first_nd, (uint32_t)t);
-      npos[t] = (int8_t)verdict;
+      vout.put(t, verdict, t == n - 1);
     }
     cur = nxt;
   }
@@ -604,7 +640,8 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   if (n_warp == 0) return;
   const Rec* rec = w.stream[kStreamMRU] + v.t_inst;
   const uint16_t* ext = w.ext[kStreamMRU] + (elig ? ext_offset(b, inst, v) : 0);
-  int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  VerdictOut vout;
+  vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
 
   double avail[KMAX];  // -inf for nodes that do not exist: they never fit
 #pragma unroll
@@ -631,7 +668,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   for (int t = 0; t < n_warp; ++t) {
     RecRegs nxt = cur;
     if (t + 1 < n) nxt = load_rec(rec + t + 1);
-    if (t + 8 < n) prefetch_l2(rec + t + 8);
+    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);
     if (t < n) {
       const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
       const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
@@ -658,7 +695,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
           if (npred > 1) pm = max(pm, p1);
           if (npred > 2) pm = max(pm, p2);
           if (pm >= first_nd || npred > 3) {
-            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || __ldcg(npos + p) >= 0; };
+            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || vout.get(p) >= 0; };
             ready = done_at(p0) && (npred < 2 || done_at(p1)) && (npred < 3 || done_at(p2));
             for (int j = 3; j < npred; ++j) ready = ready && done_at(ext[x_pred + j - 3]);
           }
@@ -743,7 +780,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
         }
       }
       if (verdict < 0) first_nd = min(first_nd, (uint32_t)t);
-      npos[t] = (int8_t)verdict;
+      vout.put(t, verdict, t == n - 1);
     }
     cur = nxt;
   }
