@@ -262,10 +262,10 @@ __device__ __forceinline__ RecRegs load_rec(const Rec* p) {
   RecRegs r;
   const uint4* q = reinterpret_cast<const uint4*>(p);
   // L2::128B: a miss in L2 brings in the whole 128-byte line, i.e. this DAG's next three records as well
-  asm volatile("ld.global.nc.L2::128B.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w) : "l"(q));
-  asm volatile("ld.global.nc.L2::128B.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(q + 1));
+  // and one 256-bit load instead of two 128-bit ones halves the requests of the 32 lanes, each on its own line
+  asm volatile("ld.global.nc.L2::128B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
+               : "l"(q));
   return r;
 }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
   for (int t = 0; t < n_warp; ++t) {
     RecRegs nxt = cur;
     if (t + 1 < n) nxt = load_rec(rec + t + 1);
-    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);
+    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);  // once per 128-byte line; (measured: of no use to MRU)
     if (t < n) {
       const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
       const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
@@ -668,7 +668,6 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   for (int t = 0; t < n_warp; ++t) {
     RecRegs nxt = cur;
     if (t + 1 < n) nxt = load_rec(rec + t + 1);
-    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);
     if (t < n) {
       const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
       const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
