@@ -21,7 +21,8 @@ namespace {
 
 constexpr int kThreadsP = 128;   // measured r1d: 64 and 256 threads per CTA are both slower for the topology kernel
 
-__global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru, int stage) {
+__global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru, int stage,
+                                                                      int check_params) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_part[33];
   __shared__ int s_maxd, s_maxdeg;
@@ -74,9 +75,11 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
       if (p >= n) bad = 1;
       if (stage) s_pidx[e] = p;
     });
-    strided_for<8>((int)v.R, [&](int e) {
-      if (__ldg(v.par_idx + e) >= v.P) bad = 1;
-    });
+    if (check_params) {  // (with the streamed path on, param_class_kernel checks them as it reads them anyway)
+      strided_for<8>((int)v.R, [&](int e) {
+        if (__ldg(v.par_idx + e) >= v.P) bad = 1;
+      });
+    }
     if (__syncthreads_or(bad)) {
       if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
       return;
@@ -183,6 +186,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     uint32_t* s_deg = s_cnt;  // reuse: out-degree per task
     for (int i = tid; i < n; i += blockDim.x) s_deg[i] = g_outdeg[i];
     __syncthreads();
+    // (one pass on the combined key (depth, degree) needs ~200 x 4 counters and was measured slower than these two)
     if (maxdeg + 2 <= n + 2) {
       stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, n + 2, s_part);
     } else {
@@ -221,8 +225,16 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   uint16_t* g_sid = w.par_sid + b.pid_off[t];
   for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
   __syncthreads();
-  strided_for<8>((int)v.R, [&](int e) { atomicAdd(&s_rc[__ldg(v.par_idx + e)], 1u); });
-  __syncthreads();
+  int bad = 0;
+  strided_for<8>((int)v.R, [&](int e) {
+    const int p = __ldg(v.par_idx + e);
+    if (p < P) atomicAdd(&s_rc[p], 1u);
+    else bad = 1;  // never trust an index that addresses shared memory
+  });
+  if (__syncthreads_or(bad)) {
+    if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
+    return;
+  }
   for (int p = tid; p < P; p += blockDim.x) s_rc[p] = s_rc[p] >= 2 ? 1u : 0u;
   __syncthreads();
   // keep the flags: after the scan, flag[p] = (scan[p+1] != scan[p])
@@ -422,7 +434,8 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
   e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   if (e != cudaSuccess) return e;
   int rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
-  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage);
+  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage,
+                                                            w.par_sid ? 0 : 1);
   if (ctx.prof) ctx.prof->end(rec, ctx.st);
   ++ctx.launches;
   ctx.why = "priority_topology_kernel launch";
