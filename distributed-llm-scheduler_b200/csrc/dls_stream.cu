@@ -797,7 +797,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
 // -------------------------------------------------------------------------------------------------------------------
 struct SlotKinds {
   int kind[4];
-  int twin[4];  // slot whose verdict bytes a kRouteTwin instance of this slot reads
+  int follower[4];  // slot whose kRouteTwin instances take this slot's verdicts (-1: none)
 };
 
 // grid (ceil(B/4), A): one warp per (instance, algorithm slot). With `staged`, verdicts are scattered into shared
@@ -809,16 +809,20 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   if (inst >= b.B) return;
   const int route = w.route[(int64_t)slot * b.B + inst];
   if (route == kRouteGeneral) return;  // the warp-per-DAG kernel writes this instance
-  const int src_slot = (route & kRouteTwin) ? sk.twin[slot] : slot;
+  if (route & kRouteTwin) return;      // written together with the slot it shares its verdicts with, below
+  const int fol = sk.follower[slot];
+  const bool dup = fol >= 0 && (w.route[(int64_t)fol * b.B + inst] & kRouteTwin);
   const int kind = sk.kind[slot];
   Inst v;
   bind_instance(b, inst, v);
   const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
                         : kind == kStreamMRU ? w.order_mru + v.t_topo
                                              : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
-  const int8_t* npos = w.node_pos + (int64_t)src_slot * b.nt_inst + v.t_inst;
+  const int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
   int8_t* node_of = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
   uint16_t* seq_pos = r.seq_pos + (int64_t)slot * b.nt_inst + v.t_inst;
+  int8_t* node_of2 = r.node_of + (int64_t)(dup ? fol : slot) * b.nt_inst + v.t_inst;
+  uint16_t* seq_pos2 = r.seq_pos + (int64_t)(dup ? fol : slot) * b.nt_inst + v.t_inst;
   int8_t* s_node = reinterpret_cast<int8_t*>(smem_raw) + (size_t)(threadIdx.x >> 5) * 3 * n_al;
   uint16_t* s_seq = reinterpret_cast<uint16_t*>(s_node + n_al);
   int base = 0;
@@ -832,15 +836,21 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
       if ((route & kRouteFailRest) && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
       const uint16_t sq = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
       if (staged) { s_node[i] = (int8_t)verdict; s_seq[i] = sq; }
-      else { node_of[i] = (int8_t)verdict; seq_pos[i] = sq; }
+      else {
+        node_of[i] = (int8_t)verdict; seq_pos[i] = sq;
+        if (dup) { node_of2[i] = (int8_t)verdict; seq_pos2[i] = sq; }
+      }
     }
     base += __popc(asg);
   }
   if (staged) {
     __syncwarp();
     for (int i = lane; i < v.n; i += 32) {
-      node_of[i] = s_node[i];
-      seq_pos[i] = s_seq[i];
+      const int8_t nd = s_node[i];
+      const uint16_t sq = s_seq[i];
+      node_of[i] = nd;
+      seq_pos[i] = sq;
+      if (dup) { node_of2[i] = nd; seq_pos2[i] = sq; }
     }
   }
 }
@@ -895,7 +905,7 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
   const int nw_done = (b.n_max + 31) / 32;
   const dim3 grid((b.B + kTPB - 1) / kTPB);
   int slot = 0;
-  SlotKinds sk = {{0, 0, 0, 0}, {0, 1, 2, 3}};
+  SlotKinds sk = {{0, 0, 0, 0}, {-1, -1, -1, -1}};
   cudaError_t e = cudaSuccess;
   const bool twins = (algo_mask & 3) == 3;  // DFS and Greedy both asked for: slots 0 and 1
   if (algo_mask & (1 << DLS_ALGO_DFS)) {
@@ -908,7 +918,7 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
     e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
                     smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done, twins ? 2 : 0, slot - 1);
     if (e != cudaSuccess) return e;
-    sk.twin[slot] = twins ? slot - 1 : slot;
+    if (twins) sk.follower[slot - 1] = slot;
     sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
