@@ -6,6 +6,7 @@
 import csv
 import io
 import json
+import re
 import subprocess
 import sys
 
@@ -39,8 +40,12 @@ def main():
         print(f"   {'-> dram bytes per instance':68s} {(rd + wr) / inst:18.0f}")
         print(f"   {'-> warp instructions per instance':68s} {ins / inst:18.0f}")
         short = name.split("::")[-1].split("(")[0]
-        short = short.replace("<0>", "<DFS>").replace("<1>", "<Greedy>").replace("<2>", "<Critical>")
-        short = short.replace("<(int)0>", "<DFS>").replace("<(int)1>", "<Greedy>").replace("<(int)2>", "<Critical>")
+        # template arguments as ncu prints them -> the names dls_kernel_name() reports
+        m = re.match(r"(sched_(?:stream|simple)_kernel)<(?:\(int\))?([0-3])(?:,\s*(?:\(int\))?\d+)?>", short)
+        if m:
+            short = f"{m.group(1)}<{('DFS', 'Greedy', 'Critical', 'MRU')[int(m.group(2))]}>"
+        short = re.sub(r"^sched_stream_mru_kernel<.*>$", "sched_stream_mru_kernel", short)
+        short = short.replace("stream_build_staged_kernel", "stream_build_kernel")
         traffic[short] = {"dram_bytes_per_instance": (rd + wr) / inst, "warp_inst_per_instance": ins / inst,
                           "instances_in_capture": inst}
     if len(sys.argv) > 3:
