@@ -39,7 +39,7 @@ def main():
         ins = float(r[col["smsp__inst_executed.sum"]])
         print(f"   {'-> dram bytes per instance':68s} {(rd + wr) / inst:18.0f}")
         print(f"   {'-> warp instructions per instance':68s} {ins / inst:18.0f}")
-        short = name.split("::")[-1].split("(")[0]
+        short = name.split("(")[0].split("::")[-1]
         # template arguments as ncu prints them -> the names dls_kernel_name() reports
         m = re.match(r"(sched_(?:stream|simple)_kernel)<(?:\(int\))?([0-3])(?:,\s*(?:\(int\))?\d+)?>", short)
         if m:
