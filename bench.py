@@ -310,6 +310,10 @@ def main():
         "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "traffic": ncu_traffic(dom, B), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
         "kernel_ms": dom_ms, "share_of_step": shares[dom][0] / ksum,
+        # the step as a whole: four schedules per instance, every kernel of the step, against the same peak
+        "step": {"algorithmic_bytes": 4 * algorithmic_bytes(host),
+                 "achieved": 4 * algorithmic_bytes(host) / (ms_total / args.steps * 1e-3) / 1e9,
+                 "frac": 4 * algorithmic_bytes(host) / (ms_total / args.steps * 1e-3) / 1e9 / peak},
         # per kernel: share of the step and, for kernels doing real work, algorithmic GB/s over the measured peak
         # (sched_* kernels of the general path only pick up routed instances here: a few tens of microseconds)
         "kernels": {k: {"ms_per_launch": v[0] / v[1], "share": v[0] / ksum,

@@ -42,7 +42,7 @@ struct __align__(16) Rec {
   double c;          // Task.compute_time
   uint16_t pred[3];  // order positions of the first three dependencies
   uint16_t npred;    // number of dependencies (beyond 3: ext list)
-  uint16_t a0, a1;   // DFS/Greedy/Critical: first two shared-param ids; MRU: eviction-order slots of first two params
+  uint16_t a0, a1;   // first two shared-param ids (0 in the MRU stream, which only holds DAGs without shared params)
   uint16_t npriv;    // DFS/Greedy/Critical: params private to this task; MRU: all params of the task
   uint8_t nsh;       // shared params of the task (beyond 2: ext list); 255 = too many, instance routed to the slow kernel
   uint8_t flags;     // bit0: first task of a round

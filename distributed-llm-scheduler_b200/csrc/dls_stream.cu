@@ -360,7 +360,7 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
 // DFS / Greedy / Critical, one thread per DAG
 // -------------------------------------------------------------------------------------------------------------------
 template <int ALGO, int KMAX>
-__global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot, int nw_done,
+__global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
                                                        int twin_mode, int twin_slot) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -466,8 +466,6 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       const uint32_t x_pred = xpos, x_sh = xpos + (uint32_t)max(0, npred - 3);
       xpos = x_sh + (uint32_t)max(0, nsh - 2);
       if (running) {
-        // is_task_ready (ref :50-53). The done word of the current 32-group is written through on every assignment,
-        // so shared memory is always current; unused dependency slots hold position 0 and are masked by the count.
         // is_task_ready (ref :50-53) without a done-bitmap: every position below `first_nd` is done, so a task
         // whose dependencies all sit below it is ready with no memory access at all; only after the first failed or
         // blocked task do the (few) later dependencies get looked up in this thread's own verdict bytes.
@@ -856,7 +854,7 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
 }
 
 template <int KMAX>
-size_t smem_simple(int /*nw_done*/) {
+size_t smem_simple() {
   return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX) * 32 * 4);
 }
 template <int KMAX>
@@ -870,7 +868,7 @@ size_t smem_mru() {
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit) {
   if (b.K_max > 8) return false;
   if (r && (r->peak || r->cached)) return false;  // extension outputs are produced by the general kernels only
-  return smem_simple<8>(0) <= (size_t)smem_limit / 2 && b.n_max >= 1;
+  return smem_simple<8>() <= (size_t)smem_limit / 2 && b.n_max >= 1;
 }
 
 template <class Kern, class... Args>
@@ -902,28 +900,27 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
 template <int KMAX>
 static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                          LaunchCtx& ctx) {
-  const int nw_done = (b.n_max + 31) / 32;
   const dim3 grid((b.B + kTPB - 1) / kTPB);
   int slot = 0;
   SlotKinds sk = {{0, 0, 0, 0}, {-1, -1, -1, -1}};
   cudaError_t e = cudaSuccess;
   const bool twins = (algo_mask & 3) == 3;  // DFS and Greedy both asked for: slots 0 and 1
   if (algo_mask & (1 << DLS_ALGO_DFS)) {
-    e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX>, DLS_KERNEL_STREAM_DFS, grid, kTPB, smem_simple<KMAX>(nw_done),
-                    ctx, b, r, w, slot, nw_done, twins ? 1 : 0, slot + 1);
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX>, DLS_KERNEL_STREAM_DFS, grid, kTPB, smem_simple<KMAX>(),
+                    ctx, b, r, w, slot, twins ? 1 : 0, slot + 1);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_GREEDY)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
-                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done, twins ? 2 : 0, slot - 1);
+                    smem_simple<KMAX>(), ctx, b, r, w, slot, twins ? 2 : 0, slot - 1);
     if (e != cudaSuccess) return e;
     if (twins) sk.follower[slot - 1] = slot;
     sk.kind[slot++] = kStreamDG;
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
-                    smem_simple<KMAX>(nw_done), ctx, b, r, w, slot, nw_done, 0, 0);
+                    smem_simple<KMAX>(), ctx, b, r, w, slot, 0, 0);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kStreamCP;
   }
