@@ -1,5 +1,9 @@
+#!/usr/bin/env python
+"""Per-kernel CUDA-event times of the scheduling step on device-generated 1k-task DAGs (no e2e leg, no CPU baseline):
+the quick loop used between kernel changes.  python tools/kernel_times.py [instances]"""
+import os
 import sys, time, ctypes as C
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from dls_b200 import _native as N
 from dls_b200.batch import schedule_batch
