@@ -85,6 +85,33 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
       return;
     }
   }
+  // ---- out-degree and reverse CSR (task_dependencies, ref schedulers.py:47-48) ----
+  for (int i = tid; i < n + 2; i += blockDim.x) s_cnt[i] = 0;
+  __syncthreads();
+  for (uint32_t e = tid; e < v.E; e += blockDim.x) atomicAdd(&s_cnt[pidx[e]], 1u);
+  __syncthreads();
+  {
+    int mdg = 0;
+    for (int i = tid; i < n; i += blockDim.x) {
+      g_outdeg[i] = (uint16_t)min(s_cnt[i], 65535u);
+      mdg = max(mdg, (int)min(s_cnt[i], 65535u));
+    }
+    atomicMax(&s_maxdeg, mdg);
+  }
+  __syncthreads();
+  block_exclusive_scan(s_cnt, n + 1, s_part);  // s_cnt[i] = start of i's dependents, s_cnt[n] = E
+  for (int i = tid; i <= n; i += blockDim.x) g_succ_ptr[i] = s_cnt[i];
+  __syncthreads();
+  // (the same walk over (task, dependency) pairs tells whether the tasks are listed in a topological order)
+  int unsorted = 0;
+  for (int i = tid; i < n; i += blockDim.x)
+    for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) {
+      const uint32_t p = pidx[e];
+      unsorted |= (int)p >= i;
+      uint32_t pos = atomicAdd(&s_cnt[p], 1u);  // order inside a list is irrelevant to max() and counts
+      g_succ_idx[pos] = (uint16_t)i;
+    }
+  unsorted = __syncthreads_or(unsorted);
   // ---- depth: relax until a fixed point (<= levels+1 sweeps; more than n+1 sweeps means a cycle) ----
   // The dependency CSR is staged in shared memory once: every sweep walks it again.
   for (int i = tid; i < n; i += blockDim.x) s_depth[i] = 0;
@@ -92,10 +119,6 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   // Tasks are usually listed in a topological order already (every dependency has a smaller index: all of the
   // reference's generators emit them that way). Then one in-order pass by a single warp is exact: a chunk of 32
   // tasks is repeated only while some task of the chunk still depends on another task of the same chunk.
-  int unsorted = 0;
-  for (int i = tid; i < n; i += blockDim.x)
-    for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) unsorted |= pidx[e] >= i;
-  unsorted = __syncthreads_or(unsorted);
   int sweeps = 0, changed = 0;
   if (!unsorted) {
     // One in-order pass, a CTA-wide chunk of tasks at a time: dependencies below the chunk are final, so a chunk is
@@ -150,28 +173,6 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     }
     atomicMax(&s_maxd, md);
   }
-  // ---- out-degree and reverse CSR (task_dependencies, ref schedulers.py:47-48) ----
-  for (int i = tid; i < n + 2; i += blockDim.x) s_cnt[i] = 0;
-  __syncthreads();
-  for (uint32_t e = tid; e < v.E; e += blockDim.x) atomicAdd(&s_cnt[pidx[e]], 1u);
-  __syncthreads();
-  {
-    int mdg = 0;
-    for (int i = tid; i < n; i += blockDim.x) {
-      g_outdeg[i] = (uint16_t)min(s_cnt[i], 65535u);
-      mdg = max(mdg, (int)min(s_cnt[i], 65535u));
-    }
-    atomicMax(&s_maxdeg, mdg);
-  }
-  __syncthreads();
-  block_exclusive_scan(s_cnt, n + 1, s_part);  // s_cnt[i] = start of i's dependents, s_cnt[n] = E
-  for (int i = tid; i <= n; i += blockDim.x) g_succ_ptr[i] = s_cnt[i];
-  __syncthreads();
-  for (int i = tid; i < n; i += blockDim.x)
-    for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) {
-      uint32_t pos = atomicAdd(&s_cnt[pidx[e]], 1u);  // order inside a list is irrelevant to max() and counts
-      g_succ_idx[pos] = (uint16_t)i;
-    }
   // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
   __syncthreads();  // the staged CSR (aliased with s_hist / s_ord / s_tmp) is dead from here on
   strided_for<8>(n, [&](int i) { s_ord[__ldg(v.rank + i)] = (uint16_t)i; });
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   if (want_mru) {
     // MRU: (depth asc, urgency desc, ready-index asc) — ref schedulers.py:462-475. LSD: urgency first, then depth.
     uint32_t* s_deg = s_cnt;  // reuse: out-degree per task
-    for (int i = tid; i < n; i += blockDim.x) s_deg[i] = g_outdeg[i];
+    strided_for<8>(n, [&](int i) { s_deg[i] = g_outdeg[i]; });
     __syncthreads();
     // (one pass on the combined key (depth, degree) needs ~200 x 4 counters and was measured slower than these two)
     if (maxdeg + 2 <= n + 2) {
