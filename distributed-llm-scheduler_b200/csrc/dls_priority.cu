@@ -380,11 +380,14 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
       const int q = s_pq[p], i = s_ord[q];
       const int g = group_of(s_depth[i], u);
       const int gs = g ? (int)s_hist[g - 1] : 0, ge = (int)s_hist[g];
-      int ahead = 0;
+      int ahead = 0, same = 0;
       for (int p2 = gs; p2 < ge; ++p2) {
         const double u2 = s_key[p2];
-        ahead += (u2 > u) || (u2 == u && s_pq[p2] < q);
+        ahead += u2 > u;
+        same += u2 == u;
       }
+      if (same > 1)  // equal keys (the task itself is one of them) keep their pi order; rare outside the LLM DAGs
+        for (int p2 = gs; p2 < ge; ++p2) ahead += (s_key[p2] == u) && (s_pq[p2] < q);
       w.order_cp[cp_off + gs + ahead] = (uint16_t)i;
     }
     return;
