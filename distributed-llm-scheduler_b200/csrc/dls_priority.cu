@@ -363,14 +363,16 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     __syncthreads();
     for (int q = tid; q < n; q += blockDim.x) {
       const int i = s_ord[q];
-      atomicAdd(&s_hist[group_of(s_depth[i], s_up[i])], 1u);
+      const int g = group_of(s_depth[i], s_up[i]);
+      s_depth[i] = (uint16_t)g;  // the depth is not needed again: from here on this array holds the task's group
+      atomicAdd(&s_hist[g], 1u);
     }
     __syncthreads();
     block_exclusive_scan(s_hist, ngroups + 1, s_part);
     for (int q = tid; q < n; q += blockDim.x) {
       const int i = s_ord[q];
       const double u = s_up[i];
-      const uint32_t pos = atomicAdd(&s_hist[group_of(s_depth[i], u)], 1u);  // afterwards s_hist[g] = end of group g
+      const uint32_t pos = atomicAdd(&s_hist[s_depth[i]], 1u);  // afterwards s_hist[g] = end of group g
       s_key[pos] = u;
       s_pq[pos] = (uint16_t)q;
     }
@@ -378,7 +380,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     for (int p = tid; p < n; p += blockDim.x) {
       const double u = s_key[p];
       const int q = s_pq[p], i = s_ord[q];
-      const int g = group_of(s_depth[i], u);
+      const int g = s_depth[i];
       const int gs = g ? (int)s_hist[g - 1] : 0, ge = (int)s_hist[g];
       int ahead = 0, same = 0;
       for (int p2 = gs; p2 < ge; ++p2) {
