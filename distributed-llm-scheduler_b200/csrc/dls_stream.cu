@@ -118,20 +118,65 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
 // shared memory. Phase 2, per processing order, permutes them through shared memory and writes the stream
 // coalesced. Used when the staged records fit shared memory (n up to ~5.5k); otherwise stream_build_kernel.
 // -------------------------------------------------------------------------------------------------------------------
-struct __align__(16) TaskRec {   // like Rec, but dependencies/params still as task / param ids, plus the depth
+// A task as staged in shared memory, in two 16-byte halves kept in two arrays: with 32-byte records every first half
+// starts on one of only four bank groups, and the gather by processing order ran at 3.5 wavefronts per ideal one
+// (ncu source view, round 1i); 16-byte strides spread the same gather over all eight.
+struct __align__(16) TaskLo {
   double m, c;
+};
+struct __align__(16) TaskHi {  // dependencies still as task ids
   uint16_t pred[3];
   uint16_t npred;
-  uint16_t p0, p1;   // (unused: padding to 32 bytes)
   uint16_t npar;
   uint16_t depth;
+  uint32_t pad;
 };
-static_assert(sizeof(TaskRec) == 32, "TaskRec is 32 bytes");
+struct TaskRec {
+  TaskLo lo;
+  TaskHi hi;
+};
+static_assert(sizeof(TaskLo) == 16 && sizeof(TaskHi) == 16, "two 16-byte halves");
+
+// The record of task `i` (staged as `tr`) for one stream, all but the round flag. `posk`: task -> position in that
+// order; ext lists (dependencies beyond three, shared params beyond two) start at ext[xo].
+__device__ __forceinline__ Rec make_rec(int kind, const TaskRec& tr, int i, const Inst& v, int nsh_topo, const uint16_t* sid,
+                                        const uint16_t* posk, uint16_t* ext, uint32_t xo) {
+  Rec rc;
+  rc.m = tr.lo.m;
+  rc.c = tr.lo.c;
+  rc.npred = tr.hi.npred;
+  rc.pred[0] = posk[tr.hi.pred[0]];  // unused slots hold task 0: a valid index, masked by the count
+  rc.pred[1] = posk[tr.hi.pred[1]];
+  rc.pred[2] = posk[tr.hi.pred[2]];
+  if (tr.hi.npred > 3) {
+    const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
+    for (uint32_t e = pb + 3; e < pe; ++e) ext[xo++] = posk[v.pred_idx[e]];
+  }
+  rc.a0 = rc.a1 = 0;
+  if (kind == kStreamMRU || nsh_topo == 0) {
+    rc.npriv = tr.hi.npar;  // every param private: the count is all the kernels need
+    rc.nsh = 0;
+  } else {
+    int nsh = 0, npriv = 0;
+    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
+    for (uint32_t e = qb; e < qe; ++e) {
+      const uint16_t sd = sid[v.par_idx[e]];
+      if (sd == 0xFFFF) { ++npriv; continue; }
+      if (nsh == 0) rc.a0 = sd;
+      else if (nsh == 1) rc.a1 = sd;
+      else ext[xo++] = sd;
+      ++nsh;
+    }
+    rc.npriv = (uint16_t)npriv;
+    rc.nsh = (uint8_t)min(nsh, 255);
+  }
+  rc.flags = 0;
+  return rc;
+}
 
 __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_batch_t b, Workspace w, int kind_mask) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_part[33];
-  __shared__ int s_any_ext;
   const int inst = blockIdx.x, tid = threadIdx.x;
   Inst v;
   bind_instance(b, inst, v);
@@ -139,26 +184,31 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
   const int n = v.n;
   if (n == 0) return;
   const int nsh_topo = w.nshared[v.topo];
-  TaskRec* s_task = reinterpret_cast<TaskRec*>(smem_raw);                    // [n]
-  uint32_t* s_extoff = reinterpret_cast<uint32_t*>(s_task + n);              // [n+1]
-  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));         // [n]
-  uint16_t* s_order = s_pos + ((n + 1) & ~1);                                // [3][n] the processing orders, staged
+  const int n_al = (n + 1) & ~1;
+  TaskLo* s_lo = reinterpret_cast<TaskLo*>(smem_raw);                        // [n]
+  TaskHi* s_hi = reinterpret_cast<TaskHi*>(s_lo + n);                        // [n]
+  uint32_t* s_extoff = reinterpret_cast<uint32_t*>(s_hi + n);                // [n+1]
+  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));         // [3][n_al] task -> position, per order
+  uint16_t* s_depth = s_pos + 3 * n_al;                                      // [n_al] compact copy for the round starts
   const uint16_t* depth = w.depth + v.t_topo;
   const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
-  if (tid == 0) s_any_ext = 0;
-  __syncthreads();
-  // ---- phase 1: task-order gather (read-only loads, unrolled: a thread keeps several tasks' loads in flight) ----
-  int any_ext = 0;
   const uint16_t* g_order[3] = {w.order_dg + v.t_topo, w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo),
                                 w.order_mru + v.t_topo};
   static_assert(kStreamDG == 0 && kStreamCP == 1 && kStreamMRU == 2, "order table follows the stream kinds");
+  bool use[3];
+#pragma unroll
+  for (int kind = 0; kind < 3; ++kind)  // DAGs the thread-per-DAG kernels leave to the general ones get no stream
+    use[kind] = ((kind_mask >> kind) & 1) && (kind == kStreamMRU ? nsh_topo == 0 : nsh_topo <= kSharedCap);
+  // ---- phase 1: task-order gather (a thread keeps several tasks' loads in flight), and the orders inverted ----
+  int any_ext = 0;
   strided_for<4>(n, [&](int i) {
 #pragma unroll
     for (int kind = 0; kind < 3; ++kind)
-      if ((kind_mask >> kind) & 1) s_order[kind * n + i] = __ldg(g_order[kind] + i);
-    TaskRec tr;
-    tr.m = __ldg(v.mem + i);
-    tr.c = __ldg(v.dur + i);
+      if (use[kind]) s_pos[kind * n_al + __ldg(g_order[kind] + i)] = (uint16_t)i;
+    TaskLo lo;
+    TaskHi tr;
+    lo.m = __ldg(v.mem + i);
+    lo.c = __ldg(v.dur + i);
     const uint32_t pb = __ldg(v.pred_ptr + i), pe = __ldg(v.pred_ptr + i + 1);
     const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
     tr.npred = (uint16_t)min(pe - pb, 65535u);
@@ -166,87 +216,69 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_
     tr.pred[0] = pe - pb > 0 ? __ldg(v.pred_idx + pb) : 0;
     tr.pred[1] = pe - pb > 1 ? __ldg(v.pred_idx + pb + 1) : 0;
     tr.pred[2] = pe - pb > 2 ? __ldg(v.pred_idx + pb + 2) : 0;
-    tr.p0 = tr.p1 = 0;
+    tr.pad = 0;
     tr.depth = __ldg(depth + i);
-    s_task[i] = tr;
+    s_lo[i] = lo;
+    s_hi[i] = tr;
+    s_depth[i] = tr.depth;
     any_ext |= (pe - pb > 3) || (nsh_topo > 0 && qe - qb > 2);
   });
-  if (any_ext) s_any_ext = 1;
-  __syncthreads();
-  const bool ext_needed = s_any_ext != 0;
-  // Where each round starts is the same in all three orders (each sorts by depth first). Without ext lists the offset
-  // array is free to hold those starts, which turns "is this the first task of a round" into one lookup.
-  uint16_t* s_lvl = reinterpret_cast<uint16_t*>(s_extoff);
+  const bool ext_needed = __syncthreads_or(any_ext) != 0;
   if (!ext_needed) {
+    // Where each round starts is the same in all three orders (each sorts by depth first). Without ext lists the
+    // offset array is free to hold those starts: "is this the first task of a round" is one lookup.
+    uint16_t* s_lvl = reinterpret_cast<uint16_t*>(s_extoff);
     const uint16_t* odg = w.order_dg + v.t_topo;
     strided_for<4>(n, [&](int t) {
-      const int d = s_task[__ldg(odg + t)].depth;
-      const int dprev = t > 0 ? (int)s_task[__ldg(odg + t - 1)].depth : -1;
+      const int d = s_depth[__ldg(odg + t)];
+      const int dprev = t > 0 ? (int)s_depth[__ldg(odg + t - 1)] : -1;
       if (d != dprev) s_lvl[d] = (uint16_t)t;
     });
+    __syncthreads();
+    // ---- phase 2: position t of all the orders in one iteration: three independent gathers per thread ----
+    strided_for<2>(n, [&](int t) {
+#pragma unroll
+      for (int kind = 0; kind < 3; ++kind) {
+        if (!use[kind]) continue;
+        const int i = __ldg(g_order[kind] + t);
+        TaskRec tr;
+        tr.lo = s_lo[i];
+        tr.hi = s_hi[i];
+        Rec rc = make_rec(kind, tr, i, v, nsh_topo, sid, s_pos + kind * n_al, w.ext[kind], 0);
+        rc.flags = t == (int)s_lvl[tr.hi.depth] ? kRecFirst : 0;
+        (w.stream[kind] + v.t_inst)[t] = rc;
+      }
+    });
+    return;
   }
-  // ---- phase 2: one pass per processing order ----
+  // Some task carries an ext list: its offset is a prefix sum over the positions of the order, one order at a time.
   for (int kind = 0; kind < 3; ++kind) {
-    if (!((kind_mask >> kind) & 1)) continue;
-    if (kind == kStreamMRU ? nsh_topo != 0 : nsh_topo > kSharedCap) continue;  // routed to the general kernels
-    const uint16_t* order = s_order + kind * n;
+    if (!use[kind]) continue;
+    const uint16_t* order = g_order[kind];
+    const uint16_t* posk = s_pos + kind * n_al;
     Rec* out = w.stream[kind] + v.t_inst;
     uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
-    __syncthreads();  // previous pass is done with s_pos / s_extoff
-    for (int t = tid; t < n; t += blockDim.x) s_pos[order[t]] = (uint16_t)t;
-    if (ext_needed) {
-      for (int t = tid; t < n; t += blockDim.x) {
-        const int i = order[t];
-        const TaskRec& tr = s_task[i];
-        int extra = max(0, (int)tr.npred - 3);
-        if (kind != kStreamMRU && nsh_topo > 0) {
-          int nsh = 0;
-          for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
-          extra += max(0, nsh - 2);
-        }
-        s_extoff[t] = (uint32_t)extra;
-      }
-      if (tid == 0) s_extoff[n] = 0;
-      __syncthreads();
-      block_exclusive_scan(s_extoff, n + 1, s_part);
-    } else {
-      __syncthreads();
-    }
+    __syncthreads();  // the previous order is done with s_extoff
     for (int t = tid; t < n; t += blockDim.x) {
       const int i = order[t];
-      const TaskRec tr = s_task[i];
-      Rec rc;
-      rc.m = tr.m;
-      rc.c = tr.c;
-      rc.npred = tr.npred;
-      rc.pred[0] = s_pos[tr.pred[0]];
-      rc.pred[1] = s_pos[tr.pred[1]];
-      rc.pred[2] = s_pos[tr.pred[2]];
-      uint32_t xo = ext_needed ? s_extoff[t] : 0;
-      if (tr.npred > 3) {
-        const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
-        for (uint32_t e = pb + 3; e < pe; ++e) ext[xo++] = s_pos[v.pred_idx[e]];
+      int extra = max(0, (int)s_hi[i].npred - 3);
+      if (kind != kStreamMRU && nsh_topo > 0) {
+        int nsh = 0;
+        for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
+        extra += max(0, nsh - 2);
       }
-      rc.a0 = rc.a1 = 0;
-      if (kind == kStreamMRU || nsh_topo == 0) {
-        rc.npriv = tr.npar;
-        rc.nsh = 0;
-      } else {
-        int nsh = 0, npriv = 0;
-        const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-        for (uint32_t e = qb; e < qe; ++e) {
-          const uint16_t sd = sid[v.par_idx[e]];
-          if (sd == 0xFFFF) { ++npriv; continue; }
-          if (nsh == 0) rc.a0 = sd;
-          else if (nsh == 1) rc.a1 = sd;
-          else ext[xo++] = sd;
-          ++nsh;
-        }
-        rc.npriv = (uint16_t)npriv;
-        rc.nsh = (uint8_t)min(nsh, 255);
-      }
-      if (ext_needed) rc.flags = (t == 0 || s_task[order[t - 1]].depth != tr.depth) ? kRecFirst : 0;
-      else rc.flags = t == (int)s_lvl[tr.depth] ? kRecFirst : 0;
+      s_extoff[t] = (uint32_t)extra;
+    }
+    if (tid == 0) s_extoff[n] = 0;
+    __syncthreads();
+    block_exclusive_scan(s_extoff, n + 1, s_part);
+    for (int t = tid; t < n; t += blockDim.x) {
+      const int i = order[t];
+      TaskRec tr;
+      tr.lo = s_lo[i];
+      tr.hi = s_hi[i];
+      Rec rc = make_rec(kind, tr, i, v, nsh_topo, sid, posk, ext, s_extoff[t]);
+      rc.flags = (t == 0 || s_depth[order[t - 1]] != tr.hi.depth) ? kRecFirst : 0;
       out[t] = rc;
     }
   }
@@ -890,7 +922,7 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
   if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
   const size_t staged = (size_t)b.n_max * 32 + ((size_t)b.n_max + 1) * sizeof(uint32_t) +
-                        (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t) + (size_t)3 * b.n_max * sizeof(uint16_t) + 16;
+                        4 * (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t) + 16;
   if (staged <= 180 * 1024)
     return launch_fast(stream_build_staged_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B), kBuildThreads, staged, ctx, b, w, kinds);
   const size_t smem = ((size_t)b.n_max + 1) * sizeof(uint32_t) + (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
