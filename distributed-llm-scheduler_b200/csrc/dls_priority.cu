@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     atomicMax(&s_maxdeg, mdg);
   }
   __syncthreads();
-  block_exclusive_scan(s_cnt, n + 1, s_part);  // s_cnt[i] = start of i's dependents, s_cnt[n] = E
+  block_exclusive_scan(s_cnt, n + 1, s_part, false);  // s_cnt[i] = start of i's dependents, s_cnt[n] = E
   for (int i = tid; i <= n; i += blockDim.x) g_succ_ptr[i] = s_cnt[i];
   __syncthreads();
   // (the same walk over (task, dependency) pairs tells whether the tasks are listed in a topological order)
