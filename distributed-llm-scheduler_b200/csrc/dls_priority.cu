@@ -177,6 +177,15 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   __syncthreads();  // the staged CSR (aliased with s_hist / s_ord / s_tmp) is dead from here on
   strided_for<8>(n, [&](int i) { s_ord[__ldg(v.rank + i)] = (uint16_t)i; });
   __syncthreads();
+  {  // rank[] must be a permutation: a repeated value would leave a position of every order unwritten
+    // (a bitmap filled with atomicOr while the ranks are first read was measured slower than this second look)
+    int dup = 0;
+    strided_for<8>(n, [&](int i) { dup |= s_ord[__ldg(v.rank + i)] != i; });
+    if (__syncthreads_or(dup)) {
+      if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
+      return;
+    }
+  }
   const int maxd = s_maxd, maxdeg = s_maxdeg;
   // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
   stable_counting_sort(s_ord, s_tmp, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, n + 2, s_part);
@@ -325,7 +334,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     // half of this kernel. So the levels are first cut into NB value buckets by a monotone function of the key
     // (an unstable counting sort by (level, bucket): pi positions travel with the keys), and pairs are counted
     // inside a bucket only. Monotone: a <= b implies bucket(a) <= bucket(b), so buckets never reorder keys.
-    // (NaN keys land in some valid bucket; the reference's own order is undefined for them.)
+    // (NaN keys: the reference's own order is undefined for them. Here they land in some valid bucket and rank as
+    // -inf among themselves in pi order, so that the result is a permutation whatever the input.)
     double lo = INFINITY, hi = -INFINITY;
     for (int i = tid; i < n; i += blockDim.x) {
       const double u = s_up[i];
@@ -373,7 +383,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
       const int i = s_ord[q];
       const double u = s_up[i];
       const uint32_t pos = atomicAdd(&s_hist[s_depth[i]], 1u);  // afterwards s_hist[g] = end of group g
-      s_key[pos] = u;
+      s_key[pos] = u == u ? u : -INFINITY;  // NaN keys: any total order will do, but it must be one (see below)
       s_pq[pos] = (uint16_t)q;
     }
     __syncthreads();
@@ -400,11 +410,12 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     const int i = s_ord[q];
     const int d = s_depth[i];
     const int ls = s_lvl[d], le = s_lvl[d + 1];
-    const double u = s_up[i];
+    auto key_of = [&](int j) { const double x = s_up[j]; return x == x ? x : -INFINITY; };  // NaN: as above
+    const double u = key_of(i);
     int ahead = 0;
     {  // very large DAGs: no room for a key array
-      for (int q2 = ls; q2 < q; ++q2) ahead += s_up[s_ord[q2]] >= u;
-      for (int q2 = q + 1; q2 < le; ++q2) ahead += s_up[s_ord[q2]] > u;
+      for (int q2 = ls; q2 < q; ++q2) ahead += key_of(s_ord[q2]) >= u;
+      for (int q2 = q + 1; q2 < le; ++q2) ahead += key_of(s_ord[q2]) > u;
     }
     w.order_cp[cp_off + ls + ahead] = (uint16_t)i;
   }

@@ -242,3 +242,28 @@ def test_cycle_is_reported_not_hung():
     res = schedule_batch(batch, N.MASK_ALL).host()
     assert (res.summary["status"] == N.ST_BAD_TOPOLOGY).all()
     assert (res.node_of == N.TASK_PENDING).all()
+
+
+def test_garbage_inputs_are_contained():
+    """Inputs outside the reference's domain must not derail the kernels: a rank[] that is not a permutation is a bad
+    topology (it would leave positions of every processing order unwritten), and NaN durations — for which the
+    reference's own sort order is undefined — still give a processing order that is a permutation, every task a
+    verdict, and no effect on the neighbouring instances of the batch."""
+    good = random_dag_batch(8, 200, 8, 0.9, seed=21)
+    want = schedule_batch(good, N.MASK_ALL).host()
+    bad = random_dag_batch(8, 200, 8, 0.9, seed=21)
+    bad.rank[3 * 200 + 17] = bad.rank[3 * 200 + 18]          # instance 3: repeated rank
+    bad.dur[5 * 200: 6 * 200][::7] = np.nan                  # instance 5: NaN durations
+    for path, got in run_both_paths(bad, N.MASK_ALL):
+        st = got.summary["status"]
+        assert (st[:, 3] == N.ST_BAD_TOPOLOGY).all() and (got.node_of[:, 3 * 200: 4 * 200] == N.TASK_PENDING).all(), path
+        s5 = got.summary[:, 5]
+        assert (s5["status"] == 0).all() and (s5["completed"] + s5["failed"] + s5["pending"] == 200).all(), path
+        for b in (0, 1, 2, 4, 6, 7):
+            np.testing.assert_array_equal(got.node_of[:, b * 200: (b + 1) * 200], want.node_of[:, b * 200: (b + 1) * 200])
+            np.testing.assert_array_equal(got.summary[:, b], want.summary[:, b])
+    prio = priorities(bad)
+    for b in (5,):
+        for name in ("order_dg", "order_cp", "order_mru"):
+            o = prio[name][b * 200: (b + 1) * 200]
+            assert sorted(o.tolist()) == list(range(200)), (name, b)
