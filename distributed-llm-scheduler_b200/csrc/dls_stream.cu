@@ -856,22 +856,32 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   int8_t* s_node = reinterpret_cast<int8_t*>(smem_raw) + (size_t)(threadIdx.x >> 5) * 3 * n_al;
   uint16_t* s_seq = reinterpret_cast<uint16_t*>(s_node + n_al);
   int base = 0;
-  for (int t0 = 0; t0 < v.n; t0 += 32) {
-    const int t = t0 + lane;
-    int verdict = DLS_TASK_PENDING;
-    if (t < v.n) verdict = npos[t];
-    const unsigned asg = __ballot_sync(DLS_FULL_MASK, verdict >= 0);
-    if (t < v.n) {
-      const int i = order[t];
-      if ((route & kRouteFailRest) && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
-      const uint16_t sq = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
-      if (staged) { s_node[i] = (int8_t)verdict; s_seq[i] = sq; }
-      else {
-        node_of[i] = (int8_t)verdict; seq_pos[i] = sq;
-        if (dup) { node_of2[i] = (int8_t)verdict; seq_pos2[i] = sq; }
-      }
+  constexpr int kU = 4;  // chunks of 32 positions whose (independent) loads are issued together
+  for (int t0 = 0; t0 < v.n; t0 += 32 * kU) {
+    int verdicts[kU], tasks[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int t = t0 + 32 * u + lane;
+      verdicts[u] = t < v.n ? (int)npos[t] : DLS_TASK_PENDING;
+      tasks[u] = t < v.n ? (int)order[t] : 0;
     }
-    base += __popc(asg);
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int t = t0 + 32 * u + lane;
+      int verdict = verdicts[u];
+      const unsigned asg = __ballot_sync(DLS_FULL_MASK, verdict >= 0);
+      if (t < v.n) {
+        const int i = tasks[u];
+        if ((route & kRouteFailRest) && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
+        const uint16_t sq = verdict >= 0 ? (uint16_t)(base + __popc(asg & ((1u << lane) - 1u))) : (uint16_t)DLS_SEQ_NONE;
+        if (staged) { s_node[i] = (int8_t)verdict; s_seq[i] = sq; }
+        else {
+          node_of[i] = (int8_t)verdict; seq_pos[i] = sq;
+          if (dup) { node_of2[i] = (int8_t)verdict; seq_pos2[i] = sq; }
+        }
+      }
+      base += __popc(asg);
+    }
   }
   if (staged) {
     __syncwarp();
