@@ -315,10 +315,12 @@ def main():
                  "achieved": 4 * algorithmic_bytes(host) / (ms_total / args.steps * 1e-3) / 1e9,
                  "frac": 4 * algorithmic_bytes(host) / (ms_total / args.steps * 1e-3) / 1e9 / peak},
         # per kernel: share of the step and, for kernels doing real work, algorithmic GB/s over the measured peak
-        # (sched_* kernels of the general path only pick up routed instances here: a few tens of microseconds)
+        # (sched_* kernels of the general path only pick up routed instances here: a few tens of microseconds;
+        # param_class and unpermute touch a fraction of a schedule's bytes: no figure)
         "kernels": {k: {"ms_per_launch": v[0] / v[1], "share": v[0] / ksum,
                         "frac": (((priority_bytes(host) if k.startswith("priority") else algorithmic_bytes(host))
-                                  / (v[0] / v[1] * 1e-3) / 1e9) / peak) if v[0] / ksum > 0.01 else None}
+                                  / (v[0] / v[1] * 1e-3) / 1e9) / peak)
+                        if v[0] / ksum > 0.01 and k.startswith(("priority", "sched_", "stream_build")) else None}
                     for k, v in shares.items()},
     }
     line = {
