@@ -17,6 +17,9 @@ namespace dls {
 
 namespace {
 
+constexpr int kWarpsPerCta = 4;  // instances per CTA of the warp-per-DAG kernels when their shared memory allows
+
+
 struct OutPtrs {
   int8_t* node_of;
   uint16_t* seq_pos;
@@ -103,9 +106,14 @@ __device__ __forceinline__ void apply_assignment(NodeRegs& nd, int params_to_loa
 // DFS / Greedy / Critical
 // ===================================================================================================================
 template <int ALGO>
-__global__ void __launch_bounds__(32) sched_simple_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot) {
-  extern __shared__ __align__(16) uint32_t smem[];
-  const int inst = blockIdx.x, lane = threadIdx.x;
+__global__ void __launch_bounds__(kWarpsPerCta * 32) sched_simple_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+                                                                        int warp_words) {
+  extern __shared__ __align__(16) uint32_t smem_all[];
+  // one WARP per instance; blockDim / 32 of them share a CTA (see launch_one), each with its own slice of shared memory
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + wic;
+  if (inst >= b.B) return;
+  uint32_t* smem = smem_all + (size_t)wic * warp_words;
   if (w.route && w.route[(int64_t)slot * b.B + inst] != 1) return;  // already done by the thread-per-DAG kernel
   Inst v;
   bind_instance(b, inst, v);
@@ -309,9 +317,13 @@ __device__ __forceinline__ void rcnt_add(const MruState& ms, const Inst& v, int 
   __syncwarp();
 }
 
-__global__ void __launch_bounds__(32) sched_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot) {
-  extern __shared__ __align__(16) uint32_t smem[];
-  const int inst = blockIdx.x, lane = threadIdx.x;
+__global__ void __launch_bounds__(kWarpsPerCta * 32) sched_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+                                                                     int warp_words) {
+  extern __shared__ __align__(16) uint32_t smem_all[];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const int inst = blockIdx.x * (blockDim.x >> 5) + wic;
+  if (inst >= b.B) return;
+  uint32_t* smem = smem_all + (size_t)wic * warp_words;
   if (w.route && w.route[(int64_t)slot * b.B + inst] != 1) return;  // already done by the thread-per-DAG kernel
   Inst v;
   bind_instance(b, inst, v);
@@ -521,11 +533,16 @@ size_t sched_smem_mru(int n_max, int P_max, int K_max) {
 template <class Kern>
 static cudaError_t launch_one(Kern kern, int kernel_id, size_t smem, const dls_batch_t& b, const dls_result_t& r,
                               const Workspace& w, int slot, LaunchCtx& ctx) {
+  // Four warps (instances) to a CTA while four slices of shared memory still leave room for several CTAs per SM,
+  // else one. Nothing is shared between the warps; it only makes the grid four times smaller, which is what an
+  // (almost) empty pick-up launch after the thread-per-DAG kernels costs: 0.07 ms per 131k one-warp CTAs.
+  const size_t slice = (smem + 15) & ~(size_t)15;
+  const int wpc = slice * kWarpsPerCta <= 48 * 1024 ? kWarpsPerCta : 1;
   ctx.why = "cudaFuncSetAttribute(sched kernel)";
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * wpc));
   if (e != cudaSuccess) return e;
   int rec = ctx.prof ? ctx.prof->begin(kernel_id, ctx.st) : -1;
-  kern<<<b.B, 32, smem, ctx.st>>>(b, r, w, slot);
+  kern<<<(b.B + wpc - 1) / wpc, 32 * wpc, slice * wpc, ctx.st>>>(b, r, w, slot, (int)(slice / 4));
   if (ctx.prof) ctx.prof->end(rec, ctx.st);
   ++ctx.launches;
   ctx.why = "sched kernel launch";
