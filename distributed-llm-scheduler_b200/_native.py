@@ -81,7 +81,7 @@ class DlsPrio(C.Structure):
 # Every symbol include/dls.h declares; tests check the built library exports all of them.
 EXPORTED_SYMBOLS = (
     "dls_version", "dls_last_error", "dls_workspace_bytes", "dls_schedule_batch", "dls_priorities",
-    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path", "dls_generate_counts", "dls_generate_fill", "dls_aggregate",
+    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path", "dls_generate_counts", "dls_generate_fill", "dls_aggregate", "dls_rows_from_degrees", "dls_repeat_rank_row",
 )
 STATIC_SCRATCH_BYTES = 32 << 20
 AGG_FIELDS = 8
@@ -153,6 +153,10 @@ def load() -> C.CDLL:
         lib.dls_generate_counts.argtypes = [C.POINTER(DlsGen), C.c_void_p, C.c_void_p, C.c_void_p]
         lib.dls_generate_fill.restype = C.c_int
         lib.dls_generate_fill.argtypes = [C.POINTER(DlsGen), C.POINTER(DlsBatch), C.c_void_p]
+        lib.dls_rows_from_degrees.restype = C.c_int
+        lib.dls_rows_from_degrees.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+        lib.dls_repeat_rank_row.restype = C.c_int
+        lib.dls_repeat_rank_row.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         lib.dls_aggregate.restype = C.c_int
         lib.dls_aggregate.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsResult), C.c_int, C.c_void_p, C.c_int32,
                                       C.c_void_p, C.c_void_p]

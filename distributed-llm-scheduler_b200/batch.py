@@ -146,6 +146,18 @@ class DeviceBatch:
         return dataclasses.replace(self.host, **vals)
 
 
+def _row_lengths(ptr: np.ndarray, task_off: np.ndarray) -> Optional[np.ndarray]:
+    """u8 row lengths of a concatenation of per-topology row-pointer arrays ([n_t + 1] each), or None if a row is
+    longer than 255."""
+    T = len(task_off) - 1
+    d = np.diff(ptr.astype(np.int64))
+    if T > 1:  # drop the differences that straddle two topologies
+        d = np.delete(d, (task_off[1:-1] + np.arange(T - 1)).astype(np.int64))
+    if d.size and (d.max() > 255 or d.min() < 0):
+        return None
+    return d.astype(np.uint8)
+
+
 def pin_batch(host: DagBatch) -> dict:
     """Pinned host staging copies of a batch's arrays (for timed host->device transfers)."""
     return {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL if getattr(host, f) is not None}
@@ -299,34 +311,61 @@ class PipelinedScheduler:
     object; results land in pinned host arrays (`.out`, same layout as ResultArrays).
     """
 
-    def __init__(self, host: DagBatch, algo_mask: int = N.MASK_ALL, device=None, chunks: int = 8, nstreams: int = 3):
+    def __init__(self, host: DagBatch, algo_mask: int = N.MASK_ALL, device=None, chunks: int = 8, nstreams: int = 3,
+                 compact: bool = True):
         torch = _torch()
         if host.T != host.B:
             raise ValueError("pipelining shards by instance: needs one topology per instance (T == B)")
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.mask, self.algos = algo_mask, algos_of(algo_mask)
         A = len(self.algos)
+        # The copy to the device is what bounds this path (PCIe), so ship fewer bytes where the device can rebuild
+        # them: row pointers as one-byte row lengths (dls_rows_from_degrees), one rank row for a homogeneous batch
+        # (dls_repeat_rank_row). 32 KB -> 24 KB per 1k-task instance.
+        self._deg, self._rank_row, skip = {}, None, set()
+        if compact:
+            for f in ("pred_ptr", "par_ptr"):
+                d = _row_lengths(getattr(host, f), host.task_off)
+                if d is not None:
+                    self._deg[f] = torch.from_numpy(d).pin_memory()
+                    skip.add(f)
+            ns = np.diff(host.task_off)
+            if host.B > 1 and (ns == ns[0]).all() and ns[0] > 0:
+                rows = host.rank.reshape(host.B, int(ns[0]))
+                if (rows == rows[0]).all():
+                    self._rank_row = torch.from_numpy(np.ascontiguousarray(rows[0]).view(np.int16)).pin_memory()
+                    skip.add("rank")
         # pinned copies of the inputs; the chunks below are numpy views into them
-        pinned = {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL if getattr(host, f) is not None}
+        pinned = {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL
+                  if getattr(host, f) is not None and f not in skip}
         import dataclasses
         views = {f: t.numpy().view(getattr(host, f).dtype) for f, t in pinned.items()}
         self._pinned = pinned
+        self._skip = skip
         self.host = dataclasses.replace(host, **views)
         chunks = max(1, min(chunks, host.B))
         bounds = [(c * host.B) // chunks for c in range(chunks + 1)]
         self.parts = [(lo, hi, self.host.shard(lo, hi)) for lo, hi in zip(bounds[:-1], bounds[1:]) if hi > lo]
         self.streams = [torch.cuda.Stream(self.device) for _ in range(min(nstreams, len(self.parts)))]
-        big = max(self.parts, key=lambda p: p[2].nt_inst)[2]
+        # per-stream result buffers and scratch sized for the largest chunk in EVERY dimension (ragged batches: the
+        # chunk with the most tasks need not be the one with the most nodes)
+        import types
+        big = types.SimpleNamespace(nt_inst=max(p[2].nt_inst for p in self.parts), B=max(p[2].B for p in self.parts),
+                                    nk_inst=max(p[2].nk_inst for p in self.parts), np_inst=0)
+        lib = N.load()
+        need = 0
+        for _, _, part in self.parts:
+            st = part.as_struct(lambda f, a: None)  # sizes only: dls_workspace_bytes reads no array
+            need = max(need, int(lib.dls_workspace_bytes(C.byref(st), algo_mask)))
         with torch.cuda.device(self.device):
             self._res = [BatchResult(big, algo_mask, self.device, False, False) for _ in self.streams]
-            probe = DeviceBatch(big, self.device)
-            need = int(N.load().dls_workspace_bytes(C.byref(probe.struct), algo_mask))
             self._ws = [torch.empty(need, dtype=torch.uint8, device=self.device) for _ in self.streams]
         pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
         self.out = {"node_of": pin((A, host.nt_inst), torch.int8), "seq_pos": pin((A, host.nt_inst), torch.int16),
                     "summary": pin((A, host.B, N.SUMMARY_BYTES), torch.uint8), "fin": pin((A, host.nk_inst), torch.float64),
                     "cnt": pin((A, host.nk_inst), torch.int32), "avail": pin((A, host.nk_inst), torch.float64)}
-        self.h2d_bytes = sum(t.numel() * t.element_size() for t in pinned.values())
+        self.h2d_bytes = (sum(t.numel() * t.element_size() for t in pinned.values()) + sum(t.numel() for t in self._deg.values())
+                          + (0 if self._rank_row is None else 2 * self._rank_row.numel() * len(self.parts)))
         self.d2h_bytes = sum(t.numel() * t.element_size() for t in self.out.values())
 
     def run(self):
@@ -337,7 +376,7 @@ class PipelinedScheduler:
             slot = c % len(self.streams)
             st = self.streams[slot]
             with torch.cuda.stream(st):
-                dev = DeviceBatch(part, self.device, non_blocking=True)
+                dev = self._to_device(part, lo, hi, st)
                 res = self._res[slot]
                 # result buffers are sized for the largest chunk; point the call at the leading part
                 sub = BatchResult.__new__(BatchResult)
@@ -369,6 +408,32 @@ class PipelinedScheduler:
                 keep.append(dev)
         self._keep = keep
         return self
+
+    def _to_device(self, part: DagBatch, lo: int, hi: int, st) -> DeviceBatch:
+        """Instances [lo, hi) in device memory: everything copied as it is, except what the device rebuilds."""
+        torch = _torch()
+        if not self._skip:
+            return DeviceBatch(part, self.device, non_blocking=True)
+        lib = N.load()
+        stream = C.c_void_p(st.cuda_stream)
+        tensors = {}
+        for f in _FIELDS_ALL:
+            a = getattr(part, f)
+            if a is not None and f not in self._skip:
+                tensors[f] = _to_torch_host(a, pin=False).to(self.device, non_blocking=True)  # view into pinned memory
+        t0, t1 = int(self.host.task_off[lo]), int(self.host.task_off[hi])
+        for f, deg in self._deg.items():
+            d = deg[t0:t1].to(self.device, non_blocking=True)
+            ptr = torch.empty(t1 - t0 + (hi - lo), dtype=torch.int32, device=self.device)
+            N.check(lib.dls_rows_from_degrees(d.data_ptr(), tensors["task_off"].data_ptr(), hi - lo, ptr.data_ptr(), stream))
+            tensors[f] = ptr
+            tensors["_deg_" + f] = d  # kept alive with the batch
+        if self._rank_row is not None:
+            row = self._rank_row.to(self.device, non_blocking=True)
+            rank = torch.empty(t1 - t0, dtype=torch.int16, device=self.device)
+            N.check(lib.dls_repeat_rank_row(row.data_ptr(), row.numel(), hi - lo, rank.data_ptr(), stream))
+            tensors["rank"], tensors["_rank_row"] = rank, row
+        return DeviceBatch.from_tensors(part, tensors, self.device)
 
     def synchronize(self):
         for st in self.streams:

@@ -316,6 +316,28 @@ int dls_aggregate(const dls_batch_t* batch, const dls_result_t* result, int algo
   return DLS_OK;
 }
 
+int dls_rows_from_degrees(const uint8_t* deg, const int64_t* task_off, int32_t T, uint32_t* ptr, void* cuda_stream) {
+  if (!deg || !task_off || !ptr || T <= 0) return fail(DLS_ERR_BAD_ARG, "NULL or empty argument in dls_rows_from_degrees");
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  cudaError_t e = dls::launch_rows_from_degrees(deg, task_off, T, ptr, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
+int dls_repeat_rank_row(const uint16_t* row, int32_t n, int32_t T, uint16_t* out, void* cuda_stream) {
+  if (!row || !out || n <= 0 || T <= 0) return fail(DLS_ERR_BAD_ARG, "NULL or empty argument in dls_repeat_rank_row");
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  cudaError_t e = dls::launch_repeat_row(row, n, T, out, ctx);
+  g_launches += ctx.launches;
+  if (e != cudaSuccess) return cuda_fail(e, ctx.why);
+  g_err.clear();
+  return DLS_OK;
+}
+
 /* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
 int dls_set_stream_path(int enabled) {

@@ -251,6 +251,8 @@ struct LaunchCtx {
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_schedule(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                             LaunchCtx& ctx);
+cudaError_t launch_rows_from_degrees(const uint8_t* deg, const int64_t* task_off, int T, uint32_t* ptr, LaunchCtx& ctx);
+cudaError_t launch_repeat_row(const uint16_t* row, int n, int T, uint16_t* out, LaunchCtx& ctx);
 cudaError_t launch_aggregate(const dls_batch_t& b, const dls_result_t& r, int nslots, const int32_t* group_of, int n_groups,
                              double* out, LaunchCtx& ctx);
 cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_count, LaunchCtx& ctx);

@@ -239,6 +239,17 @@ int dls_generate_fill(const dls_gen_t* gen, const dls_batch_t* out, void* cuda_s
 int dls_aggregate(const dls_batch_t* batch, const dls_result_t* result, int algo_mask, const int32_t* group_of,
                   int32_t n_groups, double* out, void* cuda_stream);
 
+/* Host-to-device traffic savers for pipelined HOST batches (no reference counterpart; the reference never leaves the
+ * host). A CSR row-pointer array is the prefix sum of its row lengths, and a homogeneous sweep repeats one rank row:
+ * the host ships one byte per task instead of a u32 (possible while no task has more than 255 dependencies /
+ * params) and one rank row instead of T, and these calls rebuild the arrays dls_schedule_batch reads, in device
+ * memory, on the caller's stream. All pointers are device pointers.
+ *   dls_rows_from_degrees: ptr[task_off[t] + t + i] = deg[task_off[t]] + ... + deg[task_off[t] + i - 1], i = 0..n_t
+ *     (i.e. the layout of dls_batch_t.pred_ptr / par_ptr); deg has task_off[T] entries, ptr task_off[T] + T.
+ *   dls_repeat_rank_row: out[t * n + i] = row[i] for t < T (dls_batch_t.rank of T topologies of n tasks each). */
+int dls_rows_from_degrees(const uint8_t* deg, const int64_t* task_off, int32_t T, uint32_t* ptr, void* cuda_stream);
+int dls_repeat_rank_row(const uint16_t* row, int32_t n, int32_t T, uint16_t* out, void* cuda_stream);
+
 /* Test/measurement switch (no reference counterpart). Qualifying batches (K <= 8 nodes, small per-DAG state, no
  * extension outputs requested) normally run on the thread-per-DAG streamed kernels, fed by the priority and
  * stream-build kernels. 0 forces the general warp-per-DAG kernels for everything; any other value restores the

@@ -211,11 +211,53 @@ def test_pipelined_host_path_matches_single_call(oracle_mod):
     from dls_b200.batch import PipelinedScheduler
     batch = random_dag_batch(150, 120, 8, 0.8, seed=31)
     want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    want.peak = want.cached = None
+    full = PipelinedScheduler(batch, N.MASK_ALL, chunks=7, nstreams=3, compact=False)
     pipe = PipelinedScheduler(batch, N.MASK_ALL, chunks=7, nstreams=3)
-    for _ in range(2):  # buffers are reused across runs
-        got = pipe.run().result()
-        want.peak = want.cached = None
-        assert_results_equal(got, want, "pipelined")
+    # row pointers travel as one-byte row lengths, the (shared) rank row once per chunk: 10 of 32 bytes per task saved
+    assert set(pipe._skip) == {"pred_ptr", "par_ptr", "rank"} and pipe.h2d_bytes < 0.8 * full.h2d_bytes
+    for p in (pipe, full):
+        for _ in range(2):  # buffers are reused across runs
+            assert_results_equal(p.run().result(), want, "pipelined")
+
+
+def test_pipelined_compact_transfer_ragged_and_fallback(oracle_mod):
+    """dls_rows_from_degrees / dls_repeat_rank_row on what they must not mangle: instances of different sizes and
+    their own rank rows (row pointers compacted, ranks not), and a task with more than 255 dependencies (its row
+    pointers travel as they are)."""
+    import ctypes as C
+    import torch
+    from dls_b200.batch import PipelinedScheduler, _row_lengths
+    from dls_b200.lowering import LoweredDag
+    cases = golden_io.load("cfg2_sweep_seed0.npz")[:60]       # n in {16, 30, 58, 60, 86}, own pi per instance
+    rb = golden_io.batch_of(cases)
+    pipe = PipelinedScheduler(rb, N.MASK_ALL, chunks=5, nstreams=2)
+    assert set(pipe._skip) == {"pred_ptr", "par_ptr"}
+    res = pipe.run().result()
+    for b, c in enumerate(cases):
+        for slot, a in enumerate(res.algos):
+            assert_matches_expected(c.exp[a], rb, res, slot, b, f"compact ragged {c.label} algo={a}")
+    # the expansion kernel alone, against the arrays it replaces
+    lib = N.load()
+    for f in ("pred_ptr", "par_ptr"):
+        deg = torch.from_numpy(_row_lengths(getattr(rb, f), rb.task_off)).cuda()
+        off = torch.from_numpy(rb.task_off).cuda()
+        out = torch.zeros(rb.nt_topo + rb.T, dtype=torch.int32, device="cuda")
+        N.check(lib.dls_rows_from_degrees(deg.data_ptr(), off.data_ptr(), rb.T, out.data_ptr(), None))
+        np.testing.assert_array_equal(out.cpu().numpy().view(np.uint32), getattr(rb, f))
+    # 300 dependencies on one task: no byte holds that
+    n = 320
+    wide = LoweredDag(names=[f"t{i}" for i in range(n)], param_names=[f"p{i}" for i in range(n)],
+                      pred_ptr=np.concatenate([np.zeros(n, np.uint32), [300]]).astype(np.uint32),
+                      pred_idx=np.arange(300, dtype=np.uint16), par_ptr=np.arange(n + 1, dtype=np.uint32),
+                      par_idx=np.arange(n, dtype=np.uint16), rank=np.arange(n, dtype=np.uint16),
+                      mem=np.full(n, 0.25), dur=np.full(n, 0.1))
+    wb = DagBatch.from_instances([wide, wide, wide], [(np.full(4, 30.0), np.array([1.0, 1.2, 0.8, 1.0]))] * 3)
+    wp = PipelinedScheduler(wb, N.MASK_ALL, chunks=2, nstreams=2)
+    assert set(wp._skip) == {"par_ptr", "rank"}
+    want = oracle_mod.schedule_batch(wb, N.MASK_ALL, nthreads=2)
+    want.peak = want.cached = None
+    assert_results_equal(wp.run().result(), want, "compact fallback (wide row)")
 
 
 def test_error_codes():
