@@ -260,7 +260,7 @@ def main():
     # Public API for host batches: PipelinedScheduler cuts the batch into chunks and overlaps the pinned
     # host->device copy, the kernels and the device->host copy of the results on three streams.
     from dls_b200.batch import PipelinedScheduler
-    pipe = PipelinedScheduler(host, N.MASK_ALL, device, chunks=16, nstreams=3)
+    pipe = PipelinedScheduler(host, N.MASK_ALL, device, chunks=24, nstreams=3)
 
     def step_e2e():
         nonlocal gathered

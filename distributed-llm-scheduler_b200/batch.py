@@ -308,12 +308,15 @@ class PipelinedScheduler:
     """End-to-end path for HOST batches: instances are cut into chunks and pushed through `nstreams` CUDA streams so
     that the host->device copy of chunk i+1, the kernels of chunk i and the device->host copy of chunk i-1 overlap
     (PCIe is full duplex; the kernels need neither direction). Inputs are staged in pinned memory once per batch
-    object; results land in pinned host arrays (`.out`, same layout as ResultArrays).
+    object; results land in pinned host arrays (`.out`, same layout as ResultArrays). Everything a pass needs —
+    device buffers per stream, the descriptor of every chunk, the list of copies — is built here, once: `run()` only
+    enqueues copies and library calls (no allocation, no lowering), which is what lets the host keep three streams fed.
     """
 
     def __init__(self, host: DagBatch, algo_mask: int = N.MASK_ALL, device=None, chunks: int = 8, nstreams: int = 3,
                  compact: bool = True):
         torch = _torch()
+        lib = N.load()
         if host.T != host.B:
             raise ValueError("pipelining shards by instance: needs one topology per instance (T == B)")
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
@@ -322,118 +325,151 @@ class PipelinedScheduler:
         # The copy to the device is what bounds this path (PCIe), so ship fewer bytes where the device can rebuild
         # them: row pointers as one-byte row lengths (dls_rows_from_degrees), one rank row for a homogeneous batch
         # (dls_repeat_rank_row). 32 KB -> 24 KB per 1k-task instance.
-        self._deg, self._rank_row, skip = {}, None, set()
+        deg, rank_row, skip = {}, None, set()
         if compact:
             for f in ("pred_ptr", "par_ptr"):
                 d = _row_lengths(getattr(host, f), host.task_off)
                 if d is not None:
-                    self._deg[f] = torch.from_numpy(d).pin_memory()
+                    deg[f] = torch.from_numpy(d).pin_memory()
                     skip.add(f)
             ns = np.diff(host.task_off)
             if host.B > 1 and (ns == ns[0]).all() and ns[0] > 0:
                 rows = host.rank.reshape(host.B, int(ns[0]))
                 if (rows == rows[0]).all():
-                    self._rank_row = torch.from_numpy(np.ascontiguousarray(rows[0]).view(np.int16)).pin_memory()
+                    rank_row = torch.from_numpy(np.ascontiguousarray(rows[0]).view(np.int16)).pin_memory()
                     skip.add("rank")
-        # pinned copies of the inputs; the chunks below are numpy views into them
+        self._skip = skip
+        # pinned copies of the inputs that travel as they are
         pinned = {f: _to_torch_host(getattr(host, f), pin=True) for f in _FIELDS_ALL
                   if getattr(host, f) is not None and f not in skip}
-        import dataclasses
-        views = {f: t.numpy().view(getattr(host, f).dtype) for f, t in pinned.items()}
-        self._pinned = pinned
-        self._skip = skip
-        self.host = dataclasses.replace(host, **views)
+        self._pinned, self._deg, self._rank_row = pinned, deg, rank_row
+        self.host = host
         chunks = max(1, min(chunks, host.B))
         bounds = [(c * host.B) // chunks for c in range(chunks + 1)]
-        self.parts = [(lo, hi, self.host.shard(lo, hi)) for lo, hi in zip(bounds[:-1], bounds[1:]) if hi > lo]
-        self.streams = [torch.cuda.Stream(self.device) for _ in range(min(nstreams, len(self.parts)))]
-        # per-stream result buffers and scratch sized for the largest chunk in EVERY dimension (ragged batches: the
-        # chunk with the most tasks need not be the one with the most nodes)
-        import types
-        big = types.SimpleNamespace(nt_inst=max(p[2].nt_inst for p in self.parts), B=max(p[2].B for p in self.parts),
-                                    nk_inst=max(p[2].nk_inst for p in self.parts), np_inst=0)
-        lib = N.load()
-        need = 0
-        for _, _, part in self.parts:
-            st = part.as_struct(lambda f, a: None)  # sizes only: dls_workspace_bytes reads no array
-            need = max(need, int(lib.dls_workspace_bytes(C.byref(st), algo_mask)))
-        with torch.cuda.device(self.device):
-            self._res = [BatchResult(big, algo_mask, self.device, False, False) for _ in self.streams]
-            self._ws = [torch.empty(need, dtype=torch.uint8, device=self.device) for _ in self.streams]
+        parts = [(lo, hi, host.shard(lo, hi)) for lo, hi in zip(bounds[:-1], bounds[1:]) if hi > lo]
+        self.parts = parts
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(min(nstreams, len(parts)))]
+        S = len(self.streams)
+
+        # where the arrays of chunk [lo, hi) start in the batch's arrays (offset tables are rebased copies, see below)
+        def span(f, lo, hi):
+            t0, t1 = int(host.task_off[lo]), int(host.task_off[hi])
+            if f in ("pred_ptr", "par_ptr"):
+                return t0 + lo, t1 + hi
+            if f in ("rank", "mem", "dur"):
+                return t0, t1
+            if f == "pred_idx":
+                return int(host.pred_off[lo]), int(host.pred_off[hi])
+            if f == "par_idx":
+                return int(host.par_off[lo]), int(host.par_off[hi])
+            if f in ("cap", "spd"):
+                return (int(host.node_off[lo]), int(host.node_off[hi])) if host.node_off is not None else (0, len(host.cap))
+            raise KeyError(f)
+
+        tables = ("task_off", "pred_off", "par_off", "pid_off", "node_off")
+        size = {}  # largest chunk, per array
+        for lo, hi, part in parts:
+            for f in _FIELDS_ALL:
+                a = getattr(part, f)
+                if a is not None:
+                    size[f] = max(size.get(f, 0), int(a.size))
         pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
         self.out = {"node_of": pin((A, host.nt_inst), torch.int8), "seq_pos": pin((A, host.nt_inst), torch.int16),
                     "summary": pin((A, host.B, N.SUMMARY_BYTES), torch.uint8), "fin": pin((A, host.nk_inst), torch.float64),
                     "cnt": pin((A, host.nk_inst), torch.int32), "avail": pin((A, host.nk_inst), torch.float64)}
-        self.h2d_bytes = (sum(t.numel() * t.element_size() for t in pinned.values()) + sum(t.numel() for t in self._deg.values())
-                          + (0 if self._rank_row is None else 2 * self._rank_row.numel() * len(self.parts)))
+        need = 0
+        for _, _, part in parts:
+            need = max(need, int(lib.dls_workspace_bytes(C.byref(part.as_struct(lambda f, a: None)), algo_mask)))
+        nt_max, b_max, nk_max = (max(p[2].nt_inst for p in parts), max(p[2].B for p in parts), max(p[2].nk_inst for p in parts))
+        with torch.cuda.device(self.device):
+            self._slot = []
+            for _ in range(S):
+                buf = {f: torch.empty(n, dtype=_to_torch_host(np.empty(0, getattr(host, f).dtype), False).dtype,
+                                      device=self.device) for f, n in size.items()}
+                if deg:
+                    buf["_deg"] = {f: torch.empty(size["rank"], dtype=torch.uint8, device=self.device) for f in deg}
+                if rank_row is not None:
+                    buf["_rank_row"] = torch.empty(rank_row.numel(), dtype=torch.int16, device=self.device)
+                buf["_ws"] = torch.empty(max(need, 8), dtype=torch.uint8, device=self.device)
+                buf["_res"] = {"node_of": torch.empty(A * nt_max, dtype=torch.int8, device=self.device),
+                               "seq_pos": torch.empty(A * nt_max, dtype=torch.int16, device=self.device),
+                               "summary": torch.empty(A * b_max * N.SUMMARY_BYTES, dtype=torch.uint8, device=self.device),
+                               "fin": torch.empty(A * nk_max, dtype=torch.float64, device=self.device),
+                               "cnt": torch.empty(A * nk_max, dtype=torch.int32, device=self.device),
+                               "avail": torch.empty(A * nk_max, dtype=torch.float64, device=self.device)}
+                r = N.DlsResult()
+                for f, t in buf["_res"].items():
+                    setattr(r, f, t.data_ptr())
+                buf["_rstruct"] = r
+                self._slot.append(buf)
+        # the plan: per chunk, what to copy where and the descriptor to hand to the library
+        self._plan, self._tables = [], []
+        h2d = 0
+        for c, (lo, hi, part) in enumerate(parts):
+            buf = self._slot[c % S]
+            copies, expand = [], []
+            for f in _FIELDS_ALL:
+                a = getattr(part, f)
+                if a is None:
+                    continue
+                if f in tables:  # rebased by shard(): small arrays of their own
+                    src = _to_torch_host(a, pin=True)
+                    self._tables.append(src)
+                elif f in skip:
+                    continue
+                else:
+                    a0, a1 = span(f, lo, hi)
+                    src = pinned[f][a0:a1]
+                copies.append((buf[f][:src.numel()], src))
+                h2d += src.numel() * src.element_size()
+            t0, t1 = int(host.task_off[lo]), int(host.task_off[hi])
+            for f, d in deg.items():
+                copies.append((buf["_deg"][f][:t1 - t0], d[t0:t1]))
+                h2d += t1 - t0
+                expand.append(("rows", buf["_deg"][f].data_ptr(), buf["task_off"].data_ptr(), hi - lo, buf[f].data_ptr()))
+            if rank_row is not None:
+                copies.append((buf["_rank_row"], rank_row))
+                h2d += 2 * rank_row.numel()
+                expand.append(("rank", buf["_rank_row"].data_ptr(), rank_row.numel(), hi - lo, buf["rank"].data_ptr()))
+            struct = part.as_struct_present(lambda f: buf[f].data_ptr() if f in buf else None)
+            k0, k1 = (int(host.node_off[lo]), int(host.node_off[hi])) if host.node_off is not None else (
+                lo * host.K_max, hi * host.K_max)
+            back = []
+            for a in range(A):  # one contiguous async copy per array and algorithm slot (strided copies would be staged)
+                res = buf["_res"]
+                nt, nb, nk = part.nt_inst, part.B, part.nk_inst
+                back.append((self.out["node_of"][a, t0:t1], res["node_of"][a * nt:(a + 1) * nt]))
+                back.append((self.out["seq_pos"][a, t0:t1], res["seq_pos"][a * nt:(a + 1) * nt]))
+                back.append((self.out["summary"][a, lo:hi].view(-1),
+                             res["summary"][a * nb * N.SUMMARY_BYTES:(a + 1) * nb * N.SUMMARY_BYTES]))
+                back.append((self.out["fin"][a, k0:k1], res["fin"][a * nk:(a + 1) * nk]))
+                back.append((self.out["cnt"][a, k0:k1], res["cnt"][a * nk:(a + 1) * nk]))
+                back.append((self.out["avail"][a, k0:k1], res["avail"][a * nk:(a + 1) * nk]))
+            self._plan.append((c % S, copies, expand, struct, back))
+        self.h2d_bytes = h2d
         self.d2h_bytes = sum(t.numel() * t.element_size() for t in self.out.values())
 
     def run(self):
         """One pass over the whole batch. Returns after everything has been ENQUEUED; call `.synchronize()`."""
         torch = _torch()
-        keep = []
-        for c, (lo, hi, part) in enumerate(self.parts):
-            slot = c % len(self.streams)
-            st = self.streams[slot]
-            with torch.cuda.stream(st):
-                dev = self._to_device(part, lo, hi, st)
-                res = self._res[slot]
-                # result buffers are sized for the largest chunk; point the call at the leading part
-                sub = BatchResult.__new__(BatchResult)
-                sub.batch, sub.mask, sub.algos = part, self.mask, self.algos
-                A = len(self.algos)
-                views = {"node_of": res.node_of.view(-1)[:A * part.nt_inst].view(A, part.nt_inst),
-                         "seq_pos": res.seq_pos.view(-1)[:A * part.nt_inst].view(A, part.nt_inst),
-                         "summary": res.summary.view(-1)[:A * part.B * N.SUMMARY_BYTES].view(A, part.B, N.SUMMARY_BYTES),
-                         "fin": res.fin.view(-1)[:A * part.nk_inst].view(A, part.nk_inst),
-                         "cnt": res.cnt.view(-1)[:A * part.nk_inst].view(A, part.nk_inst),
-                         "avail": res.avail.view(-1)[:A * part.nk_inst].view(A, part.nk_inst)}
-                r = N.DlsResult()
-                for f, t in views.items():
-                    setattr(sub, f, t)
-                    setattr(r, f, t.data_ptr())
-                sub.peak = sub.cached = None
-                sub.struct = r
-                schedule_batch(dev, self.mask, workspace=self._ws[slot], result=sub)
-                t0, t1 = int(self.host.task_off[lo]), int(self.host.task_off[hi])
-                k0, k1 = (int(self.host.node_off[lo]), int(self.host.node_off[hi])) if self.host.node_off is not None else (
-                    lo * self.host.K_max, hi * self.host.K_max)
-                for a in range(A):  # one contiguous async copy per array and algorithm slot (strided copies would be staged)
-                    self.out["node_of"][a, t0:t1].copy_(views["node_of"][a], non_blocking=True)
-                    self.out["seq_pos"][a, t0:t1].copy_(views["seq_pos"][a], non_blocking=True)
-                    self.out["summary"][a, lo:hi].copy_(views["summary"][a], non_blocking=True)
-                    self.out["fin"][a, k0:k1].copy_(views["fin"][a], non_blocking=True)
-                    self.out["cnt"][a, k0:k1].copy_(views["cnt"][a], non_blocking=True)
-                    self.out["avail"][a, k0:k1].copy_(views["avail"][a], non_blocking=True)
-                keep.append(dev)
-        self._keep = keep
-        return self
-
-    def _to_device(self, part: DagBatch, lo: int, hi: int, st) -> DeviceBatch:
-        """Instances [lo, hi) in device memory: everything copied as it is, except what the device rebuilds."""
-        torch = _torch()
-        if not self._skip:
-            return DeviceBatch(part, self.device, non_blocking=True)
         lib = N.load()
-        stream = C.c_void_p(st.cuda_stream)
-        tensors = {}
-        for f in _FIELDS_ALL:
-            a = getattr(part, f)
-            if a is not None and f not in self._skip:
-                tensors[f] = _to_torch_host(a, pin=False).to(self.device, non_blocking=True)  # view into pinned memory
-        t0, t1 = int(self.host.task_off[lo]), int(self.host.task_off[hi])
-        for f, deg in self._deg.items():
-            d = deg[t0:t1].to(self.device, non_blocking=True)
-            ptr = torch.empty(t1 - t0 + (hi - lo), dtype=torch.int32, device=self.device)
-            N.check(lib.dls_rows_from_degrees(d.data_ptr(), tensors["task_off"].data_ptr(), hi - lo, ptr.data_ptr(), stream))
-            tensors[f] = ptr
-            tensors["_deg_" + f] = d  # kept alive with the batch
-        if self._rank_row is not None:
-            row = self._rank_row.to(self.device, non_blocking=True)
-            rank = torch.empty(t1 - t0, dtype=torch.int16, device=self.device)
-            N.check(lib.dls_repeat_rank_row(row.data_ptr(), row.numel(), hi - lo, rank.data_ptr(), stream))
-            tensors["rank"], tensors["_rank_row"] = rank, row
-        return DeviceBatch.from_tensors(part, tensors, self.device)
+        for slot, copies, expand, struct, back in self._plan:
+            st = self.streams[slot]
+            buf = self._slot[slot]
+            stream = C.c_void_p(st.cuda_stream)
+            with torch.cuda.stream(st):
+                for dst, src in copies:
+                    dst.copy_(src, non_blocking=True)
+                for e in expand:
+                    if e[0] == "rows":
+                        N.check(lib.dls_rows_from_degrees(e[1], e[2], e[3], e[4], stream))
+                    else:
+                        N.check(lib.dls_repeat_rank_row(e[1], e[2], e[3], e[4], stream))
+                N.check(lib.dls_schedule_batch(C.byref(struct), C.byref(buf["_rstruct"]), self.mask, buf["_ws"].data_ptr(),
+                                               buf["_ws"].numel(), stream))
+                for dst, src in back:
+                    dst.copy_(src, non_blocking=True)
+        return self
 
     def synchronize(self):
         for st in self.streams:
