@@ -8,10 +8,12 @@
 // depth r, in the order of the pending set (rank) after a stable sort by the algorithm's key, so the whole
 // processing order is static:  order = sort by (depth asc, key desc, rank asc).
 //
-// priority_topology_kernel: one CTA per topology. Level-synchronous relaxation for depth, reverse CSR by
-// counting sort, and stable counting sorts (warp __match_any placement) for the DFS/Greedy and MRU orders.
-// priority_critical_kernel: one CTA per instance. Upward rank level by level from the sinks, then the
-// within-level stable sort by rank-by-counting.
+// priority_topology_kernel: one CTA per topology. Reverse CSR by counting sort; depth by one in-order pass over
+// CTA-wide chunks when the tasks are listed topologically (else level-synchronous relaxation); stable counting sorts
+// (warp __match_any placement) for the DFS/Greedy and MRU orders.
+// param_class_kernel: one CTA per topology: which params are shared between tasks.
+// priority_critical_kernel: one CTA per instance. Upward rank level by level from the sinks, then inside each level
+// value buckets and pair counting inside a bucket.
 #include "dls_common.cuh"
 #include "dls_sort.cuh"
 
@@ -253,7 +255,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   if (tid == 0) w.nshared[t] = (int)nsh;
 }
 
-__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key, int m_sort) {
+__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
   __shared__ uint32_t s_part[33];
@@ -266,11 +268,10 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   if (n == 0) return;
   const int n_al = (n + 3) & ~3;
   double* s_up = reinterpret_cast<double*>(smem_raw);             // [n]
-  // sort scratch: counting with keys (use_key): s_key[n]; bitonic (m_sort = power of two >= n): s_key[m], s_lq[m]
-  double* s_key = s_up + ((n + 1) & ~1);  // 16-byte aligned: read as double2
-  const int nkey = m_sort ? m_sort : (use_key ? ((n + 1) & ~1) : 0);
-  uint32_t* s_lq = reinterpret_cast<uint32_t*>(s_key + nkey);      // [m_sort] (level << 16 | position)
-  uint32_t* s_lvl = s_lq + m_sort;                                 // [n+2] first position of each level
+  // sort scratch (use_key): s_key[n], the keys in bucket order; without it (very large DAGs) keys are read in place
+  double* s_key = s_up + ((n + 1) & ~1);  // 16-byte aligned
+  const int nkey = use_key ? ((n + 1) & ~1) : 0;
+  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(s_key + nkey);     // [n+2] first position of each level
   uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
   uint16_t* s_depth = s_ord + n_al;                               // [n_al]
   uint16_t* s_pq = s_depth + n_al;                                // [n_al] (use_key) pi position of each bucketed key
@@ -284,7 +285,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
   // needed before the sort (if it fits: 4(n+1) + 2E bytes in 8n). From global memory the dependent loads of the level
   // loop were 53 % of this kernel (clock64 per phase, round 1e).
   const uint32_t E = (uint32_t)(b.pred_off[v.topo + 1] - b.pred_off[v.topo]);
-  const bool staged = (use_key || m_sort) && (size_t)4 * (n + 1) + (size_t)2 * E <= (size_t)8 * ((n + 1) & ~1);
+  const bool staged = use_key && (size_t)4 * (n + 1) + (size_t)2 * E <= (size_t)8 * ((n + 1) & ~1);
   uint32_t* s_sptr = reinterpret_cast<uint32_t*>(s_key);
   uint16_t* s_sidx = reinterpret_cast<uint16_t*>(s_sptr + (n + 1));
   strided_for<8>(n, [&](int q) {
@@ -432,15 +433,10 @@ size_t priority_smem_param(int /*n_max*/, int P_max) {
   return ((size_t)P_max + 2) * sizeof(uint32_t);
 }
 
-// A block-wide bitonic network over (level, up, position) was tried for the Critical order (round 1c): with its
-// ~55 barriers per 1k-task DAG it ran 2x SLOWER than the per-level counting below, so it is not used.
-static int bitonic_size(int) { return 0; }
-
 size_t priority_smem_inst(int n_max, bool with_key) {
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
-  const size_t m = with_key ? (size_t)bitonic_size(n_max) : 0;
-  const size_t nkey = m ? m : (with_key ? ((n + 1) & ~(size_t)1) : 0);
-  return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (m + n + 2) * sizeof(uint32_t) + (with_key ? 3 : 2) * n_al * sizeof(uint16_t);
+  const size_t nkey = with_key ? ((n + 1) & ~(size_t)1) : 0;
+  return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (n + 2) * sizeof(uint32_t) + (with_key ? 3 : 2) * n_al * sizeof(uint16_t);
 }
 
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
@@ -475,13 +471,12 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     size_t sm2 = priority_smem_inst(b.n_max, true);
     const int use_key = sm2 <= 96 * 1024;
     if (!use_key) sm2 = priority_smem_inst(b.n_max, false);
-    const int m_sort = use_key ? bitonic_size(b.n_max) : 0;
     ctx.why = "cudaFuncSetAttribute(priority_critical_kernel)";
     e = cudaFuncSetAttribute(priority_critical_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     int grid = w.cp_per_instance ? b.B : 1;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;
-    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w, use_key, m_sort);
+    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w, use_key);
     if (ctx.prof) ctx.prof->end(rec, ctx.st);
     ++ctx.launches;
     ctx.why = "priority_critical_kernel launch";
