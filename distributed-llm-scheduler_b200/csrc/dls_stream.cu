@@ -733,20 +733,21 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
           any_ready = true;
           // none of the task's (private) params is cached anywhere: params_to_load = npar on every node
           const double need = memory_requirement(m, npar);
-          bool all_fit = true;
+          uint32_t fits = 0;  // can_fit_on_node per node; a node that does not exist holds -inf and never fits
 #pragma unroll
-          for (int k = 0; k < KMAX; ++k) all_fit = all_fit && (k >= K || need <= avail[k]);
+          for (int k = 0; k < KMAX; ++k) fits |= need <= avail[k] ? 1u << k : 0u;
           int best = -1;
-          double best_score = -INFINITY;
-          if (all_fit) {
-            // no memory pressure: score = 0.0 + cached*20 + available_memory - len(completed_tasks)*0.5 with cached == 0
+          double best_score = -INFINITY, a = 0.0;  // a: available memory of the chosen node
+          if (fits == (1u << K) - 1u) {
+            // no memory pressure: score = 0.0 + cached*20 + available_memory - len(completed_tasks)*0.5 with cached == 0.
+            // (0.0 + x is x, but for x = -0.0, and then only the sign of a zero score differs: no comparison sees it)
             double hc[KMAX];
 #pragma unroll
             for (int k = 0; k < KMAX; ++k) hc[k] = sl.f(HCNT + k);
 #pragma unroll
             for (int k = 0; k < KMAX; ++k) {
-              const double score = __dsub_rn(__dadd_rn(0.0, avail[k]), hc[k]);  // ref :483-498 (avail = -inf off the end)
-              if (score > best_score) { best_score = score; best = k; }
+              const double score = __dsub_rn(avail[k], hc[k]);  // ref :483-498 (avail = -inf off the end)
+              if (score > best_score) { best_score = score; best = k; a = avail[k]; }
             }
           } else {
 #pragma unroll
@@ -754,7 +755,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
               if (k < K) {
                 double score = 0.0;
                 bool cand = true;
-                if (need <= avail[k]) {
+                if ((fits >> k) & 1u) {
                   score = __dadd_rn(score, avail[k]);  // ref :490-491
                 } else {
                   // evict_params_for_task mutates the node even if another node wins (ref :492)
@@ -769,8 +770,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
               }
             }
           }
-          double a = 0.0;
-          if (best >= 0) {
+          if (best >= 0 && fits != (1u << K) - 1u) {
             a = pick<KMAX>(avail, best);
             if (!(need <= a)) {  // ref :506-507 (only after a rounding mishap in the first eviction)
               uint32_t nc = sl.w(NC + best);
