@@ -60,7 +60,7 @@ SUMMARY_DTYPE = [
 class DlsResult(C.Structure):
     _fields_ = [
         ("node_of", C.c_void_p), ("seq_pos", C.c_void_p), ("summary", C.c_void_p), ("fin", C.c_void_p),
-        ("cnt", C.c_void_p), ("avail", C.c_void_p), ("peak", C.c_void_p), ("cached", C.c_void_p),
+        ("cnt", C.c_void_p), ("avail", C.c_void_p), ("peak", C.c_void_p), ("cached", C.c_void_p), ("tfin", C.c_void_p),
     ]
 
 

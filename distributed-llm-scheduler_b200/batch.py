@@ -34,9 +34,10 @@ class ResultArrays:
     avail: np.ndarray     # f64 [A, NK]
     peak: Optional[np.ndarray]    # f64 [A, NK]
     cached: Optional[np.ndarray]  # u32 [A, NP]
+    tfin: Optional[np.ndarray] = None  # f64 [A, NK] extension: node finish times on the dependency-aware timeline
 
     @classmethod
-    def empty(cls, batch: DagBatch, mask: int, peak: bool = True, cached: bool = True) -> "ResultArrays":
+    def empty(cls, batch: DagBatch, mask: int, peak: bool = True, cached: bool = True, timeline: bool = False) -> "ResultArrays":
         al = algos_of(mask)
         A = len(al)
         return cls(
@@ -45,17 +46,30 @@ class ResultArrays:
             summary=np.zeros((A, batch.B), np.dtype(N.SUMMARY_DTYPE)), fin=np.zeros((A, batch.nk_inst), np.float64),
             cnt=np.zeros((A, batch.nk_inst), np.int32), avail=np.zeros((A, batch.nk_inst), np.float64),
             peak=np.zeros((A, batch.nk_inst), np.float64) if peak else None,
-            cached=np.zeros((A, batch.np_inst), np.uint32) if cached else None)
+            cached=np.zeros((A, batch.np_inst), np.uint32) if cached else None,
+            tfin=np.zeros((A, batch.nk_inst), np.float64) if timeline else None)
 
     def slot(self, algo: int) -> int:
         return self.algos.index(algo)
 
     def host_struct(self) -> N.DlsResult:
         r = N.DlsResult()
-        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail", "peak", "cached"):
+        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail", "peak", "cached", "tfin"):
             a = getattr(self, f)
             setattr(r, f, None if a is None else a.ctypes.data)
         return r
+
+    def dependency_aware_makespan(self, batch: DagBatch) -> np.ndarray:
+        """[A, B] makespan on the dependency-aware timeline (extension, needs `timeline=True`): max of `tfin` over the
+        nodes of the instance that ran at least one task, 0.0 if none did."""
+        if self.tfin is None:
+            raise ValueError("no timeline in this result: ask for it with timeline=True")
+        out = np.zeros((len(self.algos), batch.B))
+        for b in range(batch.B):
+            ks = batch.node_slice(b)
+            used = self.cnt[:, ks] > 0
+            out[:, b] = np.where(used, self.tfin[:, ks], 0.0).max(axis=1) if used.shape[1] else 0.0
+        return out
 
 
 # ---- lifting (SURVEY.md section 8a' "RESULT LIFT") ---------------------------------------------------------
@@ -166,7 +180,7 @@ def pin_batch(host: DagBatch) -> dict:
 class BatchResult:
     """Device-resident outputs of one `schedule_batch` call; `.host()` brings them back as ResultArrays."""
 
-    def __init__(self, batch: DagBatch, mask: int, device, peak: bool, cached: bool):
+    def __init__(self, batch: DagBatch, mask: int, device, peak: bool, cached: bool, timeline: bool = False):
         torch = _torch()
         self.batch, self.mask, self.algos = batch, mask, algos_of(mask)
         A = len(self.algos)
@@ -179,8 +193,9 @@ class BatchResult:
         self.avail = torch.empty((A, batch.nk_inst), dtype=torch.float64, device=dev)
         self.peak = torch.empty((A, batch.nk_inst), dtype=torch.float64, device=dev) if peak else None
         self.cached = torch.empty((A, batch.np_inst), dtype=torch.int32, device=dev) if cached else None
+        self.tfin = torch.empty((A, batch.nk_inst), dtype=torch.float64, device=dev) if timeline else None
         r = N.DlsResult()
-        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail", "peak", "cached"):
+        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail", "peak", "cached", "tfin"):
             t = getattr(self, f)
             setattr(r, f, None if t is None else t.data_ptr())
         self.struct = r
@@ -192,7 +207,7 @@ class BatchResult:
     def d2h_bytes(self, full: bool = True) -> int:
         ts = [self.summary] + ([self.node_of, self.seq_pos, self.fin, self.cnt, self.avail] if full else [])
         if full:
-            ts += [t for t in (self.peak, self.cached) if t is not None]
+            ts += [t for t in (self.peak, self.cached, self.tfin) if t is not None]
         return sum(t.numel() * t.element_size() for t in ts)
 
     def host(self) -> ResultArrays:
@@ -202,7 +217,8 @@ class BatchResult:
             seq_pos=self.seq_pos.cpu().numpy().view(np.uint16),
             summary=self.summary_host(), fin=self.fin.cpu().numpy(), cnt=self.cnt.cpu().numpy(),
             avail=self.avail.cpu().numpy(), peak=None if self.peak is None else self.peak.cpu().numpy(),
-            cached=None if self.cached is None else self.cached.cpu().numpy().view(np.uint32))
+            cached=None if self.cached is None else self.cached.cpu().numpy().view(np.uint32),
+            tfin=None if self.tfin is None else self.tfin.cpu().numpy())
 
 
 def workspace_bytes(dev_batch: DeviceBatch, mask: int) -> int:
@@ -210,7 +226,7 @@ def workspace_bytes(dev_batch: DeviceBatch, mask: int) -> int:
 
 
 def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool = False, cached: bool = False,
-                   workspace=None, result: Optional[BatchResult] = None) -> BatchResult:
+                   workspace=None, result: Optional[BatchResult] = None, timeline: bool = False) -> BatchResult:
     """Run the algorithms in `algo_mask` over every instance of `batch` on the GPU.
 
     `batch` is a host `DagBatch` (copied to HBM here) or an already resident `DeviceBatch`. Work is enqueued
@@ -219,7 +235,8 @@ def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool =
 
     `peak` (extension: per-node peak memory) and `cached` (final Node.cached_params as bitmasks) are produced by
     the general warp-per-DAG kernels only; asking for either keeps the whole batch off the faster thread-per-DAG
-    path, so leave them off for sweeps.
+    path, so leave them off for sweeps. The same holds for `timeline` (extension: node finish times on a
+    dependency-aware timeline, see dls_result_t.tfin in include/dls.h and ResultArrays.dependency_aware_makespan).
     """
     torch = _torch()
     lib = N.load()
@@ -231,7 +248,7 @@ def schedule_batch(batch, algo_mask: int = N.MASK_ALL, device=None, peak: bool =
     device = batch.device
     with torch.cuda.device(device):
         if result is None:
-            result = BatchResult(batch.host, algo_mask, device, peak, cached)
+            result = BatchResult(batch.host, algo_mask, device, peak, cached, timeline)
         need = int(lib.dls_workspace_bytes(C.byref(batch.struct), algo_mask))
         if workspace is None or workspace.numel() < need:
             workspace = torch.empty(max(need, 8), dtype=torch.uint8, device=device)

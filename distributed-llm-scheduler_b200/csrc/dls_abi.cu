@@ -186,6 +186,13 @@ int static_scratch_address(void** out) {
 int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace, size_t ws_bytes,
                  void* cuda_stream, bool clear_status) {
   const int lim = smem_limit();
+  if (result->tfin) {  // the timeline extension keeps one finish time per task next to the rest of the per-DAG state
+    size_t need = 0;
+    if (algo_mask & 7) need = std::max(need, dls::sched_smem_simple(batch->n_max, batch->P_max));
+    if (algo_mask & (1 << DLS_ALGO_MRU)) need = std::max(need, dls::sched_smem_mru(batch->n_max, batch->P_max, batch->K_max));
+    need = ((need + 15) & ~(size_t)15) + (((size_t)batch->n_max * sizeof(double) + 15) & ~(size_t)15);
+    if (need > (size_t)lim) return fail(DLS_ERR_TOO_LARGE, "per-DAG state plus the timeline's finish times exceed shared memory");
+  }
   bool stream = g_stream_enabled && dls::stream_path_possible(*batch, result, lim);
   Layout L = layout_of(*batch, algo_mask, stream);
   if (stream && ws_bytes < L.total) {

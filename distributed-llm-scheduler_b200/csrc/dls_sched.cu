@@ -24,7 +24,7 @@ struct OutPtrs {
   int8_t* node_of;
   uint16_t* seq_pos;
   dls_summary_t* summary;
-  double *fin, *avail, *peak;
+  double *fin, *avail, *peak, *tfin;
   int32_t* cnt;
   uint32_t* cached;
 };
@@ -39,6 +39,7 @@ __device__ __forceinline__ OutPtrs bind_out(const dls_batch_t& b, const dls_resu
   o.avail = r.avail + (int64_t)slot * b.nk_inst + v.k_out;
   o.peak = r.peak ? r.peak + (int64_t)slot * b.nk_inst + v.k_out : nullptr;
   o.cached = r.cached ? r.cached + (int64_t)slot * b.np_inst + v.p_out : nullptr;
+  o.tfin = r.tfin ? r.tfin + (int64_t)slot * b.nk_inst + v.k_out : nullptr;
   return o;
 }
 
@@ -52,6 +53,7 @@ __device__ void write_unscheduled(const OutPtrs& o, const Inst& v, int lane, int
     o.cnt[lane] = 0;
     o.avail[lane] = v.cap[lane];
     if (o.peak) o.peak[lane] = 0.0;
+    if (o.tfin) o.tfin[lane] = 0.0;
   }
   if (o.cached)
     for (int p = lane; p < v.P; p += 32) o.cached[p] = 0;
@@ -67,6 +69,7 @@ __device__ void write_unscheduled(const OutPtrs& o, const Inst& v, int lane, int
 // Node state a lane carries. Lanes >= K hold inert values.
 struct NodeRegs {
   double avail, spd, cap, fin, peak;
+  double tfree;  // extension (dls_result_t.tfin): when the node is free on the dependency-aware timeline
   int cnt;
 };
 
@@ -81,6 +84,7 @@ __device__ __forceinline__ void epilogue(const OutPtrs& o, const Inst& v, int la
     o.cnt[lane] = nd.cnt;
     o.avail[lane] = nd.avail;
     if (o.peak) o.peak[lane] = nd.peak;
+    if (o.tfin) o.tfin[lane] = nd.tfree;
   }
   if (lane == 0) {
     dls_summary_t s;
@@ -102,12 +106,26 @@ __device__ __forceinline__ void apply_assignment(NodeRegs& nd, int params_to_loa
   nd.cnt += 1;
 }
 
+// Extension, no reference counterpart (dls_result_t.tfin): task `i`, just assigned to node `best`, on a timeline that
+// honours dependencies: it starts when the node is free and every dependency has finished. s_tf[j] = finish time of
+// task j (dependencies are assigned, hence written, earlier).
+__device__ __forceinline__ void timeline_step(NodeRegs& nd, double* s_tf, const Inst& v, int i, int best, int lane) {
+  double dm = 0.0;
+  for (uint32_t e = v.pred_ptr[i] + lane; e < v.pred_ptr[i + 1]; e += 32) dm = fmax(dm, s_tf[v.pred_idx[e]]);
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) dm = fmax(dm, __shfl_xor_sync(DLS_FULL_MASK, dm, off));
+  if (lane == best) nd.tfree = __dadd_rn(fmax(nd.tfree, dm), __ddiv_rn(v.dur[i], nd.spd));
+  const double tf = __shfl_sync(DLS_FULL_MASK, nd.tfree, best);
+  if (lane == 0) s_tf[i] = tf;
+  __syncwarp();
+}
+
 // ===================================================================================================================
 // DFS / Greedy / Critical
 // ===================================================================================================================
 template <int ALGO>
 __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_simple_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
-                                                                        int warp_words) {
+                                                                        int warp_words, int tl_word) {
   extern __shared__ __align__(16) uint32_t smem_all[];
   // one WARP per instance; blockDim / 32 of them share a CTA (see launch_one), each with its own slice of shared memory
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
@@ -145,7 +163,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_simple_kernel(dls_bat
   nd.avail = nd.cap;
   nd.fin = 0.0;
   nd.peak = 0.0;
+  nd.tfree = 0.0;
   nd.cnt = 0;
+  double* s_tf = (o.tfin && tl_word >= 0) ? reinterpret_cast<double*>(smem + tl_word) : nullptr;
   int completed = 0, failed = 0, hits = 0, misses = 0, rounds = 0;
   int t = 0;
   while (completed + failed < n) {  // while self.pending_tasks
@@ -186,6 +206,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_simple_kernel(dls_bat
       }
       if (best >= 0) {
         if (lane == best) apply_assignment(nd, l, m, v.dur[i]);
+        if (s_tf) timeline_step(nd, s_tf, v, i, best, lane);
         const int lb = __shfl_sync(DLS_FULL_MASK, l, best);
         misses += lb;                   // replay of simulate_execution's seen-set: without evictions it equals
         hits += (int)(qe - qb) - lb;    // the cached set at assignment time (ref simulation.py:253-258)
@@ -318,7 +339,7 @@ __device__ __forceinline__ void rcnt_add(const MruState& ms, const Inst& v, int 
 }
 
 __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
-                                                                     int warp_words) {
+                                                                     int warp_words, int tl_word) {
   extern __shared__ __align__(16) uint32_t smem_all[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const int inst = blockIdx.x * (blockDim.x >> 5) + wic;
@@ -376,7 +397,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_mru_kernel(dls_batch_
   nd.avail = nd.cap;
   nd.fin = 0.0;
   nd.peak = 0.0;
+  nd.tfree = 0.0;
   nd.cnt = 0;
+  double* s_tf = (o.tfin && tl_word >= 0) ? reinterpret_cast<double*>(smem + tl_word) : nullptr;
   int completed = 0, failed = 0, hits = 0, misses = 0, rounds = 0, status = DLS_ST_OK, carried = 0;
   int t = 0;
   while (completed + failed + carried < n) {
@@ -454,6 +477,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_mru_kernel(dls_batch_
         hits += h;
         misses += npar - h;
         if (lane == best) apply_assignment(nd, lb, m, v.dur[i]);
+        if (s_tf) timeline_step(nd, s_tf, v, i, best, lane);
         if (lane == 0) {
           ms.state[i] = 1;
           o.node_of[i] = (int8_t)best;
@@ -536,13 +560,14 @@ static cudaError_t launch_one(Kern kern, int kernel_id, size_t smem, const dls_b
   // Four warps (instances) to a CTA while four slices of shared memory still leave room for several CTAs per SM,
   // else one. Nothing is shared between the warps; it only makes the grid four times smaller, which is what an
   // (almost) empty pick-up launch after the thread-per-DAG kernels costs: 0.07 ms per 131k one-warp CTAs.
-  const size_t slice = (smem + 15) & ~(size_t)15;
+  const size_t base = (smem + 15) & ~(size_t)15;  // the timeline extension's per-task finish times follow the rest
+  const size_t slice = base + (r.tfin ? (((size_t)b.n_max * sizeof(double) + 15) & ~(size_t)15) : 0);
   const int wpc = slice * kWarpsPerCta <= 48 * 1024 ? kWarpsPerCta : 1;
   ctx.why = "cudaFuncSetAttribute(sched kernel)";
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * wpc));
   if (e != cudaSuccess) return e;
   int rec = ctx.prof ? ctx.prof->begin(kernel_id, ctx.st) : -1;
-  kern<<<(b.B + wpc - 1) / wpc, 32 * wpc, slice * wpc, ctx.st>>>(b, r, w, slot, (int)(slice / 4));
+  kern<<<(b.B + wpc - 1) / wpc, 32 * wpc, slice * wpc, ctx.st>>>(b, r, w, slot, (int)(slice / 4), r.tfin ? (int)(base / 4) : -1);
   if (ctx.prof) ctx.prof->end(rec, ctx.st);
   ++ctx.launches;
   ctx.why = "sched kernel launch";

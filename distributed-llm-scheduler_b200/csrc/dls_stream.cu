@@ -909,7 +909,7 @@ size_t smem_mru() {
 // The streamed path needs K <= 8 nodes and per-thread state small enough for a useful number of resident warps.
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit) {
   if (b.K_max > 8) return false;
-  if (r && (r->peak || r->cached)) return false;  // extension outputs are produced by the general kernels only
+  if (r && (r->peak || r->cached || r->tfin)) return false;  // extension outputs are produced by the general kernels only
   return smem_simple<8>() <= (size_t)smem_limit / 2 && b.n_max >= 1;
 }
 

@@ -129,7 +129,7 @@ typedef struct dls_summary {
 /*
  * Caller-allocated outputs. Leading dimension A = number of algorithms in algo_mask
  * (slot s = s-th set bit). NT = batch->nt_inst, NK = batch->nk_inst, NP = batch->np_inst.
- * Nullable: peak, cached.
+ * Nullable: peak, cached, tfin.
  */
 typedef struct dls_result {
   int8_t* node_of;        /* [A][NT] node index, DLS_TASK_FAILED or DLS_TASK_PENDING   Task.assigned_node schedulers.py:93 */
@@ -142,6 +142,13 @@ typedef struct dls_result {
                              between schedulers.py:95 and :126; NULL to skip */
   uint32_t* cached;       /* [A][NP] bit k set = param cached on node k at the end (Node.cached_params,
                              schedulers.py:26,88,428); NULL to skip */
+  double* tfin;           /* [A][NK] extension, no reference counterpart: node finish
+                             time on a DEPENDENCY-AWARE timeline. `fin` follows simulate_execution, which lets a node
+                             run its tasks back to back whatever they depend on (simulation.py:238-271); here a task
+                             starts when its node is free AND all its dependencies have finished:
+                             t_i = max(node free, max finish of deps) + compute_time / compute_speed, tasks taken in
+                             assignment order. The dependency-aware makespan is the maximum over nodes with cnt > 0.
+                             NULL to skip; like peak / cached it is produced by the warp-per-DAG kernels. */
 } dls_result_t;
 
 /* Outputs of the priority pass alone (kernel P). All nullable. Per topology-task arrays have

@@ -47,10 +47,10 @@ def load():
     return _lib
 
 
-def schedule_batch(batch: DagBatch, mask: int = N.MASK_ALL, nthreads: int = 1) -> ResultArrays:
+def schedule_batch(batch: DagBatch, mask: int = N.MASK_ALL, nthreads: int = 1, timeline: bool = False) -> ResultArrays:
     """Oracle twin of dls_b200.schedule_batch on host arrays."""
     lib = load()
-    res = ResultArrays.empty(batch, mask)
+    res = ResultArrays.empty(batch, mask, timeline=timeline)
     bs = batch.host_struct()
     rs = res.host_struct()
     rc = lib.dls_oracle_schedule_batch(C.byref(bs), C.byref(rs), mask, nthreads)

@@ -32,7 +32,7 @@ def test_header_symbols_exported(lib):
 def test_struct_layout_matches_header():
     assert C.sizeof(N.DlsSummary) == 40
     assert C.sizeof(N.DlsBatch) == 8 * 4 + 6 * 8 + 14 * 8
-    assert C.sizeof(N.DlsResult) == 8 * 8 and C.sizeof(N.DlsPrio) == 6 * 8
+    assert C.sizeof(N.DlsResult) == 9 * 8 and C.sizeof(N.DlsPrio) == 6 * 8
 
 
 def test_argument_validation_needs_no_device(lib):

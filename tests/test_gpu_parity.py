@@ -309,3 +309,20 @@ def test_garbage_inputs_are_contained():
         for name in ("order_dg", "order_cp", "order_mru"):
             o = prio[name][b * 200: (b + 1) * 200]
             assert sorted(o.tolist()) == list(range(200)), (name, b)
+
+
+def test_timeline_extension_matches_oracle(oracle_mod):
+    """dls_result_t.tfin (extension: node finish times on a dependency-aware timeline) — no reference output exists
+    for it, so parity is pinned by the oracle only: bit for bit, on random DAGs under memory pressure, on DAGs with
+    shared params and wide dependency lists, and without disturbing any other output."""
+    from dls_b200.gen import random_shared_param_batch
+    for batch in (random_dag_batch(48, 300, 8, 0.8, seed=9), random_shared_param_batch(64, 60, 8, 12, 1.2, seed=4),
+                  random_dag_batch(4, 1000, 4, 1.0, seed=2)):
+        want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=4, timeline=True)
+        got = schedule_batch(batch, N.MASK_ALL, timeline=True).host()
+        np.testing.assert_array_equal(got.tfin, want.tfin)
+        assert (got.tfin >= got.fin).all() and (got.tfin > got.fin).any()
+        plain = schedule_batch(batch, N.MASK_ALL).host()
+        for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail"):
+            np.testing.assert_array_equal(getattr(got, f), getattr(plain, f))
+        np.testing.assert_array_equal(got.dependency_aware_makespan(batch), want.dependency_aware_makespan(batch))

@@ -62,3 +62,29 @@ def test_oracle_priorities_match_definitions(oracle_mod):
         assert pr["order_dg"][ts].tolist() == key(np.zeros(d.n))
         assert pr["order_mru"][ts].tolist() == key(outdeg)
         assert pr["order_cp"][ts].tolist() == key(up)
+
+
+def test_timeline_extension_hand_example(oracle_mod):
+    """dls_result_t.tfin (extension, no reference counterpart): a task starts when its node is free
+    and its dependencies are done. Diamond a -> (b, c) -> d, unit work, two equal nodes with room for everything:
+    Greedy puts a, b, d on the first node and c on the second (first fitting node, then strictly more memory), so
+    simulate_execution's back-to-back finish times are 3 and 1, the dependency-aware ones 3 and 2."""
+    import numpy as np
+    from dls_b200 import _native as N
+    from dls_b200.lowering import DagBatch, LoweredDag
+    dag = LoweredDag(names=["a", "b", "c", "d"], param_names=[], pred_ptr=np.array([0, 0, 1, 2, 4], np.uint32),
+                     pred_idx=np.array([0, 0, 1, 2], np.uint16), par_ptr=np.zeros(5, np.uint32),
+                     par_idx=np.zeros(0, np.uint16), rank=np.arange(4, dtype=np.uint16), mem=np.full(4, 1.0),
+                     dur=np.full(4, 1.0))
+    batch = DagBatch.from_instances([dag], [(np.array([10.0, 10.0]), np.array([1.0, 1.0]))])
+    res = oracle_mod.schedule_batch(batch, 1 << N.ALGO_DFS, timeline=True)
+    seq = res.seq_pos[0].tolist()
+    assert (res.node_of[0] >= 0).all() and seq[0] == 0 and seq[3] == 3
+    # whatever the node choice, d cannot finish before time 3 on a timeline that honours a -> b/c -> d
+    assert res.dependency_aware_makespan(batch)[0, 0] >= 3.0
+    assert (res.tfin >= res.fin).all()
+    # one node only: the timeline is the plain sum, like simulate_execution
+    one = DagBatch.from_instances([dag], [(np.array([10.0]), np.array([2.0]))])
+    r1 = oracle_mod.schedule_batch(one, N.MASK_ALL, timeline=True)
+    np.testing.assert_array_equal(r1.tfin, r1.fin)
+    assert r1.dependency_aware_makespan(one).tolist() == [[2.0]] * 4
