@@ -326,3 +326,45 @@ def test_timeline_extension_matches_oracle(oracle_mod):
         for f in ("node_of", "seq_pos", "summary", "fin", "cnt", "avail"):
             np.testing.assert_array_equal(getattr(got, f), getattr(plain, f))
         np.testing.assert_array_equal(got.dependency_aware_makespan(batch), want.dependency_aware_makespan(batch))
+
+
+def _relabelled(batch, b, perm, K):
+    """Instance b of `batch` with task i renamed perm[i] (same DAG, listed in another order)."""
+    from dls_b200.lowering import LoweredDag
+    ts = batch.task_slice(b)
+    n = ts.stop - ts.start
+    pp = batch.pred_ptr[ts.start + b: ts.stop + b + 1].astype(np.int64)
+    qp = batch.par_ptr[ts.start + b: ts.stop + b + 1].astype(np.int64)
+    pi = batch.pred_idx[batch.pred_off[b]: batch.pred_off[b + 1]]
+    qi = batch.par_idx[batch.par_off[b]: batch.par_off[b + 1]]
+    inv = np.argsort(perm)                      # new index j holds old task inv[j]
+    preds = [perm[pi[pp[i] - pp[0]: pp[i + 1] - pp[0]]] for i in inv]
+    pars = [qi[qp[i] - qp[0]: qp[i + 1] - qp[0]] for i in inv]
+    ks = batch.node_slice(b)
+    dag = LoweredDag(names=[f"t{j}" for j in range(n)], param_names=[f"p{j}" for j in range(int(qi.max()) + 1)],
+                     pred_ptr=np.concatenate([[0], np.cumsum([len(p) for p in preds])]).astype(np.uint32),
+                     pred_idx=np.concatenate(preds).astype(np.uint16) if n else np.zeros(0, np.uint16),
+                     par_ptr=np.concatenate([[0], np.cumsum([len(p) for p in pars])]).astype(np.uint32),
+                     par_idx=np.concatenate(pars).astype(np.uint16), rank=batch.rank[ts][inv].astype(np.uint16),
+                     mem=batch.mem[ts][inv], dur=batch.dur[ts][inv])
+    return dag, (batch.cap[ks].copy(), batch.spd[ks].copy())
+
+
+def test_tasks_listed_in_any_order(oracle_mod):
+    """The reference's generators list every task after its dependencies, and kernel P has a fast pass for that; a
+    DAG listed in any other order (dependencies with larger indices) takes the level-synchronous relaxation instead
+    and must give the reference's answer all the same — reversed, and randomly relabelled."""
+    base = random_dag_batch(24, 180, 8, 0.85, seed=41)
+    rng = np.random.default_rng(5)
+    dags, nodes = [], []
+    for b in range(base.B):
+        perm = np.arange(180)[::-1].copy() if b % 2 == 0 else rng.permutation(180)
+        d, nd = _relabelled(base, b, perm, 8)
+        dags.append(d)
+        nodes.append(nd)
+    batch = DagBatch.from_instances(dags, nodes)
+    assert (batch.pred_idx.astype(np.int64).max() > 0)
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=4)
+    assert (want.summary["status"] == 0).all() and want.summary["completed"].sum() > 0
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} relabelled tasks")
