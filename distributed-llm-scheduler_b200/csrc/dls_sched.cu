@@ -562,7 +562,7 @@ static cudaError_t launch_one(Kern kern, int kernel_id, size_t smem, const dls_b
   // (almost) empty pick-up launch after the thread-per-DAG kernels costs: 0.07 ms per 131k one-warp CTAs.
   const size_t base = (smem + 15) & ~(size_t)15;  // the timeline extension's per-task finish times follow the rest
   const size_t slice = base + (r.tfin ? (((size_t)b.n_max * sizeof(double) + 15) & ~(size_t)15) : 0);
-  const int wpc = slice * kWarpsPerCta <= 48 * 1024 ? kWarpsPerCta : 1;
+  const int wpc = slice * kWarpsPerCta <= 100 * 1024 ? kWarpsPerCta : 1;
   ctx.why = "cudaFuncSetAttribute(sched kernel)";
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * wpc));
   if (e != cudaSuccess) return e;
