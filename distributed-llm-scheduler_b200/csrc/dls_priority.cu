@@ -251,7 +251,9 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   __syncthreads();
   // keep the flags: after the scan, flag[p] = (scan[p+1] != scan[p])
   const uint32_t nsh = block_exclusive_scan(s_rc, P + 1, s_part);
-  for (int p = tid; p < P; p += blockDim.x) g_sid[p] = (s_rc[p + 1] != s_rc[p]) ? (uint16_t)s_rc[p] : (uint16_t)0xFFFF;
+  // (a DAG without shared params — every DAG of a random sweep — needs no table: its readers test nshared first)
+  if (nsh != 0)
+    for (int p = tid; p < P; p += blockDim.x) g_sid[p] = (s_rc[p + 1] != s_rc[p]) ? (uint16_t)s_rc[p] : (uint16_t)0xFFFF;
   if (tid == 0) w.nshared[t] = (int)nsh;
 }
 

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
     const int npred = (int)(v.pred_ptr[i + 1] - v.pred_ptr[i]);
     int extra = max(0, npred - 3);
     const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-    if (kind != kStreamMRU) {  // (the MRU stream only ever holds DAGs without shared params)
+    if (kind != kStreamMRU && nsh_topo > 0) {  // (no shared param in the DAG: nothing to look up, par_sid not even written)
       int nsh = 0;
       for (uint32_t e = qb; e < qe; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
       extra += max(0, nsh - 2);
@@ -91,8 +91,8 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
     }
     const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
     rc.a0 = rc.a1 = 0;
-    if (kind == kStreamMRU) {
-      rc.npriv = (uint16_t)(qe - qb);  // all private: the count is all the MRU kernel needs
+    if (kind == kStreamMRU || nsh_topo == 0) {
+      rc.npriv = (uint16_t)(qe - qb);  // all private: the count is all the kernels need
       rc.nsh = 0;
     } else {
       int nsh = 0, npriv = 0;
