@@ -92,6 +92,7 @@ dls::Workspace carve(void* base, const Layout& L) {
   w.succ_idx = reinterpret_cast<uint16_t*>(p + L.off_succ_idx);
   w.topo_status = reinterpret_cast<int32_t*>(p + L.off_status);
   w.cp_per_instance = L.cp_per_instance;
+  w.keep_up = 0;
   w.par_sid = nullptr; w.nshared = nullptr; w.node_pos = nullptr; w.route = nullptr;
   for (int k = 0; k < 3; ++k) { w.stream[k] = nullptr; w.ext[k] = nullptr; }
   if (L.stream) {
@@ -360,7 +361,8 @@ int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, 
   const Layout L = layout_of(*batch);
   if (!workspace || workspace_bytes < L.total) return fail(DLS_ERR_WORKSPACE, "workspace smaller than dls_workspace_bytes()");
   if (reinterpret_cast<uintptr_t>(workspace) % kAlign) return fail(DLS_ERR_WORKSPACE, "workspace must be 256-byte aligned");
-  const dls::Workspace w = carve(workspace, L);
+  dls::Workspace w = carve(workspace, L);
+  w.keep_up = 1;
   dls::LaunchCtx ctx;
   ctx.st = static_cast<cudaStream_t>(cuda_stream);
   ctx.prof = g_prof.on ? &g_prof : nullptr;

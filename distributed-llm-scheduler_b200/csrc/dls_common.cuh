@@ -27,6 +27,7 @@ struct Workspace {
   uint16_t* succ_idx;   // [e_total]
   int32_t* topo_status; // [T]         0 ok, DLS_ST_BAD_TOPOLOGY
   int cp_per_instance;  // order_cp/up indexed per instance (T==B or per-instance durations) or per topology
+  int keep_up;          // the upward ranks are an output (dls_priorities); the scheduling call only needs the order they give
   // ---- streamed (thread-per-DAG) path; all null when that path is not used ----
   uint16_t* par_sid;    // [np_topo]   dense id of a param shared by >= 2 tasks, 0xFFFF if private to one task
   int32_t* nshared;     // [T]

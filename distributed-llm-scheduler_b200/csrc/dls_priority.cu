@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     double lo = INFINITY, hi = -INFINITY;
     for (int i = tid; i < n; i += blockDim.x) {
       const double u = s_up[i];
-      w.up[cp_off + i] = u;
+      if (w.keep_up) w.up[cp_off + i] = u;
       lo = fmin(lo, u);
       hi = fmax(hi, u);
     }
@@ -407,7 +407,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_
     }
     return;
   }
-  for (int i = tid; i < n; i += blockDim.x) w.up[cp_off + i] = s_up[i];
+  if (w.keep_up)
+    for (int i = tid; i < n; i += blockDim.x) w.up[cp_off + i] = s_up[i];
   __syncthreads();
   for (int q = tid; q < n; q += blockDim.x) {
     const int i = s_ord[q];
