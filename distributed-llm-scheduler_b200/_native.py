@@ -14,7 +14,8 @@ import threading
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(PKG_DIR)
 CSRC_DIR = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.path.join(PKG_DIR, "libdls_b200.so")
+# DLS_B200_LIB: load another build of the same sources instead (kernel A/B measurements, tools/build_variant.py)
+LIB_PATH = os.environ.get("DLS_B200_LIB") or os.path.join(PKG_DIR, "libdls_b200.so")
 INCLUDE_DIR = os.path.join(REPO_ROOT, "include")
 
 ALGO_DFS, ALGO_GREEDY, ALGO_CRITICAL, ALGO_MRU = 0, 1, 2, 3
@@ -44,15 +45,15 @@ class DlsBatch(C.Structure):
 
 class DlsSummary(C.Structure):
     _fields_ = [
-        ("makespan", C.c_double), ("completed", C.c_int32), ("failed", C.c_int32), ("pending", C.c_int32),
+        ("makespan", C.c_double), ("peak", C.c_double), ("completed", C.c_int32), ("failed", C.c_int32), ("pending", C.c_int32),
         ("hits", C.c_int32), ("misses", C.c_int32), ("rounds", C.c_int32), ("status", C.c_int32),
         ("reserved", C.c_int32),
     ]
 
 
-SUMMARY_BYTES = C.sizeof(DlsSummary)  # 40
+SUMMARY_BYTES = C.sizeof(DlsSummary)  # 48
 SUMMARY_DTYPE = [
-    ("makespan", "<f8"), ("completed", "<i4"), ("failed", "<i4"), ("pending", "<i4"), ("hits", "<i4"),
+    ("makespan", "<f8"), ("peak", "<f8"), ("completed", "<i4"), ("failed", "<i4"), ("pending", "<i4"), ("hits", "<i4"),
     ("misses", "<i4"), ("rounds", "<i4"), ("status", "<i4"), ("reserved", "<i4"),
 ]
 
@@ -109,12 +110,14 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/*.cu for sm_100a into libdls_b200.so, in-tree (so it travels to the GPU box)."""
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, defines=(), out: str = None) -> str:
+    """Compile csrc/*.cu for sm_100a into libdls_b200.so, in-tree (so it travels to the GPU box). `defines` / `out`
+    build a variant library next to it (extra -D macros) for A/B measurements."""
+    out = out or LIB_PATH
+    if not force and not defines and out == LIB_PATH and not needs_build():
         return LIB_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc] + NVCC_FLAGS + ["-I", INCLUDE_DIR, "-I", CSRC_DIR, "-o", LIB_PATH] + sources()
+    cmd = [nvcc] + NVCC_FLAGS + [f"-D{d}" for d in defines] + ["-I", INCLUDE_DIR, "-I", CSRC_DIR, "-o", out] + sources()
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     proc = subprocess.run(cmd, capture_output=True, text=True)
@@ -122,7 +125,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout + proc.stderr)
     if verbose:
         print(proc.stderr)
-    return LIB_PATH
+    return out
 
 
 _lib = None

@@ -30,28 +30,33 @@ struct Workspace {
   int keep_up;          // the upward ranks are an output (dls_priorities); the scheduling call only needs the order they give
   // ---- streamed (thread-per-DAG) path; all null when that path is not used ----
   uint16_t* par_sid;    // [np_topo]   dense id of a param shared by >= 2 tasks, 0xFFFF if private to one task
-  int32_t* nshared;     // [T]
-  struct Rec* stream[3];   // [nt_inst] task records in processing order: 0 DFS/Greedy, 1 Critical, 2 MRU
-  uint16_t* ext[3];        // overflow lists (dependencies beyond 3, params beyond 2), e+r entries per instance
+  int32_t* nshared;     // [T]         shared params of the topology; kUnstreamable = leave the DAG to the general kernels
+  struct Rec* rec_topo; // [nt_topo]   one record per task, in TASK order, written by the topology kernel
+  struct Rec* rec_inst; // [nt_inst]   the records the scheduling threads read: rec_topo itself when T == B, else a copy per
+                        //             instance with that instance's duration / memory (record_expand_kernel)
   int8_t* node_pos;     // [A][nt_inst] verdict per order position (node, -1 failed, -2 pending)
   uint8_t* route;       // [A][B]      1 = instance left to the warp-per-DAG kernel
 };
 
-// One task in processing order, everything kernel S needs for a step in 32 bytes (one DRAM sector).
+// One task, everything kernel S needs for a step in 32 bytes (one DRAM sector, read by one 256-bit load). The record
+// does not depend on the processing order: dependencies are task ids, and "a new round starts here" is the parity of
+// the task's depth changing (the orders list depth 0, 1, 2, ... without gaps). So ONE array of records per instance,
+// in task order, serves all four algorithms; each scheduling thread visits it through its own order array.
 struct __align__(16) Rec {
   double m;          // Task.memory_required
   double c;          // Task.compute_time
-  uint16_t pred[3];  // order positions of the first three dependencies
-  uint16_t npred;    // number of dependencies (beyond 3: ext list)
-  uint16_t a0, a1;   // first two shared-param ids (0 in the MRU stream, which only holds DAGs without shared params)
-  uint16_t npriv;    // DFS/Greedy/Critical: params private to this task; MRU: all params of the task
-  uint8_t nsh;       // shared params of the task (beyond 2: ext list); 255 = too many, instance routed to the slow kernel
-  uint8_t flags;     // bit0: first task of a round
+  uint16_t pred[3];  // task ids of the first three dependencies (the rest: pred_idx of the input, from pred_ptr[id] + 3)
+  uint16_t id;       // the task itself (what a thread that reads records sequentially needs for its done-bitmap)
+  uint16_t a0, a1;   // first two shared-param ids (with more than two: all of them are looked up through par_idx / par_sid)
+  uint16_t npriv;    // params private to this task
+  uint8_t npred;     // number of dependencies (255 and more: DAG left to the general kernels)
+  uint8_t nsh_par;   // bits 0-6: shared params of the task (127 and more: general kernels); bit 7: depth & 1
 };
 static_assert(sizeof(Rec) == 32, "Rec must be one 32-byte sector");
-constexpr int kRecFirst = 1;
-constexpr int kStreamDG = 0, kStreamCP = 1, kStreamMRU = 2;
+constexpr int kRecParity = 0x80;
+constexpr int kOrderDG = 0, kOrderCP = 1, kOrderMRU = 2;  // which of kernel P's orders an algorithm slot walks
 constexpr int kSharedCap = 32;   // shared params per DAG the streamed DFS/Greedy/Critical kernel keeps masks for
+constexpr int kUnstreamable = 0x7fffffff;  // value of nshared[t] for DAGs a record cannot describe
 
 // One DAG instance resolved against the batch descriptor.
 struct Inst {
@@ -258,7 +263,7 @@ cudaError_t launch_aggregate(const dls_batch_t& b, const dls_result_t& r, int ns
                              double* out, LaunchCtx& ctx);
 cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_count, LaunchCtx& ctx);
 cudaError_t launch_gen_fill(const dls_gen_t& g, const dls_batch_t& out, LaunchCtx& ctx);
-cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
+cudaError_t launch_record_expand(const dls_batch_t& b, const Workspace& w, LaunchCtx& ctx);
 cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                 LaunchCtx& ctx);
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit);

@@ -53,6 +53,43 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   uint32_t* g_succ_ptr = w.succ_ptr + v.t_topo + t;
   uint16_t* g_succ_idx = w.succ_idx + b.pred_off[t];
 
+  // With the streamed path on, param_class_kernel has run first: it has checked the param CSR and left the number of
+  // shared params; a topology it rejected is not looked at again.
+  const bool classed = w.nshared != nullptr;
+  if (classed && w.topo_status[t] != DLS_ST_OK) return;
+  const int nsh_topo = classed ? w.nshared[t] : 0;
+  Rec* g_rec = w.rec_topo ? w.rec_topo + v.t_topo : nullptr;
+  const double* g_mem = b.mem + v.t_topo;  // (T == 1 with per-instance values: row 0; record_expand_kernel puts in the rest)
+  const double* g_dur = b.dur + v.t_topo;
+  const uint16_t* g_sid = classed ? w.par_sid + b.pid_off[t] : nullptr;
+  int unstreamable = 0;
+  // The record of task i (dls::Rec): what a scheduling thread needs for one step, whatever the processing order.
+  auto emit_record = [&](int i, uint32_t np, uint32_t p0, uint32_t p1, uint32_t p2, int depth, double m, double c,
+                         uint32_t qb, uint32_t qe) {
+    uint32_t nsh = 0, a0 = 0, a1 = 0, npriv = qe - qb;
+    if (nsh_topo > 0) {
+      npriv = 0;
+      for (uint32_t e = qb; e < qe; ++e) {
+        const uint32_t sd = g_sid[__ldg(v.par_idx + e)];
+        if (sd == 0xFFFF) { ++npriv; continue; }
+        if (nsh == 0) a0 = sd;
+        else if (nsh == 1) a1 = sd;
+        ++nsh;
+      }
+    }
+    if (np >= 255u || nsh >= 127u || npriv > 65535u) { unstreamable = 1; np = min(np, 255u); nsh = min(nsh, 127u); npriv = min(npriv, 65535u); }
+    uint4 lo, hi;
+    lo.x = (uint32_t)__double2loint(m); lo.y = (uint32_t)__double2hiint(m);
+    lo.z = (uint32_t)__double2loint(c); lo.w = (uint32_t)__double2hiint(c);
+    hi.x = (np > 0 ? p0 : 0u) | ((np > 1 ? p1 : 0u) << 16);
+    hi.y = (np > 2 ? p2 : 0u) | ((uint32_t)i << 16);
+    hi.z = a0 | (a1 << 16);
+    hi.w = npriv | (np << 16) | (nsh << 24) | ((uint32_t)(depth & 1) << 31);
+    uint4* dst = reinterpret_cast<uint4*>(g_rec + i);
+    dst[0] = lo;
+    dst[1] = hi;
+  };
+
   if (tid == 0) { s_maxd = 0; s_maxdeg = 0; }
   __syncthreads();
   // ---- validate the descriptor slice (never trust indices that address shared memory) ----
@@ -127,6 +164,10 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     // repeated only while one of its tasks still depends on another task of the same chunk whose depth moved.
     for (int base = 0; base < n; base += blockDim.x) {
       const int i = base + tid;
+      // (the record's values from global memory: in flight while the chunk's depths settle)
+      double rm = 0.0, rc = 0.0;
+      uint32_t rqb = 0, rqe = 0;
+      if (g_rec && i < n) { rm = __ldg(g_mem + i); rc = __ldg(g_dur + i); rqb = __ldg(v.par_ptr + i); rqe = __ldg(v.par_ptr + i + 1); }
       const uint32_t eb = i < n ? pptr[i] : 0, ee = i < n ? pptr[i + 1] : 0, np = ee - eb;
       const uint32_t p0 = np > 0 ? pidx[eb] : 0, p1 = np > 1 ? pidx[eb + 1] : 0, p2 = np > 2 ? pidx[eb + 2] : 0;
       const bool inside = (np > 0 && (int)p0 >= base) || (np > 1 && (int)p1 >= base) || (np > 2 && (int)p2 >= base) || np > 3;
@@ -144,6 +185,7 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
         if (moved) s_depth[i] = (uint16_t)d;
         again = __syncthreads_or(moved) && any_inside;
       } while (again);
+      if (g_rec && i < n) emit_record(i, np, p0, p1, p2, (int)s_depth[i], rm, rc, rqb, rqe);
     }
     __syncthreads();
   } else {
@@ -165,6 +207,16 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   if (changed) {
     if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
     return;
+  }
+  if (g_rec && unsorted) {  // (the in-order pass above writes the records as it goes)
+    for (int i = tid; i < n; i += blockDim.x) {
+      const uint32_t eb = pptr[i], np = pptr[i + 1] - eb;
+      emit_record(i, np, np > 0 ? pidx[eb] : 0, np > 1 ? pidx[eb + 1] : 0, np > 2 ? pidx[eb + 2] : 0, (int)s_depth[i],
+                  __ldg(g_mem + i), __ldg(g_dur + i), __ldg(v.par_ptr + i), __ldg(v.par_ptr + i + 1));
+    }
+  }
+  if (g_rec && __syncthreads_or(unstreamable)) {
+    if (tid == 0) w.nshared[t] = kUnstreamable;  // a count no record can hold: the general kernels take this DAG
   }
   if (tid == 0) w.topo_status[t] = DLS_ST_OK;
   {
@@ -220,40 +272,51 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   }
 }
 
-// Classify params of one topology (one CTA each):
-//   par_sid[p] = dense id among params referenced by >= 2 tasks ("shared"), 0xFFFF for params private to one task;
-//   nshared[t] = number of shared params.
+// Classify params of one topology (one CTA each); the first kernel of a scheduling call on the streamed path:
+//   topo_status[t] = OK, or BAD_TOPOLOGY when the param CSR is inconsistent with the descriptor;
+//   nshared[t]    = number of params referenced by >= 2 tasks ("shared");
+//   par_sid[p]    = dense id among the shared params, 0xFFFF for params private to one task (written only if any).
 // Tasks whose params are all private cost the same on every node (nothing of theirs is ever cached when they are
 // looked at), which is what the thread-per-DAG kernels build their short cuts on.
+// Most DAGs of a sweep have no shared param at all. That is settled without counting: every reference writes its
+// own index into its param's slot, and a second look finds a foreign index exactly where a param has two references.
 __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, Workspace w) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_part[33];
   const int t = blockIdx.x, tid = threadIdx.x;
   Inst v;
   bind_topology(b, t, v);
-  if (w.topo_status[t] != DLS_ST_OK) return;
   const int P = v.P;
+  if (tid == 0) w.nshared[t] = 0;
+  if (v.n > b.n_max || P > b.P_max || P < 0 || v.n < 0 || v.E > (uint32_t)b.E_max || v.R > (uint32_t)b.R_max) {
+    if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;  // descriptor maxima are what shared memory was sized for
+    return;
+  }
   uint32_t* s_rc = reinterpret_cast<uint32_t*>(smem_raw);             // [P+2]
   uint16_t* g_sid = w.par_sid + b.pid_off[t];
-  for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
-  __syncthreads();
   int bad = 0;
   strided_for<8>((int)v.R, [&](int e) {
     const int p = __ldg(v.par_idx + e);
-    if (p < P) atomicAdd(&s_rc[p], 1u);
+    if (p < P) s_rc[p] = (uint32_t)e;
     else bad = 1;  // never trust an index that addresses shared memory
   });
   if (__syncthreads_or(bad)) {
     if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
     return;
   }
+  if (tid == 0) w.topo_status[t] = DLS_ST_OK;
+  int twice = 0;
+  strided_for<8>((int)v.R, [&](int e) { twice |= s_rc[__ldg(v.par_idx + e)] != (uint32_t)e; });
+  if (!__syncthreads_or(twice)) return;  // nshared[t] = 0 stands; par_sid is not read for such a DAG
+  for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
+  __syncthreads();
+  strided_for<8>((int)v.R, [&](int e) { atomicAdd(&s_rc[__ldg(v.par_idx + e)], 1u); });
+  __syncthreads();
   for (int p = tid; p < P; p += blockDim.x) s_rc[p] = s_rc[p] >= 2 ? 1u : 0u;
   __syncthreads();
   // keep the flags: after the scan, flag[p] = (scan[p+1] != scan[p])
   const uint32_t nsh = block_exclusive_scan(s_rc, P + 1, s_part);
-  // (a DAG without shared params — every DAG of a random sweep — needs no table: its readers test nshared first)
-  if (nsh != 0)
-    for (int p = tid; p < P; p += blockDim.x) g_sid[p] = (s_rc[p + 1] != s_rc[p]) ? (uint16_t)s_rc[p] : (uint16_t)0xFFFF;
+  for (int p = tid; p < P; p += blockDim.x) g_sid[p] = (s_rc[p + 1] != s_rc[p]) ? (uint16_t)s_rc[p] : (uint16_t)0xFFFF;
   if (tid == 0) w.nshared[t] = (int)nsh;
 }
 
@@ -444,19 +507,7 @@ size_t priority_smem_inst(int n_max, bool with_key) {
 
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
   cudaError_t e;
-  size_t sm1 = priority_smem_topo(b.n_max, b.E_max);
-  const int stage = 1;
-  ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
-  e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-  if (e != cudaSuccess) return e;
-  int rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
-  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage,
-                                                            w.par_sid ? 0 : 1);
-  if (ctx.prof) ctx.prof->end(rec, ctx.st);
-  ++ctx.launches;
-  ctx.why = "priority_topology_kernel launch";
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  int rec;
   if (w.par_sid) {
     size_t smp = priority_smem_param(b.n_max, b.P_max);
     ctx.why = "cudaFuncSetAttribute(param_class_kernel)";
@@ -470,6 +521,19 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
+  size_t sm1 = priority_smem_topo(b.n_max, b.E_max);
+  const int stage = 1;
+  ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
+  e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+  if (e != cudaSuccess) return e;
+  rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
+  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage,
+                                                            w.par_sid ? 0 : 1);
+  if (ctx.prof) ctx.prof->end(rec, ctx.st);
+  ++ctx.launches;
+  ctx.why = "priority_topology_kernel launch";
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
     size_t sm2 = priority_smem_inst(b.n_max, true);
     const int use_key = sm2 <= 96 * 1024;

@@ -60,6 +60,7 @@ __device__ void write_unscheduled(const OutPtrs& o, const Inst& v, int lane, int
   if (lane == 0) {
     dls_summary_t s;
     s.makespan = 0.0;
+    s.peak = 0.0;
     s.completed = 0; s.failed = 0; s.pending = v.n; s.hits = 0; s.misses = 0; s.rounds = 0;
     s.status = status; s.reserved = 0;
     *o.summary = s;
@@ -86,9 +87,13 @@ __device__ __forceinline__ void epilogue(const OutPtrs& o, const Inst& v, int la
     if (o.peak) o.peak[lane] = nd.peak;
     if (o.tfin) o.tfin[lane] = nd.tfree;
   }
+  double pk = (o.peak && lane < v.K) ? nd.peak : 0.0;  // dls_summary_t.peak: the largest node peak, when peaks are asked for
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) pk = fmax(pk, __shfl_xor_sync(DLS_FULL_MASK, pk, off));
   if (lane == 0) {
     dls_summary_t s;
     s.makespan = completed > 0 ? mk : 0.0;
+    s.peak = pk;
     s.completed = completed; s.failed = failed; s.pending = v.n - completed - failed;
     s.hits = hits; s.misses = misses; s.rounds = rounds; s.status = status; s.reserved = 0;
     *o.summary = s;

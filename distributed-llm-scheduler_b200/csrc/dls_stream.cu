@@ -1,17 +1,21 @@
-// dls_stream.cu — the throughput path: one THREAD per DAG instance over an order-permuted record stream.
+// dls_stream.cu — the throughput path: one THREAD per DAG instance.
 //
 // Why: the list-scheduling loop is a serial chain of n dependent steps per DAG, but a sweep has ~10^5..10^6
 // independent DAGs. With one warp per DAG every instruction of the chain serves one DAG (≈340 warp-instructions per
-// task-step, profiles/r1a_*); with one thread per DAG the same instruction serves 32. To make that work the
-// per-thread memory accesses must not scatter: stream_build_kernel rewrites each DAG, once per processing order, as
-// a contiguous array of 32-byte records (one DRAM sector per step, dependencies already translated to order
-// positions), so every step of every thread reads exactly one fully used sector, and per-thread mutable state lives
-// in shared memory laid out [word][lane] (each lane owns a bank: no conflicts whatever the index).
+// task-step, profiles/r1a_*); with one thread per DAG the same instruction serves 32. To make that work a step must
+// cost a thread ONE memory access: kernel P leaves, per instance, one array of 32-byte task records (dls::Rec, one
+// DRAM sector each, in task order, independent of the processing order) next to the three static orders, and a
+// scheduling thread walks `rec[order[t]]`: the order indices arrive eight at a time (one 16-byte load per eight
+// steps), the record by one 256-bit load issued two steps ahead. Per-thread mutable state lives in shared memory laid
+// out [word][lane] (each lane owns a bank: no conflicts whatever the index), including one done-bit per task.
+// (Round 1 rewrote every instance three times into order-permuted record streams so that the threads could read
+// sequentially: 96 KB written and read back per 1k-task instance and a 4.3 ms kernel for 131k instances.)
 //
-// Verdicts are written in order-position space (sequential bytes per thread); unpermute_kernel maps them back to
-// task ids and derives seq_pos by a prefix count. Instances the fast kernels cannot take (more than 8 nodes, more
-// than 32 shared params, MRU with any shared param, bad topology) are flagged in `route` and picked up by the
-// warp-per-DAG kernels of dls_sched.cu, which remain the general implementation.
+// Verdicts are written in order-position space (sequential bytes per thread, stored a word at a time);
+// unpermute_kernel maps them back to task ids and derives seq_pos by a prefix count. Instances the fast kernels
+// cannot take (more than 8 nodes, more than 32 shared params, MRU with any shared param, a task with 255+
+// dependencies, bad topology) are flagged in `route` and picked up by the warp-per-DAG kernels of dls_sched.cu, which
+// remain the general implementation.
 //
 // All fp64 arithmetic is the same op-by-op replay as in dls_sched.cu (see the header comment there).
 #include <math.h>
@@ -28,259 +32,26 @@ namespace {
 constexpr int kRouteGeneral = 1, kRouteFailRest = 2, kRouteTwin = 4, kRouteOpen = 0xFF;
 constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG DFS/Greedy/Critical kernels
 constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp CTAs, 7 instead of 6 warps/SM, are slower)
-constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
-
-__device__ __forceinline__ int64_t ext_offset(const dls_batch_t& b, int inst, const Inst& v) {
-  return b.T == 1 ? (int64_t)inst * (int64_t)(v.E + v.R) : b.pred_off[inst] + b.par_off[inst];
-}
+constexpr int kBitmapWordsMax = 64;  // done-bits in shared memory up to 2048 tasks per DAG; beyond, done-bytes in HBM
 
 // -------------------------------------------------------------------------------------------------------------------
-// stream_build_kernel: grid (B, 3). One CTA rewrites one instance for one processing order.
+// record_expand_kernel: T == 1 (one topology, B instances). The topology kernel wrote one record per task; every
+// instance gets its own copy, with its own duration / memory where the batch carries them per instance.
 // -------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t b, Workspace w, int kind_mask) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ uint32_t s_part[33];
-  const int inst = blockIdx.x, kind = blockIdx.y, tid = threadIdx.x;
-  if (!((kind_mask >> kind) & 1)) return;
-  Inst v;
-  bind_instance(b, inst, v);
-  if (w.topo_status[v.topo] != DLS_ST_OK) return;
-  const int n = v.n;
-  if (n == 0) return;
-  const int nsh_topo = w.nshared[v.topo];
-  if (kind == kStreamMRU ? nsh_topo != 0 : nsh_topo > kSharedCap) return;  // routed to the general kernels
-  uint32_t* s_extoff = reinterpret_cast<uint32_t*>(smem_raw);           // [n+1]
-  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));    // [n] task -> order position
-  const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
-                        : kind == kStreamMRU ? w.order_mru + v.t_topo
-                                             : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
-  const uint16_t* depth = w.depth + v.t_topo;
-  const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
-  Rec* out = w.stream[kind] + v.t_inst;
-  uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
-
-  for (int t = tid; t < n; t += blockDim.x) {
-    const int i = order[t];
-    s_pos[i] = (uint16_t)t;
-    const int npred = (int)(v.pred_ptr[i + 1] - v.pred_ptr[i]);
-    int extra = max(0, npred - 3);
-    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-    if (kind != kStreamMRU && nsh_topo > 0) {  // (no shared param in the DAG: nothing to look up, par_sid not even written)
-      int nsh = 0;
-      for (uint32_t e = qb; e < qe; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
-      extra += max(0, nsh - 2);
-    }
-    s_extoff[t] = (uint32_t)extra;
-  }
-  if (tid == 0) s_extoff[n] = 0;
-  __syncthreads();
-  block_exclusive_scan(s_extoff, n + 1, s_part);
-  for (int t = tid; t < n; t += blockDim.x) {
-    const int i = order[t];
-    Rec rc;
-    rc.m = v.mem[i];
-    rc.c = v.dur[i];
-    const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
-    uint32_t xo = s_extoff[t];
-    rc.pred[0] = rc.pred[1] = rc.pred[2] = 0;
-    rc.npred = (uint16_t)min(pe - pb, 65535u);
-    for (uint32_t e = pb; e < pe; ++e) {
-      const uint16_t pp = s_pos[v.pred_idx[e]];
-      if (e - pb < 3) rc.pred[e - pb] = pp;
-      else ext[xo++] = pp;
-    }
-    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-    rc.a0 = rc.a1 = 0;
-    if (kind == kStreamMRU || nsh_topo == 0) {
-      rc.npriv = (uint16_t)(qe - qb);  // all private: the count is all the kernels need
-      rc.nsh = 0;
-    } else {
-      int nsh = 0, npriv = 0;
-      for (uint32_t e = qb; e < qe; ++e) {
-        const uint16_t s = sid[v.par_idx[e]];
-        if (s == 0xFFFF) { ++npriv; continue; }
-        if (nsh == 0) rc.a0 = s;
-        else if (nsh == 1) rc.a1 = s;
-        else ext[xo++] = s;
-        ++nsh;
-      }
-      rc.npriv = (uint16_t)npriv;
-      rc.nsh = (uint8_t)min(nsh, 255);
-    }
-    rc.flags = (t == 0 || depth[order[t - 1]] != depth[i]) ? kRecFirst : 0;
-    out[t] = rc;
-  }
-}
-
-// -------------------------------------------------------------------------------------------------------------------
-// stream_build_staged_kernel: grid B. One CTA per instance builds all requested streams.
-// Phase 1 reads the instance's arrays ONCE, in task order (fully coalesced), into task-indexed 32-byte records in
-// shared memory. Phase 2, per processing order, permutes them through shared memory and writes the stream
-// coalesced. Used when the staged records fit shared memory (n up to ~5.5k); otherwise stream_build_kernel.
-// -------------------------------------------------------------------------------------------------------------------
-// A task as staged in shared memory, in two 16-byte halves kept in two arrays: with 32-byte records every first half
-// starts on one of only four bank groups, and the gather by processing order ran at 3.5 wavefronts per ideal one
-// (ncu source view, round 1i); 16-byte strides spread the same gather over all eight.
-struct __align__(16) TaskLo {
-  double m, c;
-};
-struct __align__(16) TaskHi {  // dependencies still as task ids
-  uint16_t pred[3];
-  uint16_t npred;
-  uint16_t npar;
-  uint16_t depth;
-  uint32_t pad;
-};
-struct TaskRec {
-  TaskLo lo;
-  TaskHi hi;
-};
-static_assert(sizeof(TaskLo) == 16 && sizeof(TaskHi) == 16, "two 16-byte halves");
-
-// The record of task `i` (staged as `tr`) for one stream, all but the round flag. `posk`: task -> position in that
-// order; ext lists (dependencies beyond three, shared params beyond two) start at ext[xo].
-__device__ __forceinline__ Rec make_rec(int kind, const TaskRec& tr, int i, const Inst& v, int nsh_topo, const uint16_t* sid,
-                                        const uint16_t* posk, uint16_t* ext, uint32_t xo) {
-  Rec rc;
-  rc.m = tr.lo.m;
-  rc.c = tr.lo.c;
-  rc.npred = tr.hi.npred;
-  rc.pred[0] = posk[tr.hi.pred[0]];  // unused slots hold task 0: a valid index, masked by the count
-  rc.pred[1] = posk[tr.hi.pred[1]];
-  rc.pred[2] = posk[tr.hi.pred[2]];
-  if (tr.hi.npred > 3) {
-    const uint32_t pb = v.pred_ptr[i], pe = v.pred_ptr[i + 1];
-    for (uint32_t e = pb + 3; e < pe; ++e) ext[xo++] = posk[v.pred_idx[e]];
-  }
-  rc.a0 = rc.a1 = 0;
-  if (kind == kStreamMRU || nsh_topo == 0) {
-    rc.npriv = tr.hi.npar;  // every param private: the count is all the kernels need
-    rc.nsh = 0;
-  } else {
-    int nsh = 0, npriv = 0;
-    const uint32_t qb = v.par_ptr[i], qe = v.par_ptr[i + 1];
-    for (uint32_t e = qb; e < qe; ++e) {
-      const uint16_t sd = sid[v.par_idx[e]];
-      if (sd == 0xFFFF) { ++npriv; continue; }
-      if (nsh == 0) rc.a0 = sd;
-      else if (nsh == 1) rc.a1 = sd;
-      else ext[xo++] = sd;
-      ++nsh;
-    }
-    rc.npriv = (uint16_t)npriv;
-    rc.nsh = (uint8_t)min(nsh, 255);
-  }
-  rc.flags = 0;
-  return rc;
-}
-
-__global__ void __launch_bounds__(kBuildThreads) stream_build_staged_kernel(dls_batch_t b, Workspace w, int kind_mask) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ uint32_t s_part[33];
-  const int inst = blockIdx.x, tid = threadIdx.x;
-  Inst v;
-  bind_instance(b, inst, v);
-  if (w.topo_status[v.topo] != DLS_ST_OK) return;
-  const int n = v.n;
-  if (n == 0) return;
-  const int nsh_topo = w.nshared[v.topo];
-  const int n_al = (n + 1) & ~1;
-  TaskLo* s_lo = reinterpret_cast<TaskLo*>(smem_raw);                        // [n]
-  TaskHi* s_hi = reinterpret_cast<TaskHi*>(s_lo + n);                        // [n]
-  uint32_t* s_extoff = reinterpret_cast<uint32_t*>(s_hi + n);                // [n+1]
-  uint16_t* s_pos = reinterpret_cast<uint16_t*>(s_extoff + (n + 1));         // [3][n_al] task -> position, per order
-  uint16_t* s_depth = s_pos + 3 * n_al;                                      // [n_al] compact copy for the round starts
-  const uint16_t* depth = w.depth + v.t_topo;
-  const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
-  const uint16_t* g_order[3] = {w.order_dg + v.t_topo, w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo),
-                                w.order_mru + v.t_topo};
-  static_assert(kStreamDG == 0 && kStreamCP == 1 && kStreamMRU == 2, "order table follows the stream kinds");
-  bool use[3];
-#pragma unroll
-  for (int kind = 0; kind < 3; ++kind)  // DAGs the thread-per-DAG kernels leave to the general ones get no stream
-    use[kind] = ((kind_mask >> kind) & 1) && (kind == kStreamMRU ? nsh_topo == 0 : nsh_topo <= kSharedCap);
-  // ---- phase 1: task-order gather (a thread keeps several tasks' loads in flight), and the orders inverted ----
-  int any_ext = 0;
-  strided_for<4>(n, [&](int i) {
-#pragma unroll
-    for (int kind = 0; kind < 3; ++kind)
-      if (use[kind]) s_pos[kind * n_al + __ldg(g_order[kind] + i)] = (uint16_t)i;
-    TaskLo lo;
-    TaskHi tr;
-    lo.m = __ldg(v.mem + i);
-    lo.c = __ldg(v.dur + i);
-    const uint32_t pb = __ldg(v.pred_ptr + i), pe = __ldg(v.pred_ptr + i + 1);
-    const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
-    tr.npred = (uint16_t)min(pe - pb, 65535u);
-    tr.npar = (uint16_t)min(qe - qb, 65535u);
-    tr.pred[0] = pe - pb > 0 ? __ldg(v.pred_idx + pb) : 0;
-    tr.pred[1] = pe - pb > 1 ? __ldg(v.pred_idx + pb + 1) : 0;
-    tr.pred[2] = pe - pb > 2 ? __ldg(v.pred_idx + pb + 2) : 0;
-    tr.pad = 0;
-    tr.depth = __ldg(depth + i);
-    s_lo[i] = lo;
-    s_hi[i] = tr;
-    s_depth[i] = tr.depth;
-    any_ext |= (pe - pb > 3) || (nsh_topo > 0 && qe - qb > 2);
-  });
-  const bool ext_needed = __syncthreads_or(any_ext) != 0;
-  if (!ext_needed) {
-    // Where each round starts is the same in all three orders (each sorts by depth first). Without ext lists the
-    // offset array is free to hold those starts: "is this the first task of a round" is one lookup.
-    uint16_t* s_lvl = reinterpret_cast<uint16_t*>(s_extoff);
-    const uint16_t* odg = w.order_dg + v.t_topo;
-    strided_for<4>(n, [&](int t) {
-      const int d = s_depth[__ldg(odg + t)];
-      const int dprev = t > 0 ? (int)s_depth[__ldg(odg + t - 1)] : -1;
-      if (d != dprev) s_lvl[d] = (uint16_t)t;
-    });
-    __syncthreads();
-    // ---- phase 2: position t of all the orders in one iteration: three independent gathers per thread ----
-    strided_for<2>(n, [&](int t) {
-#pragma unroll
-      for (int kind = 0; kind < 3; ++kind) {
-        if (!use[kind]) continue;
-        const int i = __ldg(g_order[kind] + t);
-        TaskRec tr;
-        tr.lo = s_lo[i];
-        tr.hi = s_hi[i];
-        Rec rc = make_rec(kind, tr, i, v, nsh_topo, sid, s_pos + kind * n_al, w.ext[kind], 0);
-        rc.flags = t == (int)s_lvl[tr.hi.depth] ? kRecFirst : 0;
-        (w.stream[kind] + v.t_inst)[t] = rc;
-      }
-    });
-    return;
-  }
-  // Some task carries an ext list: its offset is a prefix sum over the positions of the order, one order at a time.
-  for (int kind = 0; kind < 3; ++kind) {
-    if (!use[kind]) continue;
-    const uint16_t* order = g_order[kind];
-    const uint16_t* posk = s_pos + kind * n_al;
-    Rec* out = w.stream[kind] + v.t_inst;
-    uint16_t* ext = w.ext[kind] + ext_offset(b, inst, v);
-    __syncthreads();  // the previous order is done with s_extoff
-    for (int t = tid; t < n; t += blockDim.x) {
-      const int i = order[t];
-      int extra = max(0, (int)s_hi[i].npred - 3);
-      if (kind != kStreamMRU && nsh_topo > 0) {
-        int nsh = 0;
-        for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) nsh += sid[v.par_idx[e]] != 0xFFFF;
-        extra += max(0, nsh - 2);
-      }
-      s_extoff[t] = (uint32_t)extra;
-    }
-    if (tid == 0) s_extoff[n] = 0;
-    __syncthreads();
-    block_exclusive_scan(s_extoff, n + 1, s_part);
-    for (int t = tid; t < n; t += blockDim.x) {
-      const int i = order[t];
-      TaskRec tr;
-      tr.lo = s_lo[i];
-      tr.hi = s_hi[i];
-      Rec rc = make_rec(kind, tr, i, v, nsh_topo, sid, posk, ext, s_extoff[t]);
-      rc.flags = (t == 0 || s_depth[order[t - 1]] != tr.hi.depth) ? kRecFirst : 0;
-      out[t] = rc;
-    }
+__global__ void __launch_bounds__(256) record_expand_kernel(dls_batch_t b, Workspace w) {
+  if (w.topo_status[0] != DLS_ST_OK) return;
+  const int n = (int)(b.task_off[1] - b.task_off[0]);
+  const long long total = (long long)n * b.B;
+  const bool dur_pi = (b.flags & DLS_F_DUR_PER_INSTANCE) != 0, mem_pi = (b.flags & DLS_F_MEM_PER_INSTANCE) != 0;
+  for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
+    const int i = (int)(k % n);
+    const uint4* src = reinterpret_cast<const uint4*>(w.rec_topo + i);
+    uint4 lo = __ldg(src), hi = __ldg(src + 1);
+    if (mem_pi) { const double m = __ldg(b.mem + k); lo.x = (uint32_t)__double2loint(m); lo.y = (uint32_t)__double2hiint(m); }
+    if (dur_pi) { const double c = __ldg(b.dur + k); lo.z = (uint32_t)__double2loint(c); lo.w = (uint32_t)__double2hiint(c); }
+    uint4* dst = reinterpret_cast<uint4*>(w.rec_inst + k);
+    dst[0] = lo;
+    dst[1] = hi;
   }
 }
 
@@ -293,18 +64,71 @@ struct RecRegs {
 __device__ __forceinline__ RecRegs load_rec(const Rec* p) {
   RecRegs r;
   const uint4* q = reinterpret_cast<const uint4*>(p);
-  // L2::128B: a miss in L2 brings in the whole 128-byte line, i.e. this DAG's next three records as well
-  // and one 256-bit load instead of two 128-bit ones halves the requests of the 32 lanes, each on its own line
-  asm volatile("ld.global.nc.L2::128B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+  // one 256-bit load instead of two 128-bit ones halves the requests of the 32 lanes, each on its own line
+  // (a record is read once: keeping it out of L1 took 35 % off the MRU kernel, measured round 2a)
+#if defined(DLS_REC_L1ALLOC)
+  asm volatile("ld.global.nc.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+#else
+  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+#endif
                : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
                : "l"(q));
   return r;
 }
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// Field accessors of a record held in registers (layout of dls::Rec).
+__device__ __forceinline__ double rec_m(const RecRegs& r) { return __hiloint2double((int)r.lo.y, (int)r.lo.x); }
+__device__ __forceinline__ double rec_c(const RecRegs& r) { return __hiloint2double((int)r.lo.w, (int)r.lo.z); }
+__device__ __forceinline__ uint32_t rec_p0(const RecRegs& r) { return r.hi.x & 0xffff; }
+__device__ __forceinline__ uint32_t rec_p1(const RecRegs& r) { return r.hi.x >> 16; }
+__device__ __forceinline__ uint32_t rec_p2(const RecRegs& r) { return r.hi.y & 0xffff; }
+__device__ __forceinline__ int rec_a0(const RecRegs& r) { return (int)(r.hi.z & 0xffff); }
+__device__ __forceinline__ int rec_a1(const RecRegs& r) { return (int)(r.hi.z >> 16); }
+__device__ __forceinline__ int rec_npriv(const RecRegs& r) { return (int)(r.hi.w & 0xffff); }
+__device__ __forceinline__ int rec_npred(const RecRegs& r) { return (int)((r.hi.w >> 16) & 0xff); }
+__device__ __forceinline__ int rec_nsh(const RecRegs& r) { return (int)((r.hi.w >> 24) & 0x7f); }
+__device__ __forceinline__ int rec_parity(const RecRegs& r) { return (int)(r.hi.w >> 31); }
+
+// A thread's walk over its order array: u16 task ids, fetched as aligned 16-byte groups (one load per eight steps,
+// the group after the current one already in flight).
+struct OrderCursor {
+  const uint4* next;   // next aligned group to fetch
+  unsigned long long lo, hi;  // ids not yet handed out, lowest first
+  uint4 ahead;         // the group after those (in flight)
+  int left;            // ids left in lo/hi
+  int groups;          // groups not yet fetched
+  __device__ __forceinline__ void set(const uint4& g) {
+    lo = (unsigned long long)g.x | ((unsigned long long)g.y << 32);
+    hi = (unsigned long long)g.z | ((unsigned long long)g.w << 32);
+  }
+  __device__ __forceinline__ void init(const uint16_t* order, int n) {  // n > 0
+    const uintptr_t a = reinterpret_cast<uintptr_t>(order);
+    const int mis = (int)(a & 15) >> 1;
+    next = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
+    groups = (mis + n + 7) >> 3;
+    const uint4 g = __ldg(next++);
+    --groups;
+    ahead = make_uint4(0, 0, 0, 0);
+    if (groups > 0) { ahead = __ldg(next++); --groups; }
+    set(g);
+    for (int k = 0; k < mis; ++k) { lo = (lo >> 16) | (hi << 48); hi >>= 16; }
+    left = 8 - mis;
+  }
+  __device__ __forceinline__ int take() {
+    const int i = (int)(lo & 0xffffull);
+    lo = (lo >> 16) | (hi << 48);
+    hi >>= 16;
+    if (--left == 0) {
+      set(ahead);
+      left = 8;
+      if (groups > 0) { ahead = __ldg(next++); --groups; }
+    }
+    return i;
+  }
+};
 
 // A thread's verdict bytes (node or DLS_TASK_*) by order position. They leave in aligned words: 32 lanes storing one
 // byte each to 32 different lines cost the L1-to-L2 request path — what bounds these kernels — as much as a record
-// load. The (up to three) positions not yet stored are answered from the register.
+// load.
 struct VerdictOut {
   int8_t* base;
   uint32_t mis, acc;
@@ -328,10 +152,6 @@ struct VerdictOut {
       acc = 0;
     }
   }
-  __device__ __forceinline__ int get(uint32_t p) const {  // p below the position being decided
-    if ((int)p >= flushed) return (int8_t)(acc >> (8 * ((p + mis) & 3u)));
-    return __ldcg(base + p);
-  }
 };
 
 // Per-warp shared-memory slab: word `wd` of the calling lane.
@@ -341,6 +161,27 @@ struct Slab {
   int lane;
   __device__ __forceinline__ uint32_t& w(int wd) const { return u[wd * 32 + lane]; }
   __device__ __forceinline__ double& f(int k) const { return d[k * 32 + lane]; }
+};
+
+// Which tasks of this thread's DAG are completed (is_task_ready, ref schedulers.py:50-53). One bit per task id in the
+// thread's column of the slab; for DAGs too large for that (bm_words == 0) the verdict bytes the thread itself writes
+// in task space into the node_of output (unpermute_kernel rewrites that array afterwards with the same values).
+struct DoneSet {
+  Slab sl;
+  int bm;            // first bitmap word in the slab
+  bool in_smem;
+  int8_t* bytes;     // task-space verdict bytes (node_of of this slot and instance)
+  __device__ __forceinline__ bool test(uint32_t p) const {
+    if (in_smem) return (sl.w(bm + (int)(p >> 5)) >> (p & 31u)) & 1u;
+    return __ldcg(bytes + p) >= 0;
+  }
+  __device__ __forceinline__ void record(int i, int verdict) const {  // called for every task visited while running
+    if (in_smem) {
+      if (verdict >= 0) sl.w(bm + (i >> 5)) |= 1u << (i & 31);
+    } else {
+      bytes[i] = (int8_t)verdict;
+    }
+  }
 };
 
 template <int KMAX>
@@ -356,12 +197,15 @@ struct ThreadOut {
   bool fail_rest;
 };
 
+// amin_base >= 0: the slab holds, per node, the smallest available memory seen right after a task's own memory was
+// taken (between ref schedulers.py:95 and :126) and the node's capacity. Rounding is monotone, so the largest
+// fl(cap - avail) over those moments — what the warp-per-DAG kernels and the oracle accumulate — is fl(cap - smallest).
 template <int KMAX>
 __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int slot,
                                               int inst, const Inst& v, const double (&avail)[KMAX], const Slab& sl,
-                                              int fin_base, int cnt_base, const ThreadOut& to, int route_or = 0) {
+                                              int fin_base, int cnt_base, int amin_base, const ThreadOut& to, int route_or = 0) {
   const int64_t ko = (int64_t)slot * b.nk_inst + v.k_out;
-  double mk = 0.0;
+  double mk = 0.0, pk = 0.0;
   bool any = false;
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) {
@@ -372,10 +216,16 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
       r.cnt[ko + k] = c;
       r.avail[ko + k] = avail[k];
       if (c > 0 && (!any || f > mk)) { mk = f; any = true; }
+      if (amin_base >= 0) {
+        const double p = fmax(0.0, __dsub_rn(sl.f(amin_base + KMAX + k), sl.f(amin_base + k)));
+        r.peak[ko + k] = p;
+        pk = fmax(pk, p);
+      }
     }
   }
   dls_summary_t s;
   s.makespan = any ? mk : 0.0;
+  s.peak = pk;
   s.completed = to.completed;
   s.failed = to.fail_rest ? v.n - to.completed : to.failed;
   s.pending = v.n - s.completed - s.failed;
@@ -391,31 +241,33 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
 // -------------------------------------------------------------------------------------------------------------------
 // DFS / Greedy / Critical, one thread per DAG
 // -------------------------------------------------------------------------------------------------------------------
-template <int ALGO, int KMAX>
+template <int ALGO, int KMAX, bool PEAK>
 __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
-                                                       int twin_mode, int twin_slot) {
+                                                       int twin_mode, int twin_slot, int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab layout per warp: doubles fin[KMAX], spd[KMAX]; words smask[kSharedCap/4], cnt[KMAX]
-  constexpr int kD = 2 * KMAX;
-  const int kW = kSharedCap / 4 + KMAX;
+  // slab layout per warp: doubles fin[KMAX], spd[KMAX] (+ amin[KMAX], cap[KMAX]); words smask[kSharedCap/4], cnt[KMAX],
+  // done-bits[bm_words]
+  constexpr int kD = (PEAK ? 4 : 2) * KMAX;
+  const int kW = kSharedCap / 4 + KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
   sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
-  const int FIN = 0, SPD = KMAX, SMASK = 0, CNT = kSharedCap / 4;
+  constexpr int FIN = 0, SPD = KMAX, AMIN = 2 * KMAX, SMASK = 0, CNT = kSharedCap / 4, BM = kSharedCap / 4 + KMAX;
 
   const int inst = blockIdx.x * kTPB + threadIdx.x;
   const bool have = inst < b.B;
   Inst v;
-  v.n = 0; v.K = 0; v.topo = 0; v.t_inst = 0;
+  v.n = 0; v.K = 0; v.topo = 0; v.t_inst = 0; v.t_topo = 0;
   // DFS and Greedy walk the same order, and on a DAG without shared params they are the same function: every param
   // must be loaded whichever node is taken, so Greedy's (fewest loads, then most memory) is DFS's (most memory), see
   // the node choice below. The DFS launch (twin_mode 1) then stores its result in Greedy's slot as well, and the Greedy
   // launch (twin_mode 2) leaves those instances alone. The one case where the two differ even so (no node has more
   // than -1 available: DFS starts from max_memory = -1, Greedy from the first fitting node) withdraws the offer.
   bool elig = false, twin_ok = false;
+  int nsh_topo = 0;
   if (have) {
     bind_instance(b, inst, v);
     bool taken = false;
@@ -423,9 +275,10 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       const int rt = w.route[(int64_t)slot * b.B + inst];
       taken = rt != kRouteOpen && (rt & kRouteTwin);
     }
-    elig = !taken && w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] <= kSharedCap;
+    nsh_topo = w.nshared[v.topo];
+    elig = !taken && w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && v.K >= 0 && nsh_topo <= kSharedCap;
     if (!elig && !taken) w.route[(int64_t)slot * b.B + inst] = kRouteGeneral;
-    twin_ok = ALGO == DLS_ALGO_DFS && twin_mode == 1 && elig && w.nshared[v.topo] == 0;
+    twin_ok = ALGO == DLS_ALGO_DFS && twin_mode == 1 && elig && nsh_topo == 0;
   }
   const int n = elig ? v.n : 0, K = v.K;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
@@ -433,11 +286,17 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
     if (have && twin_mode == 1) w.route[(int64_t)twin_slot * b.B + inst] = kRouteOpen;
     return;
   }
-  constexpr int kind = ALGO == DLS_ALGO_CRITICAL ? kStreamCP : kStreamDG;
-  const Rec* rec = w.stream[kind] + v.t_inst;
-  const uint16_t* ext = w.ext[kind] + (elig ? ext_offset(b, inst, v) : 0);
+  const Rec* rec = w.rec_inst + v.t_inst;
+  const uint16_t* order = ALGO == DLS_ALGO_CRITICAL ? w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo)
+                                                    : w.order_dg + v.t_topo;
+  const uint16_t* sid = w.par_sid + (have ? b.pid_off[v.topo] : 0);
   VerdictOut vout;
   vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
+  DoneSet done;
+  done.sl = sl;
+  done.bm = BM;
+  done.in_smem = bm_words > 0;
+  done.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
 
   // Node state. avail[k] of a node that does not exist is -inf: it never fits and never wins a max.
   double avail[KMAX];
@@ -452,6 +311,10 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
     sl.f(FIN + k) = 0.0;
     sl.f(SPD + k) = sp;
     sl.w(CNT + k) = 0;
+    if constexpr (PEAK) {
+      sl.f(AMIN + k) = INFINITY;
+      sl.f(AMIN + KMAX + k) = on ? v.cap[k] : 0.0;
+    }
   }
   if constexpr (ALGO == DLS_ALGO_CRITICAL) {
 #pragma unroll
@@ -467,50 +330,61 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
     }
   }
   for (int x = 0; x < kSharedCap / 4; ++x) sl.w(SMASK + x) = 0;
+  for (int x = 0; x < bm_words; ++x) sl.w(BM + x) = 0;
 
   ThreadOut to;
   to.completed = to.failed = to.hits = to.misses = to.rounds = 0;
   to.status = DLS_ST_OK;
   to.fail_rest = false;
   bool running = elig, any_ready = false, any_assigned = false;
-  uint32_t first_nd = 0xffffffffu;  // smallest order position whose task is not completed (none so far)
-  uint32_t xpos = 0;
-  RecRegs cur;
-  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
-  if (n > 0) cur = load_rec(rec);
+  bool clean = true;  // no task so far was failed or left pending: every dependency of the next task is done
+  int prev_par = 0;
+  OrderCursor oc;
+  RecRegs r0, r1;
+  r0.lo = r0.hi = r1.lo = r1.hi = make_uint4(0, 0, 0, 0);
+  int i0 = 0, i1 = 0;
+  if (n > 0) { oc.init(order, n); i0 = oc.take(); r0 = load_rec(rec + i0); }
+  if (n > 1) { i1 = oc.take(); r1 = load_rec(rec + i1); }
   for (int t = 0; t < n_warp; ++t) {
-    RecRegs nxt = cur;
-    if (t + 1 < n) nxt = load_rec(rec + t + 1);
-    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);  // once per 128-byte line; (measured: of no use to MRU)
+    const RecRegs cur = r0;
+    const int i = i0;
+    r0 = r1;
+    i0 = i1;
+    if (t + 2 < n) { i1 = oc.take(); r1 = load_rec(rec + i1); }
     if (t < n) {
-      const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
-      const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
-      const int npred = cur.hi.y >> 16, npriv = cur.hi.w & 0xffff, nsh = (cur.hi.w >> 16) & 0xff;
-      const int flags = cur.hi.w >> 24;
-      if (flags & kRecFirst) {
+      const double m = rec_m(cur), c = rec_c(cur);
+      const int npred = rec_npred(cur), npriv = rec_npriv(cur), nsh = rec_nsh(cur);
+      const int par = rec_parity(cur);
+      if (t == 0 || par != prev_par) {  // first task of a round
         if (t > 0 && running) {
           if (!any_ready) running = false;                       // ready list empty (ref schedulers.py:172-174)
           else if (!any_assigned) { running = false; to.fail_rest = true; }  // no progress (ref :202-206)
         }
         if (running) { ++to.rounds; any_ready = any_assigned = false; }
       }
+      prev_par = par;
       int verdict = DLS_TASK_PENDING;
-      const uint32_t x_pred = xpos, x_sh = xpos + (uint32_t)max(0, npred - 3);
-      xpos = x_sh + (uint32_t)max(0, nsh - 2);
+      // the shared params of the task: the first two ride in the record, with more all are read from the input
+      auto for_each_shared = [&](auto f) {
+        if (nsh <= 2) {
+          if (nsh > 0) f(rec_a0(cur));
+          if (nsh > 1) f(rec_a1(cur));
+        } else {
+          for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) {
+            const int sd = sid[v.par_idx[e]];
+            if (sd != 0xFFFF) f(sd);
+          }
+        }
+      };
       if (running) {
-        // is_task_ready (ref :50-53) without a done-bitmap: every position below `first_nd` is done, so a task
-        // whose dependencies all sit below it is ready with no memory access at all; only after the first failed or
-        // blocked task do the (few) later dependencies get looked up in this thread's own verdict bytes.
+        // is_task_ready (ref :50-53): dependencies live in earlier rounds; while no task has failed or stayed pending
+        // they are all done and nothing is looked up
         bool ready = true;
-        if (npred > 0) {
-          const uint32_t p0 = cur.hi.x & 0xffff, p1 = cur.hi.x >> 16, p2 = cur.hi.y & 0xffff;
-          uint32_t pm = p0;
-          if (npred > 1) pm = max(pm, p1);
-          if (npred > 2) pm = max(pm, p2);
-          if (pm >= first_nd || npred > 3) {
-            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || vout.get(p) >= 0; };
-            ready = done_at(p0) && (npred < 2 || done_at(p1)) && (npred < 3 || done_at(p2));
-            for (int j = 3; j < npred; ++j) ready = ready && done_at(ext[x_pred + j - 3]);
+        if (npred > 0 && !clean) {
+          ready = done.test(rec_p0(cur)) && (npred < 2 || done.test(rec_p1(cur))) && (npred < 3 || done.test(rec_p2(cur)));
+          if (npred > 3 && ready) {
+            const uint32_t pb = v.pred_ptr[i];
+            for (int j = 3; j < npred && ready; ++j) ready = done.test(v.pred_idx[pb + j]);
           }
         }
         if (ready) {
@@ -540,12 +414,11 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
           } else {
             // shared params not yet cached, per node, packed one byte per node
             unsigned long long miss = 0;
-            for (int j = 0; j < nsh; ++j) {
-              const int sd = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
+            for_each_shared([&](int sd) {
               const uint32_t mask = (sl.w(SMASK + (sd >> 2)) >> ((sd & 3) * 8)) & 0xffu;
               const unsigned long long spread = ((unsigned long long)(mask ^ 0xffu) * 0x0101010101010101ull) & 0x8040201008040201ull;
               miss += ((spread + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
-            }
+            });
             double bv = ALGO == DLS_ALGO_DFS ? -1.0 : 0.0;  // max_memory = -1 (ref :187) / best_available_memory = 0 (ref :269)
             int bl = 0x7fffffff, bk = 0x7fffffff;             // min_params_to_load = inf (ref :268)
 #pragma unroll
@@ -572,6 +445,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
             if (lbest > 1) a = __dsub_rn(a, 0.5);
             for (int j = 2; j < lbest; ++j) a = __dsub_rn(a, 0.5);
             a = __dsub_rn(a, m);                   // ref :95
+            if constexpr (PEAK) sl.f(AMIN + best) = fmin(sl.f(AMIN + best), a);
             a = __dadd_rn(a, m);                   // complete_task frees it again (ref :126)
 #pragma unroll
             for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
@@ -579,10 +453,8 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
             sl.w(CNT + best) += 1;
             to.misses += lbest;
             to.hits += npriv + nsh - lbest;
-            for (int j = 0; j < nsh; ++j) {
-              const int sd = j == 0 ? (int)(cur.hi.z & 0xffff) : j == 1 ? (int)(cur.hi.z >> 16) : (int)ext[x_sh + j - 2];
-              sl.w(SMASK + (sd >> 2)) |= (1u << best) << ((sd & 3) * 8);
-            }
+            if (nsh > 0)
+              for_each_shared([&](int sd) { sl.w(SMASK + (sd >> 2)) |= (1u << best) << ((sd & 3) * 8); });
             verdict = best;
             ++to.completed;
             any_assigned = true;
@@ -591,19 +463,19 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
             ++to.failed;
           }
         }
+        done.record(i, verdict);
       }
-      if (verdict < 0) first_nd = min(first_nd, (uint32_t)t);
+      if (verdict < 0) clean = false;
       vout.put(t, verdict, t == n - 1);
     }
-    cur = nxt;
   }
   if (elig) {
     if (running) {
       if (any_ready && !any_assigned) to.fail_rest = true;
       else if (any_ready && to.completed + to.failed < n) ++to.rounds;  // one more iteration finds nothing ready
     }
-    finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, to);
-    if (twin_ok) finish_thread<KMAX>(b, r, w, twin_slot, inst, v, avail, sl, FIN, CNT, to, kRouteTwin);
+    finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, PEAK ? AMIN : -1, to);
+    if (twin_ok) finish_thread<KMAX>(b, r, w, twin_slot, inst, v, avail, sl, FIN, CNT, PEAK ? AMIN : -1, to, kRouteTwin);
   }
   if (have && twin_mode == 1 && !twin_ok) w.route[(int64_t)twin_slot * b.B + inst] = kRouteOpen;
 }
@@ -640,38 +512,45 @@ __device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_
   return false;
 }
 
-template <int KMAX>
-__global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot) {
+template <int KMAX, bool PEAK>
+__global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+                                                                 int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX]; words cnt[KMAX], ncached[KMAX]
-  constexpr int kD = 3 * KMAX;
-  constexpr int kW = 2 * KMAX;
+  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX] (+ amin[KMAX], cap[KMAX]); words cnt[KMAX], ncached[KMAX],
+  // done-bits[bm_words]
+  constexpr int kD = (PEAK ? 5 : 3) * KMAX;
+  const int kW = 2 * KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
   sl.d = reinterpret_cast<double*>(smem_raw + wib * warp_bytes);
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
   // HCNT[k] = len(node.completed_tasks) * 0.5 kept as a double: every += 0.5 is exact (ref schedulers.py:498)
-  const int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, CNT = 0, NC = KMAX;
+  constexpr int FIN = 0, SPD = KMAX, HCNT = 2 * KMAX, AMIN = 3 * KMAX, CNT = 0, NC = KMAX, BM = 2 * KMAX;
 
   const int inst = blockIdx.x * kTPBM + threadIdx.x;
   const bool have = inst < b.B;
   Inst v;
-  v.n = 0; v.K = 0; v.topo = 0; v.P = 0; v.t_inst = 0;
+  v.n = 0; v.K = 0; v.topo = 0; v.P = 0; v.t_inst = 0; v.t_topo = 0;
   bool elig = false;
   if (have) {
     bind_instance(b, inst, v);
-    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && w.nshared[v.topo] == 0;
+    elig = w.topo_status[v.topo] == DLS_ST_OK && v.n > 0 && v.K <= KMAX && v.K >= 0 && w.nshared[v.topo] == 0;
     if (!elig) w.route[(int64_t)slot * b.B + inst] = kRouteGeneral;
   }
   const int n = elig ? v.n : 0, K = v.K;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
   if (n_warp == 0) return;
-  const Rec* rec = w.stream[kStreamMRU] + v.t_inst;
-  const uint16_t* ext = w.ext[kStreamMRU] + (elig ? ext_offset(b, inst, v) : 0);
+  const Rec* rec = w.rec_inst + v.t_inst;
+  const uint16_t* order = w.order_mru + v.t_topo;
   VerdictOut vout;
   vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
+  DoneSet done;
+  done.sl = sl;
+  done.bm = BM;
+  done.in_smem = bm_words > 0;
+  done.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
 
   double avail[KMAX];  // -inf for nodes that do not exist: they never fit
 #pragma unroll
@@ -683,50 +562,52 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
     sl.f(HCNT + k) = 0.0;
     sl.w(CNT + k) = 0;
     sl.w(NC + k) = 0;  // len(node.cached_params)
+    if constexpr (PEAK) {
+      sl.f(AMIN + k) = INFINITY;
+      sl.f(AMIN + KMAX + k) = on ? v.cap[k] : 0.0;
+    }
   }
+  for (int x = 0; x < bm_words; ++x) sl.w(BM + x) = 0;
 
   ThreadOut to;
   to.completed = to.failed = to.hits = to.misses = to.rounds = 0;
   to.status = DLS_ST_OK;
   to.fail_rest = false;
   int carried = 0;
-  bool running = elig, any_ready = false, any_assigned = false;
-  uint32_t first_nd = 0xffffffffu, xpos = 0;
-  RecRegs cur;
-  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
-  if (n > 0) cur = load_rec(rec);
+  bool running = elig, any_ready = false, any_assigned = false, clean = true;
+  int prev_par = 0;
+  OrderCursor oc;
+  RecRegs r0, r1;
+  r0.lo = r0.hi = r1.lo = r1.hi = make_uint4(0, 0, 0, 0);
+  int i0 = 0, i1 = 0;
+  if (n > 0) { oc.init(order, n); i0 = oc.take(); r0 = load_rec(rec + i0); }
+  if (n > 1) { i1 = oc.take(); r1 = load_rec(rec + i1); }
   for (int t = 0; t < n_warp; ++t) {
-    RecRegs nxt = cur;
-    if (t + 1 < n) nxt = load_rec(rec + t + 1);
+    const RecRegs cur = r0;
+    const int i = i0;
+    r0 = r1;
+    i0 = i1;
+    if (t + 2 < n) { i1 = oc.take(); r1 = load_rec(rec + i1); }
     if (t < n) {
-      const double m = __hiloint2double((int)cur.lo.y, (int)cur.lo.x);
-      const double c = __hiloint2double((int)cur.lo.w, (int)cur.lo.z);
-      const int npred = cur.hi.y >> 16, npar = cur.hi.w & 0xffff;
-      const int flags = cur.hi.w >> 24;
-      if (flags & kRecFirst) {
+      const double m = rec_m(cur), c = rec_c(cur);
+      const int npred = rec_npred(cur), npar = rec_npriv(cur);
+      const int par = rec_parity(cur);
+      if (t == 0 || par != prev_par) {
         if (t > 0 && running) {
           if (!any_ready) running = false;
           else if (!any_assigned) { running = false; to.fail_rest = true; }
         }
         if (running) { ++to.rounds; any_ready = any_assigned = false; }  // self.time_step += 1 (ref :453)
       }
+      prev_par = par;
       int verdict = DLS_TASK_PENDING;
-      const uint32_t x_pred = xpos;
-      xpos += (uint32_t)max(0, npred - 3);
       if (running) {
-        // is_task_ready (ref :50-53) without a done-bitmap: every position below `first_nd` is done, so a task
-        // whose dependencies all sit below it is ready with no memory access at all; only after the first failed or
-        // blocked task do the (few) later dependencies get looked up in this thread's own verdict bytes.
-        bool ready = true;
-        if (npred > 0) {
-          const uint32_t p0 = cur.hi.x & 0xffff, p1 = cur.hi.x >> 16, p2 = cur.hi.y & 0xffff;
-          uint32_t pm = p0;
-          if (npred > 1) pm = max(pm, p1);
-          if (npred > 2) pm = max(pm, p2);
-          if (pm >= first_nd || npred > 3) {
-            auto done_at = [&](uint32_t p) -> bool { return p < first_nd || vout.get(p) >= 0; };
-            ready = done_at(p0) && (npred < 2 || done_at(p1)) && (npred < 3 || done_at(p2));
-            for (int j = 3; j < npred; ++j) ready = ready && done_at(ext[x_pred + j - 3]);
+        bool ready = true;  // is_task_ready (ref :50-53), as in sched_stream_kernel
+        if (npred > 0 && !clean) {
+          ready = done.test(rec_p0(cur)) && (npred < 2 || done.test(rec_p1(cur))) && (npred < 3 || done.test(rec_p2(cur)));
+          if (npred > 3 && ready) {
+            const uint32_t pb = v.pred_ptr[i];
+            for (int j = 3; j < npred && ready; ++j) ready = done.test(v.pred_idx[pb + j]);
           }
         }
         if (ready) {
@@ -790,6 +671,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
               if (npar > 1) a = __dsub_rn(a, 0.5);
               for (int j = 2; j < npar; ++j) a = __dsub_rn(a, 0.5);
               a = __dsub_rn(a, m);
+              if constexpr (PEAK) sl.f(AMIN + best) = fmin(sl.f(AMIN + best), a);
               a = __dadd_rn(a, m);
 #pragma unroll
               for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
@@ -807,18 +689,18 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
             ++to.failed;
           }
         }
+        done.record(i, verdict);
       }
-      if (verdict < 0) first_nd = min(first_nd, (uint32_t)t);
+      if (verdict < 0) clean = false;
       vout.put(t, verdict, t == n - 1);
     }
-    cur = nxt;
   }
   if (elig) {
     if (running) {
       if (any_ready && !any_assigned) to.fail_rest = true;
       else if (any_ready && to.completed + to.failed + carried < n) ++to.rounds;
     }
-    finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, to);
+    finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, PEAK ? AMIN : -1, to);
   }
 }
 
@@ -845,9 +727,9 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   const int kind = sk.kind[slot];
   Inst v;
   bind_instance(b, inst, v);
-  const uint16_t* order = kind == kStreamDG ? w.order_dg + v.t_topo
-                        : kind == kStreamMRU ? w.order_mru + v.t_topo
-                                             : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
+  const uint16_t* order = kind == kOrderDG ? w.order_dg + v.t_topo
+                        : kind == kOrderMRU ? w.order_mru + v.t_topo
+                                            : w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo);
   const int8_t* npos = w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst;
   int8_t* node_of = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
   uint16_t* seq_pos = r.seq_pos + (int64_t)slot * b.nt_inst + v.t_inst;
@@ -895,13 +777,17 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   }
 }
 
-template <int KMAX>
-size_t smem_simple() {
-  return (size_t)(kTPB / 32) * ((size_t)2 * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX) * 32 * 4);
+int bitmap_words(int n_max) {
+  const int wds = (n_max + 31) >> 5;
+  return wds <= kBitmapWordsMax ? wds : 0;
 }
 template <int KMAX>
-size_t smem_mru() {
-  return (size_t)(kTPBM / 32) * ((size_t)3 * KMAX * 32 * 8 + (size_t)(2 * KMAX) * 32 * 4);
+size_t smem_simple(bool peak, int bm_words) {
+  return (size_t)(kTPB / 32) * ((size_t)(peak ? 4 : 2) * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX + bm_words) * 32 * 4);
+}
+template <int KMAX>
+size_t smem_mru(bool peak, int bm_words) {
+  return (size_t)(kTPBM / 32) * ((size_t)(peak ? 5 : 3) * KMAX * 32 * 8 + (size_t)(2 * KMAX + bm_words) * 32 * 4);
 }
 
 }  // namespace
@@ -909,8 +795,8 @@ size_t smem_mru() {
 // The streamed path needs K <= 8 nodes and per-thread state small enough for a useful number of resident warps.
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit) {
   if (b.K_max > 8) return false;
-  if (r && (r->peak || r->cached || r->tfin)) return false;  // extension outputs are produced by the general kernels only
-  return smem_simple<8>() <= (size_t)smem_limit / 2 && b.n_max >= 1;
+  if (r && (r->cached || r->tfin)) return false;  // these extension outputs are produced by the general kernels only
+  return smem_mru<8>(true, kBitmapWordsMax) <= (size_t)smem_limit / 2 && b.n_max >= 1;
 }
 
 template <class Kern, class... Args>
@@ -926,51 +812,47 @@ static cudaError_t launch_fast(Kern kern, int kernel_id, dim3 grid, int threads,
   return cudaGetLastError();
 }
 
-cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
-  int kinds = 0;
-  if (algo_mask & 3) kinds |= 1 << kStreamDG;
-  if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kStreamCP;
-  if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kStreamMRU;
-  const size_t staged = (size_t)b.n_max * 32 + ((size_t)b.n_max + 1) * sizeof(uint32_t) +
-                        4 * (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t) + 16;
-  if (staged <= 180 * 1024)
-    return launch_fast(stream_build_staged_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B), kBuildThreads, staged, ctx, b, w, kinds);
-  const size_t smem = ((size_t)b.n_max + 1) * sizeof(uint32_t) + (((size_t)b.n_max + 1) & ~(size_t)1) * sizeof(uint16_t);
-  return launch_fast(stream_build_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B, 3), kBuildThreads, smem, ctx, b, w, kinds);
+cudaError_t launch_record_expand(const dls_batch_t& b, const Workspace& w, LaunchCtx& ctx) {
+  const long long total = b.nt_inst;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  const int grid = blocks > 0 ? (int)blocks : 1;
+  return launch_fast(record_expand_kernel, DLS_KERNEL_RECORD_EXPAND, dim3(grid), 256, 0, ctx, b, w);
 }
 
-template <int KMAX>
+template <int KMAX, bool PEAK>
 static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                          LaunchCtx& ctx) {
   const dim3 grid((b.B + kTPB - 1) / kTPB);
+  const int bmw = bitmap_words(b.n_max);
   int slot = 0;
   SlotKinds sk = {{0, 0, 0, 0}, {-1, -1, -1, -1}};
   cudaError_t e = cudaSuccess;
   const bool twins = (algo_mask & 3) == 3;  // DFS and Greedy both asked for: slots 0 and 1
   if (algo_mask & (1 << DLS_ALGO_DFS)) {
-    e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX>, DLS_KERNEL_STREAM_DFS, grid, kTPB, smem_simple<KMAX>(),
-                    ctx, b, r, w, slot, twins ? 1 : 0, slot + 1);
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_DFS, KMAX, PEAK>, DLS_KERNEL_STREAM_DFS, grid, kTPB,
+                    smem_simple<KMAX>(PEAK, bmw), ctx, b, r, w, slot, twins ? 1 : 0, slot + 1, bmw);
     if (e != cudaSuccess) return e;
-    sk.kind[slot++] = kStreamDG;
+    sk.kind[slot++] = kOrderDG;
   }
   if (algo_mask & (1 << DLS_ALGO_GREEDY)) {
-    e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
-                    smem_simple<KMAX>(), ctx, b, r, w, slot, twins ? 2 : 0, slot - 1);
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_GREEDY, KMAX, PEAK>, DLS_KERNEL_STREAM_GREEDY, grid, kTPB,
+                    smem_simple<KMAX>(PEAK, bmw), ctx, b, r, w, slot, twins ? 2 : 0, slot - 1, bmw);
     if (e != cudaSuccess) return e;
     if (twins) sk.follower[slot - 1] = slot;
-    sk.kind[slot++] = kStreamDG;
+    sk.kind[slot++] = kOrderDG;
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
-    e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
-                    smem_simple<KMAX>(), ctx, b, r, w, slot, 0, 0);
+    e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX, PEAK>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
+                    smem_simple<KMAX>(PEAK, bmw), ctx, b, r, w, slot, 0, 0, bmw);
     if (e != cudaSuccess) return e;
-    sk.kind[slot++] = kStreamCP;
+    sk.kind[slot++] = kOrderCP;
   }
   if (algo_mask & (1 << DLS_ALGO_MRU)) {
-    e = launch_fast(sched_stream_mru_kernel<KMAX>, DLS_KERNEL_STREAM_MRU, dim3((b.B + kTPBM - 1) / kTPBM), kTPBM,
-                    smem_mru<KMAX>(), ctx, b, r, w, slot);
+    e = launch_fast(sched_stream_mru_kernel<KMAX, PEAK>, DLS_KERNEL_STREAM_MRU, dim3((b.B + kTPBM - 1) / kTPBM), kTPBM,
+                    smem_mru<KMAX>(PEAK, bmw), ctx, b, r, w, slot, bmw);
     if (e != cudaSuccess) return e;
-    sk.kind[slot++] = kStreamMRU;
+    sk.kind[slot++] = kOrderMRU;
   }
   // verdicts of all slots back to task ids in one launch
   const int n_al = (b.n_max + 3) & ~3;
@@ -982,9 +864,14 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
 
 cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                 LaunchCtx& ctx) {
-  if (b.K_max <= 2) return launch_stream_sched_k<2>(b, r, w, algo_mask, ctx);
-  if (b.K_max <= 4) return launch_stream_sched_k<4>(b, r, w, algo_mask, ctx);
-  return launch_stream_sched_k<8>(b, r, w, algo_mask, ctx);
+  if (r.peak) {
+    if (b.K_max <= 2) return launch_stream_sched_k<2, true>(b, r, w, algo_mask, ctx);
+    if (b.K_max <= 4) return launch_stream_sched_k<4, true>(b, r, w, algo_mask, ctx);
+    return launch_stream_sched_k<8, true>(b, r, w, algo_mask, ctx);
+  }
+  if (b.K_max <= 2) return launch_stream_sched_k<2, false>(b, r, w, algo_mask, ctx);
+  if (b.K_max <= 4) return launch_stream_sched_k<4, false>(b, r, w, algo_mask, ctx);
+  return launch_stream_sched_k<8, false>(b, r, w, algo_mask, ctx);
 }
 
 }  // namespace dls

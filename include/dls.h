@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define DLS_VERSION 100 /* major*100 + minor */
+#define DLS_VERSION 200 /* major*100 + minor; 2.0: dls_summary_t carries the instance's peak memory (48 bytes) */
 
 /* algorithm ids (slot order inside results = increasing id among those requested) */
 #define DLS_ALGO_DFS 0      /* DFSScheduler           schedulers.py:138-208 */
@@ -116,6 +116,8 @@ typedef struct dls_batch {
  * (simulation.py:336-346) plus simulate_execution's outputs (simulation.py:216-278). */
 typedef struct dls_summary {
   double makespan;   /* max over nodes of the sequential sum of dur/spd   simulation.py:261-271 */
+  double peak;       /* extension, no reference counterpart: largest per-node peak memory of the instance (max over
+                        nodes of dls_result_t.peak); 0.0 unless the peak output was requested */
   int32_t completed; /* len(scheduler.completed_tasks)                    simulation.py:339 */
   int32_t failed;    /* len(scheduler.failed_tasks)                       simulation.py:340 */
   int32_t pending;   /* len(scheduler.pending_tasks) after schedule() */
@@ -139,7 +141,7 @@ typedef struct dls_result {
   int32_t* cnt;           /* [A][NK] len(node.completed_tasks)              schedulers.py:123 */
   double* avail;          /* [A][NK] final node.available_memory (bit-exact fp64 replay) schedulers.py:89,95,126 */
   double* peak;           /* [A][NK] extension, no reference counterpart: max of total-available sampled
-                             between schedulers.py:95 and :126; NULL to skip */
+                             between schedulers.py:95 and :126; NULL to skip. Produced by every kernel path. */
   uint32_t* cached;       /* [A][NP] bit k set = param cached on node k at the end (Node.cached_params,
                              schedulers.py:26,88,428); NULL to skip */
   double* tfin;           /* [A][NK] extension, no reference counterpart: node finish
@@ -148,7 +150,7 @@ typedef struct dls_result {
                              starts when its node is free AND all its dependencies have finished:
                              t_i = max(node free, max finish of deps) + compute_time / compute_speed, tasks taken in
                              assignment order. The dependency-aware makespan is the maximum over nodes with cnt > 0.
-                             NULL to skip; like peak / cached it is produced by the warp-per-DAG kernels. */
+                             NULL to skip; like cached it is produced by the warp-per-DAG kernels only. */
 } dls_result_t;
 
 /* Outputs of the priority pass alone (kernel P). All nullable. Per topology-task arrays have
@@ -277,7 +279,7 @@ int64_t dls_launch_count(void);
 #define DLS_KERNEL_SCHED_CRITICAL 4
 #define DLS_KERNEL_SCHED_MRU 5
 #define DLS_KERNEL_PARAM_CLASS 6
-#define DLS_KERNEL_STREAM_BUILD 7
+#define DLS_KERNEL_RECORD_EXPAND 7
 #define DLS_KERNEL_STREAM_DFS 8
 #define DLS_KERNEL_STREAM_GREEDY 9
 #define DLS_KERNEL_STREAM_CRITICAL 10

@@ -62,18 +62,20 @@ def assert_results_equal(a: ResultArrays, b: ResultArrays, what: str = ""):
     np.testing.assert_array_equal(bits(a.avail), bits(b.avail), err_msg=what + " avail bits")
     if a.peak is not None and b.peak is not None:
         np.testing.assert_array_equal(bits(a.peak), bits(b.peak), err_msg=what + " peak bits")
+        np.testing.assert_array_equal(bits(a.summary["peak"]), bits(b.summary["peak"]), err_msg=what + " summary peak bits")
     if a.cached is not None and b.cached is not None:
         np.testing.assert_array_equal(a.cached, b.cached, err_msg=what + " cached")
 
 
 def run_both_paths(batch, mask):
     """Yield (label, ResultArrays) for the device implementations: the general warp-per-DAG kernels (which also
-    produce the peak/cached extensions) and the thread-per-DAG streamed kernels (taken when no extension output is
-    requested and the batch qualifies; otherwise the library falls back to the general ones by itself)."""
+    produce the cached / timeline extensions) and the thread-per-DAG streamed kernels (taken when the batch qualifies;
+    otherwise the library falls back to the general ones by itself), the latter with and without peak memory."""
     from dls_b200.batch import schedule_batch
     from dls_b200 import _native as N
     yield "general", schedule_batch(batch, mask, peak=True, cached=True).host()
     yield "streamed", schedule_batch(batch, mask, peak=False, cached=False).host()
+    yield "streamed, peak", schedule_batch(batch, mask, peak=True, cached=False).host()
     old = N.load().dls_set_stream_path(0)  # the general kernels again, this time without the extension outputs
     try:
         yield "general, no extensions", schedule_batch(batch, mask, peak=False, cached=False).host()

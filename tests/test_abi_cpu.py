@@ -26,11 +26,11 @@ def test_header_symbols_exported(lib):
     assert declared == set(N.EXPORTED_SYMBOLS), declared ^ set(N.EXPORTED_SYMBOLS)
     for s in declared:
         assert hasattr(lib, s), s
-    assert lib.dls_version() == 100
+    assert lib.dls_version() == 200
 
 
 def test_struct_layout_matches_header():
-    assert C.sizeof(N.DlsSummary) == 40
+    assert C.sizeof(N.DlsSummary) == 48
     assert C.sizeof(N.DlsBatch) == 8 * 4 + 6 * 8 + 14 * 8
     assert C.sizeof(N.DlsResult) == 9 * 8 and C.sizeof(N.DlsPrio) == 6 * 8
 

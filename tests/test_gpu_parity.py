@@ -66,17 +66,18 @@ def test_dfs_result_shared_with_greedy_only_where_they_agree(oracle_mod):
     for path, got in run_both_paths(batch, N.MASK_ALL):
         assert_results_equal(got, want, f"{path} dfs/greedy twins")
     for mask in (3, 2, 1, 11):
-        got = schedule_batch(batch, mask).host()
+        got = schedule_batch(batch, mask, peak=True).host()
         for slot, a in enumerate(got.algos):
             np.testing.assert_array_equal(got.node_of[slot], want.node_of[a])
             np.testing.assert_array_equal(got.summary[slot], want.summary[a])
 
 
 def test_single_algorithm_masks_and_slots(oracle_mod):
+    """Any subset of the algorithms gives, slot by slot, what the oracle gives for that algorithm."""
     batch = random_dag_batch(16, 200, 8, 0.8, seed=5)
-    full = schedule_batch(batch, N.MASK_ALL).host()
+    full = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=4)
     for mask in (1, 2, 4, 8, 5, 10, 12):
-        got = schedule_batch(batch, mask).host()
+        got = schedule_batch(batch, mask, peak=True).host()
         for slot, a in enumerate(got.algos):
             np.testing.assert_array_equal(got.node_of[slot], full.node_of[a])
             np.testing.assert_array_equal(got.seq_pos[slot], full.seq_pos[a])
@@ -168,7 +169,8 @@ def test_streamed_path_is_taken_and_falls_back():
     lib.dls_profile_enable(0)
     names = {lib.dls_kernel_name(k).decode(): int(cnt[k]) for k in range(N.NUM_KERNELS)}
     assert names["sched_stream_kernel<DFS>"] == 1 and names["sched_stream_mru_kernel"] == 1 and names["unpermute_kernel"] == 1
-    assert names["priority_topology_kernel"] == 1 and names["stream_build_kernel"] == 1
+    assert names["priority_topology_kernel"] == 1 and names["param_class_kernel"] == 1
+    assert names["record_expand_kernel"] == 0   # one topology per instance: the topology kernel's records are read as they are
     old = lib.dls_set_stream_path(0)
     try:
         slow = schedule_batch(batch, N.MASK_ALL).host()
@@ -286,13 +288,21 @@ def test_cycle_is_reported_not_hung():
     assert (res.node_of == N.TASK_PENDING).all()
 
 
-def test_garbage_inputs_are_contained():
+def _summary_equal(got, want, with_peak):
+    """dls_summary_t records field by field; `peak` only where the run asked for peaks (it is 0.0 otherwise)."""
+    for f in got.dtype.names:
+        if f == "peak" and not with_peak:
+            continue
+        np.testing.assert_array_equal(got[f], want[f], err_msg=f)
+
+
+def test_garbage_inputs_are_contained(oracle_mod):
     """Inputs outside the reference's domain must not derail the kernels: a rank[] that is not a permutation is a bad
     topology (it would leave positions of every processing order unwritten), and NaN durations — for which the
     reference's own sort order is undefined — still give a processing order that is a permutation, every task a
     verdict, and no effect on the neighbouring instances of the batch."""
     good = random_dag_batch(8, 200, 8, 0.9, seed=21)
-    want = schedule_batch(good, N.MASK_ALL).host()
+    want = oracle_mod.schedule_batch(good, N.MASK_ALL, nthreads=4)   # what the untouched neighbours must still give
     bad = random_dag_batch(8, 200, 8, 0.9, seed=21)
     bad.rank[3 * 200 + 17] = bad.rank[3 * 200 + 18]          # instance 3: repeated rank
     bad.dur[5 * 200: 6 * 200][::7] = np.nan                  # instance 5: NaN durations
@@ -303,7 +313,7 @@ def test_garbage_inputs_are_contained():
         assert (s5["status"] == 0).all() and (s5["completed"] + s5["failed"] + s5["pending"] == 200).all(), path
         for b in (0, 1, 2, 4, 6, 7):
             np.testing.assert_array_equal(got.node_of[:, b * 200: (b + 1) * 200], want.node_of[:, b * 200: (b + 1) * 200])
-            np.testing.assert_array_equal(got.summary[:, b], want.summary[:, b])
+            _summary_equal(got.summary[:, b], want.summary[:, b], got.peak is not None)
     prio = priorities(bad)
     for b in (5,):
         for name in ("order_dg", "order_cp", "order_mru"):
