@@ -18,7 +18,7 @@ dls::Profiler g_prof;
 const char* const kKernelNames[DLS_NUM_KERNELS] = {"priority_topology_kernel", "priority_critical_kernel",
                                                    "sched_simple_kernel<DFS>", "sched_simple_kernel<Greedy>",
                                                    "sched_simple_kernel<Critical>", "sched_mru_kernel",
-                                                   "param_class_kernel", "record_expand_kernel",
+                                                   "param_class_kernel", "stream_build_kernel",
                                                    "sched_stream_kernel<DFS>", "sched_stream_kernel<Greedy>",
                                                    "sched_stream_kernel<Critical>", "sched_stream_mru_kernel",
                                                    "unpermute_kernel"};
@@ -35,7 +35,7 @@ struct Layout {
   size_t off_depth, off_outdeg, off_order_dg, off_order_mru, off_order_cp, off_up, off_succ_ptr, off_succ_idx,
       off_status, total;
   // streamed path (present when `stream` is set)
-  size_t off_sid, off_nshared, off_rec_topo, off_rec_inst, off_node_pos, off_route;
+  size_t off_sid, off_nshared, off_stream[3], off_node_pos, off_route;
   bool stream;
   int cp_per_instance;
 };
@@ -57,16 +57,20 @@ Layout layout_of(const dls_batch_t& b, int algo_mask = DLS_MASK_ALL, bool stream
   L.off_succ_ptr = o;  o = align_up(o + (nt + (size_t)b.T) * sizeof(uint32_t));
   L.off_succ_idx = o;  o = align_up(o + (size_t)b.e_total * sizeof(uint16_t));
   L.off_status = o;    o = align_up(o + (size_t)b.T * sizeof(int32_t));
-  L.off_sid = L.off_nshared = L.off_rec_topo = L.off_rec_inst = L.off_node_pos = L.off_route = 0;
+  L.off_sid = L.off_nshared = L.off_node_pos = L.off_route = 0;
+  for (int k = 0; k < 3; ++k) L.off_stream[k] = 0;
   if (stream) {
     const size_t np = (size_t)(b.T == 1 ? b.P_max : b.np_inst);
     const int A = count_bits(algo_mask & DLS_MASK_ALL);
     L.off_sid = o;     o = align_up(o + np * sizeof(uint16_t));
     L.off_nshared = o; o = align_up(o + (size_t)b.T * sizeof(int32_t));
-    // one 32-byte record per task; with one topology for all instances (T == 1) a copy per instance as well
-    L.off_rec_topo = o; o = align_up(o + nt * 32);
-    L.off_rec_inst = L.off_rec_topo;
-    if (b.T == 1) { L.off_rec_inst = o; o = align_up(o + (size_t)b.nt_inst * 32); }
+    // per processing order in use, one 32-byte record per instance-task
+    const bool need[3] = {(algo_mask & 3) != 0, (algo_mask & (1 << DLS_ALGO_CRITICAL)) != 0,
+                          (algo_mask & (1 << DLS_ALGO_MRU)) != 0};
+    for (int k = 0; k < 3; ++k) {
+      if (!need[k]) continue;
+      L.off_stream[k] = o; o = align_up(o + (size_t)b.nt_inst * 32 + 256);  // (+ room for the last prefetch)
+    }
     L.off_node_pos = o; o = align_up(o + (size_t)A * (size_t)b.nt_inst);
     L.off_route = o;    o = align_up(o + (size_t)A * (size_t)b.B);
   }
@@ -89,12 +93,12 @@ dls::Workspace carve(void* base, const Layout& L) {
   w.cp_per_instance = L.cp_per_instance;
   w.keep_up = 0;
   w.par_sid = nullptr; w.nshared = nullptr; w.node_pos = nullptr; w.route = nullptr;
-  w.rec_topo = nullptr; w.rec_inst = nullptr;
+  for (int k = 0; k < 3; ++k) w.stream[k] = nullptr;
   if (L.stream) {
     w.par_sid = reinterpret_cast<uint16_t*>(p + L.off_sid);
     w.nshared = reinterpret_cast<int32_t*>(p + L.off_nshared);
-    w.rec_topo = reinterpret_cast<dls::Rec*>(p + L.off_rec_topo);
-    w.rec_inst = reinterpret_cast<dls::Rec*>(p + L.off_rec_inst);
+    for (int k = 0; k < 3; ++k)
+      if (L.off_stream[k]) w.stream[k] = reinterpret_cast<dls::Rec*>(p + L.off_stream[k]);
     w.node_pos = reinterpret_cast<int8_t*>(p + L.off_node_pos);
     w.route = reinterpret_cast<uint8_t*>(p + L.off_route);
   }
@@ -209,7 +213,7 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(built-in scratch)");
   }
   e = dls::launch_priority(*batch, w, algo_mask, ctx);
-  if (e == cudaSuccess && stream && batch->T == 1) e = dls::launch_record_expand(*batch, w, ctx);
+  if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
   if (e == cudaSuccess && stream) e = dls::launch_stream_sched(*batch, *result, w, algo_mask, ctx);
   if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
   g_launches += ctx.launches;

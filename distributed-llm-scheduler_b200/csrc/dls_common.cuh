@@ -31,17 +31,17 @@ struct Workspace {
   // ---- streamed (thread-per-DAG) path; all null when that path is not used ----
   uint16_t* par_sid;    // [np_topo]   dense id of a param shared by >= 2 tasks, 0xFFFF if private to one task
   int32_t* nshared;     // [T]         shared params of the topology; kUnstreamable = leave the DAG to the general kernels
-  struct Rec* rec_topo; // [nt_topo]   one record per task, in TASK order, written by the topology kernel
-  struct Rec* rec_inst; // [nt_inst]   the records the scheduling threads read: rec_topo itself when T == B, else a copy per
-                        //             instance with that instance's duration / memory (record_expand_kernel)
+  struct Rec* stream[3];   // [nt_inst] task records in processing order: kOrderDG (DFS/Greedy), kOrderCP, kOrderMRU
   int8_t* node_pos;     // [A][nt_inst] verdict per order position (node, -1 failed, -2 pending)
   uint8_t* route;       // [A][B]      1 = instance left to the warp-per-DAG kernel
 };
 
 // One task, everything kernel S needs for a step in 32 bytes (one DRAM sector, read by one 256-bit load). The record
 // does not depend on the processing order: dependencies are task ids, and "a new round starts here" is the parity of
-// the task's depth changing (the orders list depth 0, 1, 2, ... without gaps). So ONE array of records per instance,
-// in task order, serves all four algorithms; each scheduling thread visits it through its own order array.
+// the task's depth changing (the orders list depth 0, 1, 2, ... without gaps). A stream is therefore nothing but the
+// records permuted: stream_build_kernel makes each record once and copies it to its place in every order.
+// (Reading ONE array of records through the order arrays instead was measured in round 2a: each 32-byte read costs
+// a 128-byte DRAM line, 133 KB per instance and kernel, and the scheduling kernels ran 2.4x slower.)
 struct __align__(16) Rec {
   double m;          // Task.memory_required
   double c;          // Task.compute_time
@@ -263,7 +263,7 @@ cudaError_t launch_aggregate(const dls_batch_t& b, const dls_result_t& r, int ns
                              double* out, LaunchCtx& ctx);
 cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_count, LaunchCtx& ctx);
 cudaError_t launch_gen_fill(const dls_gen_t& g, const dls_batch_t& out, LaunchCtx& ctx);
-cudaError_t launch_record_expand(const dls_batch_t& b, const Workspace& w, LaunchCtx& ctx);
+cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_stream_sched(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                                 LaunchCtx& ctx);
 bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_limit);

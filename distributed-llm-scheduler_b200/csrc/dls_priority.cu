@@ -53,43 +53,9 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   uint32_t* g_succ_ptr = w.succ_ptr + v.t_topo + t;
   uint16_t* g_succ_idx = w.succ_idx + b.pred_off[t];
 
-  // With the streamed path on, param_class_kernel has run first: it has checked the param CSR and left the number of
-  // shared params; a topology it rejected is not looked at again.
-  const bool classed = w.nshared != nullptr;
-  if (classed && w.topo_status[t] != DLS_ST_OK) return;
-  const int nsh_topo = classed ? w.nshared[t] : 0;
-  Rec* g_rec = w.rec_topo ? w.rec_topo + v.t_topo : nullptr;
-  const double* g_mem = b.mem + v.t_topo;  // (T == 1 with per-instance values: row 0; record_expand_kernel puts in the rest)
-  const double* g_dur = b.dur + v.t_topo;
-  const uint16_t* g_sid = classed ? w.par_sid + b.pid_off[t] : nullptr;
-  int unstreamable = 0;
-  // The record of task i (dls::Rec): what a scheduling thread needs for one step, whatever the processing order.
-  auto emit_record = [&](int i, uint32_t np, uint32_t p0, uint32_t p1, uint32_t p2, int depth, double m, double c,
-                         uint32_t qb, uint32_t qe) {
-    uint32_t nsh = 0, a0 = 0, a1 = 0, npriv = qe - qb;
-    if (nsh_topo > 0) {
-      npriv = 0;
-      for (uint32_t e = qb; e < qe; ++e) {
-        const uint32_t sd = g_sid[__ldg(v.par_idx + e)];
-        if (sd == 0xFFFF) { ++npriv; continue; }
-        if (nsh == 0) a0 = sd;
-        else if (nsh == 1) a1 = sd;
-        ++nsh;
-      }
-    }
-    if (np >= 255u || nsh >= 127u || npriv > 65535u) { unstreamable = 1; np = min(np, 255u); nsh = min(nsh, 127u); npriv = min(npriv, 65535u); }
-    uint4 lo, hi;
-    lo.x = (uint32_t)__double2loint(m); lo.y = (uint32_t)__double2hiint(m);
-    lo.z = (uint32_t)__double2loint(c); lo.w = (uint32_t)__double2hiint(c);
-    hi.x = (np > 0 ? p0 : 0u) | ((np > 1 ? p1 : 0u) << 16);
-    hi.y = (np > 2 ? p2 : 0u) | ((uint32_t)i << 16);
-    hi.z = a0 | (a1 << 16);
-    hi.w = npriv | (np << 16) | (nsh << 24) | ((uint32_t)(depth & 1) << 31);
-    uint4* dst = reinterpret_cast<uint4*>(g_rec + i);
-    dst[0] = lo;
-    dst[1] = hi;
-  };
-
+  // With the streamed path on, param_class_kernel has run first and has checked the param CSR against the
+  // descriptor; a topology it rejected is not looked at again.
+  if (w.nshared != nullptr && w.topo_status[t] != DLS_ST_OK) return;
   if (tid == 0) { s_maxd = 0; s_maxdeg = 0; }
   __syncthreads();
   // ---- validate the descriptor slice (never trust indices that address shared memory) ----
@@ -164,10 +130,6 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     // repeated only while one of its tasks still depends on another task of the same chunk whose depth moved.
     for (int base = 0; base < n; base += blockDim.x) {
       const int i = base + tid;
-      // (the record's values from global memory: in flight while the chunk's depths settle)
-      double rm = 0.0, rc = 0.0;
-      uint32_t rqb = 0, rqe = 0;
-      if (g_rec && i < n) { rm = __ldg(g_mem + i); rc = __ldg(g_dur + i); rqb = __ldg(v.par_ptr + i); rqe = __ldg(v.par_ptr + i + 1); }
       const uint32_t eb = i < n ? pptr[i] : 0, ee = i < n ? pptr[i + 1] : 0, np = ee - eb;
       const uint32_t p0 = np > 0 ? pidx[eb] : 0, p1 = np > 1 ? pidx[eb + 1] : 0, p2 = np > 2 ? pidx[eb + 2] : 0;
       const bool inside = (np > 0 && (int)p0 >= base) || (np > 1 && (int)p1 >= base) || (np > 2 && (int)p2 >= base) || np > 3;
@@ -185,7 +147,6 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
         if (moved) s_depth[i] = (uint16_t)d;
         again = __syncthreads_or(moved) && any_inside;
       } while (again);
-      if (g_rec && i < n) emit_record(i, np, p0, p1, p2, (int)s_depth[i], rm, rc, rqb, rqe);
     }
     __syncthreads();
   } else {
@@ -207,16 +168,6 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   if (changed) {
     if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
     return;
-  }
-  if (g_rec && unsorted) {  // (the in-order pass above writes the records as it goes)
-    for (int i = tid; i < n; i += blockDim.x) {
-      const uint32_t eb = pptr[i], np = pptr[i + 1] - eb;
-      emit_record(i, np, np > 0 ? pidx[eb] : 0, np > 1 ? pidx[eb + 1] : 0, np > 2 ? pidx[eb + 2] : 0, (int)s_depth[i],
-                  __ldg(g_mem + i), __ldg(g_dur + i), __ldg(v.par_ptr + i), __ldg(v.par_ptr + i + 1));
-    }
-  }
-  if (g_rec && __syncthreads_or(unstreamable)) {
-    if (tid == 0) w.nshared[t] = kUnstreamable;  // a count no record can hold: the general kernels take this DAG
   }
   if (tid == 0) w.topo_status[t] = DLS_ST_OK;
   {

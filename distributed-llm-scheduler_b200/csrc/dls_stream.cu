@@ -1,15 +1,18 @@
-// dls_stream.cu — the throughput path: one THREAD per DAG instance.
+// dls_stream.cu — the throughput path: one THREAD per DAG instance over an order-permuted record stream.
 //
 // Why: the list-scheduling loop is a serial chain of n dependent steps per DAG, but a sweep has ~10^5..10^6
 // independent DAGs. With one warp per DAG every instruction of the chain serves one DAG (≈340 warp-instructions per
-// task-step, profiles/r1a_*); with one thread per DAG the same instruction serves 32. To make that work a step must
-// cost a thread ONE memory access: kernel P leaves, per instance, one array of 32-byte task records (dls::Rec, one
-// DRAM sector each, in task order, independent of the processing order) next to the three static orders, and a
-// scheduling thread walks `rec[order[t]]`: the order indices arrive eight at a time (one 16-byte load per eight
-// steps), the record by one 256-bit load issued two steps ahead. Per-thread mutable state lives in shared memory laid
-// out [word][lane] (each lane owns a bank: no conflicts whatever the index), including one done-bit per task.
-// (Round 1 rewrote every instance three times into order-permuted record streams so that the threads could read
-// sequentially: 96 KB written and read back per 1k-task instance and a 4.3 ms kernel for 131k instances.)
+// task-step, profiles/r1a_*); with one thread per DAG the same instruction serves 32. To make that work the
+// per-thread memory accesses must not scatter: stream_build_kernel writes each DAG, once per processing order, as a
+// contiguous array of 32-byte records (dls::Rec, one DRAM sector per step), so every step of every thread reads
+// exactly one fully used sector, and per-thread mutable state lives in shared memory laid out [word][lane] (each lane
+// owns a bank: no conflicts whatever the index), including one done-bit per task.
+//
+// A record does not depend on the order it is placed in (dependencies are task ids, a new round is the depth parity
+// flipping): the build kernel makes every record once, in task order with coalesced reads, and then only permutes.
+// (Round 1 translated dependencies to order positions per stream: an inverted order per stream, three look-ups per
+// record and a 4.3 ms kernel. Round 2a tried no streams at all — one record array read through the order arrays — and
+// found every 32-byte read costing a 128-byte DRAM line: the scheduling kernels ran 2.4x slower.)
 //
 // Verdicts are written in order-position space (sequential bytes per thread, stored a word at a time);
 // unpermute_kernel maps them back to task ids and derives seq_pos by a prefix count. Instances the fast kernels
@@ -32,99 +35,158 @@ namespace {
 constexpr int kRouteGeneral = 1, kRouteFailRest = 2, kRouteTwin = 4, kRouteOpen = 0xFF;
 constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG DFS/Greedy/Critical kernels
 constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp CTAs, 7 instead of 6 warps/SM, are slower)
+#ifndef DLS_S_MINB
+#define DLS_S_MINB 1
+#endif
+constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
 constexpr int kBitmapWordsMax = 64;  // done-bits in shared memory up to 2048 tasks per DAG; beyond, done-bytes in HBM
 
 // -------------------------------------------------------------------------------------------------------------------
-// record_expand_kernel: T == 1 (one topology, B instances). The topology kernel wrote one record per task; every
-// instance gets its own copy, with its own duration / memory where the batch carries them per instance.
+// stream_build_kernel: grid B. One CTA per instance makes the instance's records and writes them in every requested
+// processing order.
 // -------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) record_expand_kernel(dls_batch_t b, Workspace w) {
-  if (w.topo_status[0] != DLS_ST_OK) return;
-  const int n = (int)(b.task_off[1] - b.task_off[0]);
-  const long long total = (long long)n * b.B;
-  const bool dur_pi = (b.flags & DLS_F_DUR_PER_INSTANCE) != 0, mem_pi = (b.flags & DLS_F_MEM_PER_INSTANCE) != 0;
-  for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < total; k += (long long)gridDim.x * blockDim.x) {
-    const int i = (int)(k % n);
-    const uint4* src = reinterpret_cast<const uint4*>(w.rec_topo + i);
-    uint4 lo = __ldg(src), hi = __ldg(src + 1);
-    if (mem_pi) { const double m = __ldg(b.mem + k); lo.x = (uint32_t)__double2loint(m); lo.y = (uint32_t)__double2hiint(m); }
-    if (dur_pi) { const double c = __ldg(b.dur + k); lo.z = (uint32_t)__double2loint(c); lo.w = (uint32_t)__double2hiint(c); }
-    uint4* dst = reinterpret_cast<uint4*>(w.rec_inst + k);
-    dst[0] = lo;
-    dst[1] = hi;
+struct RecRegs {
+  uint4 lo, hi;
+};
+
+// The record of task i (dls::Rec) from the instance's arrays. Sets `unstreamable` when a count does not fit its field.
+__device__ __forceinline__ RecRegs make_record(const Inst& v, int i, const uint16_t* depth, int nsh_topo, const uint16_t* sid,
+                                               int& unstreamable) {
+  const double m = __ldg(v.mem + i), c = __ldg(v.dur + i);
+  const uint32_t pb = __ldg(v.pred_ptr + i), pe = __ldg(v.pred_ptr + i + 1);
+  const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
+  uint32_t np = pe - pb;
+  const uint32_t p0 = np > 0 ? __ldg(v.pred_idx + pb) : 0u;
+  const uint32_t p1 = np > 1 ? __ldg(v.pred_idx + pb + 1) : 0u;
+  const uint32_t p2 = np > 2 ? __ldg(v.pred_idx + pb + 2) : 0u;
+  const uint32_t d = __ldg(depth + i);
+  uint32_t nsh = 0, a0 = 0, a1 = 0, npriv = qe - qb;
+  if (nsh_topo > 0) {  // (no shared param in the DAG: nothing to look up, par_sid not even written)
+    npriv = 0;
+    for (uint32_t e = qb; e < qe; ++e) {
+      const uint32_t sd = sid[__ldg(v.par_idx + e)];
+      if (sd == 0xFFFF) { ++npriv; continue; }
+      if (nsh == 0) a0 = sd;
+      else if (nsh == 1) a1 = sd;
+      ++nsh;
+    }
   }
+  if (np >= 255u || nsh >= 127u || npriv > 65535u) {
+    unstreamable = 1;
+    np = min(np, 255u); nsh = min(nsh, 127u); npriv = min(npriv, 65535u);
+  }
+  RecRegs r;
+  r.lo.x = (uint32_t)__double2loint(m); r.lo.y = (uint32_t)__double2hiint(m);
+  r.lo.z = (uint32_t)__double2loint(c); r.lo.w = (uint32_t)__double2hiint(c);
+  r.hi.x = p0 | (p1 << 16);
+  r.hi.y = p2 | ((uint32_t)i << 16);
+  r.hi.z = a0 | (a1 << 16);
+  r.hi.w = npriv | (np << 16) | (nsh << 24) | ((d & 1u) << 31);
+  return r;
+}
+
+__device__ __forceinline__ void store_rec(Rec* p, const RecRegs& r) {
+#if defined(DLS_ST_V4)
+  uint4* q = reinterpret_cast<uint4*>(p);
+  q[0] = r.lo;
+  q[1] = r.hi;
+#else
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(r.lo.x), "r"(r.lo.y), "r"(r.lo.z),
+               "r"(r.lo.w), "r"(r.hi.x), "r"(r.hi.y), "r"(r.hi.z), "r"(r.hi.w)
+               : "memory");
+#endif
+}
+
+// `staged`: the records are made in task order (coalesced reads) into shared memory, two 16-byte halves in two arrays
+// (with whole 32-byte records every first half starts on one of only four bank groups: 3.5 wavefronts per ideal one on
+// the gather, ncu source view round 1i), and each order then gathers them. Without (DAGs beyond ~7k tasks): every
+// thread makes the record of the task at its position, once per order.
+__global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t b, Workspace w, int kind_mask, int staged) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int inst = blockIdx.x;
+  Inst v;
+  bind_instance(b, inst, v);
+  if (w.topo_status[v.topo] != DLS_ST_OK) return;
+  const int n = v.n;
+  if (n == 0) return;
+  const int nsh_topo = w.nshared[v.topo];
+  const uint16_t* depth = w.depth + v.t_topo;
+  const uint16_t* sid = w.par_sid + b.pid_off[v.topo];
+  const uint16_t* g_order[3] = {w.order_dg + v.t_topo, w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo),
+                                w.order_mru + v.t_topo};
+  static_assert(kOrderDG == 0 && kOrderCP == 1 && kOrderMRU == 2, "order table follows the order kinds");
+  bool use[3];
+#pragma unroll
+  for (int kind = 0; kind < 3; ++kind)  // DAGs the thread-per-DAG kernels leave to the general ones get no stream
+    use[kind] = ((kind_mask >> kind) & 1) && (kind == kOrderMRU ? nsh_topo == 0 : nsh_topo <= kSharedCap);
+  if (!use[0] && !use[1] && !use[2]) return;
+  int unstreamable = 0;
+  if (staged) {
+    uint4* s_lo = reinterpret_cast<uint4*>(smem_raw);  // [n]
+    uint4* s_hi = s_lo + n;                            // [n]
+    strided_for<4>(n, [&](int i) {
+      const RecRegs r = make_record(v, i, depth, nsh_topo, sid, unstreamable);
+      s_lo[i] = r.lo;
+      s_hi[i] = r.hi;
+    });
+    __syncthreads();
+    // position t of all the orders in one iteration: three independent gathers per thread
+    strided_for<2>(n, [&](int t) {
+#pragma unroll
+      for (int kind = 0; kind < 3; ++kind) {
+        if (!use[kind]) continue;
+        const int i = __ldg(g_order[kind] + t);
+        RecRegs r;
+        r.lo = s_lo[i];
+        r.hi = s_hi[i];
+        store_rec(w.stream[kind] + v.t_inst + t, r);
+      }
+    });
+  } else {
+    for (int kind = 0; kind < 3; ++kind) {
+      if (!use[kind]) continue;
+      strided_for<2>(n, [&](int t) {
+        const int i = __ldg(g_order[kind] + t);
+        store_rec(w.stream[kind] + v.t_inst + t, make_record(v, i, depth, nsh_topo, sid, unstreamable));
+      });
+    }
+  }
+  // a count no record can hold: the general kernels take this DAG (nshared is what routes it there)
+  if (unstreamable) w.nshared[v.topo] = kUnstreamable;
 }
 
 // -------------------------------------------------------------------------------------------------------------------
 // Shared pieces of the thread-per-DAG kernels
 // -------------------------------------------------------------------------------------------------------------------
-struct RecRegs {
-  uint4 lo, hi;
-};
 __device__ __forceinline__ RecRegs load_rec(const Rec* p) {
   RecRegs r;
   const uint4* q = reinterpret_cast<const uint4*>(p);
-  // one 256-bit load instead of two 128-bit ones halves the requests of the 32 lanes, each on its own line
-  // (a record is read once: keeping it out of L1 took 35 % off the MRU kernel, measured round 2a)
-#if defined(DLS_REC_L1ALLOC)
-  asm volatile("ld.global.nc.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+  // L2::128B: a miss in L2 brings in the whole 128-byte line, i.e. this DAG's next three records as well
+  // and one 256-bit load instead of two 128-bit ones halves the requests of the 32 lanes, each on its own line.
+  // L1::no_allocate: a record is read once; kept out of L1 the MRU kernel runs 2.19 instead of 2.87 ms (round 2b)
+#if !defined(DLS_REC_L1ALLOC)
+  asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
 #else
-  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+  asm volatile("ld.global.nc.L2::128B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
 #endif
                : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
                : "l"(q));
   return r;
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // Field accessors of a record held in registers (layout of dls::Rec).
 __device__ __forceinline__ double rec_m(const RecRegs& r) { return __hiloint2double((int)r.lo.y, (int)r.lo.x); }
 __device__ __forceinline__ double rec_c(const RecRegs& r) { return __hiloint2double((int)r.lo.w, (int)r.lo.z); }
 __device__ __forceinline__ uint32_t rec_p0(const RecRegs& r) { return r.hi.x & 0xffff; }
 __device__ __forceinline__ uint32_t rec_p1(const RecRegs& r) { return r.hi.x >> 16; }
 __device__ __forceinline__ uint32_t rec_p2(const RecRegs& r) { return r.hi.y & 0xffff; }
+__device__ __forceinline__ int rec_id(const RecRegs& r) { return (int)(r.hi.y >> 16); }
 __device__ __forceinline__ int rec_a0(const RecRegs& r) { return (int)(r.hi.z & 0xffff); }
 __device__ __forceinline__ int rec_a1(const RecRegs& r) { return (int)(r.hi.z >> 16); }
 __device__ __forceinline__ int rec_npriv(const RecRegs& r) { return (int)(r.hi.w & 0xffff); }
 __device__ __forceinline__ int rec_npred(const RecRegs& r) { return (int)((r.hi.w >> 16) & 0xff); }
 __device__ __forceinline__ int rec_nsh(const RecRegs& r) { return (int)((r.hi.w >> 24) & 0x7f); }
 __device__ __forceinline__ int rec_parity(const RecRegs& r) { return (int)(r.hi.w >> 31); }
-
-// A thread's walk over its order array: u16 task ids, fetched as aligned 16-byte groups (one load per eight steps,
-// the group after the current one already in flight).
-struct OrderCursor {
-  const uint4* next;   // next aligned group to fetch
-  unsigned long long lo, hi;  // ids not yet handed out, lowest first
-  uint4 ahead;         // the group after those (in flight)
-  int left;            // ids left in lo/hi
-  int groups;          // groups not yet fetched
-  __device__ __forceinline__ void set(const uint4& g) {
-    lo = (unsigned long long)g.x | ((unsigned long long)g.y << 32);
-    hi = (unsigned long long)g.z | ((unsigned long long)g.w << 32);
-  }
-  __device__ __forceinline__ void init(const uint16_t* order, int n) {  // n > 0
-    const uintptr_t a = reinterpret_cast<uintptr_t>(order);
-    const int mis = (int)(a & 15) >> 1;
-    next = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
-    groups = (mis + n + 7) >> 3;
-    const uint4 g = __ldg(next++);
-    --groups;
-    ahead = make_uint4(0, 0, 0, 0);
-    if (groups > 0) { ahead = __ldg(next++); --groups; }
-    set(g);
-    for (int k = 0; k < mis; ++k) { lo = (lo >> 16) | (hi << 48); hi >>= 16; }
-    left = 8 - mis;
-  }
-  __device__ __forceinline__ int take() {
-    const int i = (int)(lo & 0xffffull);
-    lo = (lo >> 16) | (hi << 48);
-    hi >>= 16;
-    if (--left == 0) {
-      set(ahead);
-      left = 8;
-      if (groups > 0) { ahead = __ldg(next++); --groups; }
-    }
-    return i;
-  }
-};
 
 // A thread's verdict bytes (node or DLS_TASK_*) by order position. They leave in aligned words: 32 lanes storing one
 // byte each to 32 different lines cost the L1-to-L2 request path — what bounds these kernels — as much as a record
@@ -242,7 +304,7 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
 // DFS / Greedy / Critical, one thread per DAG
 // -------------------------------------------------------------------------------------------------------------------
 template <int ALGO, int KMAX, bool PEAK>
-__global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+__global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
                                                        int twin_mode, int twin_slot, int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -286,9 +348,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
     if (have && twin_mode == 1) w.route[(int64_t)twin_slot * b.B + inst] = kRouteOpen;
     return;
   }
-  const Rec* rec = w.rec_inst + v.t_inst;
-  const uint16_t* order = ALGO == DLS_ALGO_CRITICAL ? w.order_cp + (w.cp_per_instance ? v.t_inst : v.t_topo)
-                                                    : w.order_dg + v.t_topo;
+  const Rec* rec = w.stream[ALGO == DLS_ALGO_CRITICAL ? kOrderCP : kOrderDG] + v.t_inst;
   const uint16_t* sid = w.par_sid + (have ? b.pid_off[v.topo] : 0);
   VerdictOut vout;
   vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
@@ -339,19 +399,15 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
   bool running = elig, any_ready = false, any_assigned = false;
   bool clean = true;  // no task so far was failed or left pending: every dependency of the next task is done
   int prev_par = 0;
-  OrderCursor oc;
-  RecRegs r0, r1;
-  r0.lo = r0.hi = r1.lo = r1.hi = make_uint4(0, 0, 0, 0);
-  int i0 = 0, i1 = 0;
-  if (n > 0) { oc.init(order, n); i0 = oc.take(); r0 = load_rec(rec + i0); }
-  if (n > 1) { i1 = oc.take(); r1 = load_rec(rec + i1); }
+  RecRegs cur;
+  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
+  if (n > 0) cur = load_rec(rec);
   for (int t = 0; t < n_warp; ++t) {
-    const RecRegs cur = r0;
-    const int i = i0;
-    r0 = r1;
-    i0 = i1;
-    if (t + 2 < n) { i1 = oc.take(); r1 = load_rec(rec + i1); }
+    RecRegs nxt = cur;
+    if (t + 1 < n) nxt = load_rec(rec + t + 1);
+    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);  // once per 128-byte line; (measured: of no use to MRU)
     if (t < n) {
+      const int i = rec_id(cur);
       const double m = rec_m(cur), c = rec_c(cur);
       const int npred = rec_npred(cur), npriv = rec_npriv(cur), nsh = rec_nsh(cur);
       const int par = rec_parity(cur);
@@ -468,6 +524,7 @@ __global__ void __launch_bounds__(kTPB) sched_stream_kernel(dls_batch_t b, dls_r
       if (verdict < 0) clean = false;
       vout.put(t, verdict, t == n - 1);
     }
+    cur = nxt;
   }
   if (elig) {
     if (running) {
@@ -513,7 +570,7 @@ __device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_
 }
 
 template <int KMAX, bool PEAK>
-__global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+__global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
                                                                  int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -542,8 +599,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   const int n = elig ? v.n : 0, K = v.K;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
   if (n_warp == 0) return;
-  const Rec* rec = w.rec_inst + v.t_inst;
-  const uint16_t* order = w.order_mru + v.t_topo;
+  const Rec* rec = w.stream[kOrderMRU] + v.t_inst;
   VerdictOut vout;
   vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
   DoneSet done;
@@ -576,19 +632,14 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
   int carried = 0;
   bool running = elig, any_ready = false, any_assigned = false, clean = true;
   int prev_par = 0;
-  OrderCursor oc;
-  RecRegs r0, r1;
-  r0.lo = r0.hi = r1.lo = r1.hi = make_uint4(0, 0, 0, 0);
-  int i0 = 0, i1 = 0;
-  if (n > 0) { oc.init(order, n); i0 = oc.take(); r0 = load_rec(rec + i0); }
-  if (n > 1) { i1 = oc.take(); r1 = load_rec(rec + i1); }
+  RecRegs cur;
+  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
+  if (n > 0) cur = load_rec(rec);
   for (int t = 0; t < n_warp; ++t) {
-    const RecRegs cur = r0;
-    const int i = i0;
-    r0 = r1;
-    i0 = i1;
-    if (t + 2 < n) { i1 = oc.take(); r1 = load_rec(rec + i1); }
+    RecRegs nxt = cur;
+    if (t + 1 < n) nxt = load_rec(rec + t + 1);
     if (t < n) {
+      const int i = rec_id(cur);
       const double m = rec_m(cur), c = rec_c(cur);
       const int npred = rec_npred(cur), npar = rec_npriv(cur);
       const int par = rec_parity(cur);
@@ -694,6 +745,7 @@ __global__ void __launch_bounds__(kTPBM) sched_stream_mru_kernel(dls_batch_t b, 
       if (verdict < 0) clean = false;
       vout.put(t, verdict, t == n - 1);
     }
+    cur = nxt;
   }
   if (elig) {
     if (running) {
@@ -812,12 +864,15 @@ static cudaError_t launch_fast(Kern kern, int kernel_id, dim3 grid, int threads,
   return cudaGetLastError();
 }
 
-cudaError_t launch_record_expand(const dls_batch_t& b, const Workspace& w, LaunchCtx& ctx) {
-  const long long total = b.nt_inst;
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  const int grid = blocks > 0 ? (int)blocks : 1;
-  return launch_fast(record_expand_kernel, DLS_KERNEL_RECORD_EXPAND, dim3(grid), 256, 0, ctx, b, w);
+cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
+  int kinds = 0;
+  if (algo_mask & 3) kinds |= 1 << kOrderDG;
+  if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kOrderCP;
+  if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kOrderMRU;
+  const size_t smem = (size_t)b.n_max * 32;
+  const int staged = smem <= 200 * 1024;
+  return launch_fast(stream_build_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B), kBuildThreads, staged ? smem : 0, ctx, b, w, kinds,
+                     staged);
 }
 
 template <int KMAX, bool PEAK>

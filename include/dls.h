@@ -279,7 +279,7 @@ int64_t dls_launch_count(void);
 #define DLS_KERNEL_SCHED_CRITICAL 4
 #define DLS_KERNEL_SCHED_MRU 5
 #define DLS_KERNEL_PARAM_CLASS 6
-#define DLS_KERNEL_RECORD_EXPAND 7
+#define DLS_KERNEL_STREAM_BUILD 7
 #define DLS_KERNEL_STREAM_DFS 8
 #define DLS_KERNEL_STREAM_GREEDY 9
 #define DLS_KERNEL_STREAM_CRITICAL 10

@@ -170,7 +170,7 @@ def test_streamed_path_is_taken_and_falls_back():
     names = {lib.dls_kernel_name(k).decode(): int(cnt[k]) for k in range(N.NUM_KERNELS)}
     assert names["sched_stream_kernel<DFS>"] == 1 and names["sched_stream_mru_kernel"] == 1 and names["unpermute_kernel"] == 1
     assert names["priority_topology_kernel"] == 1 and names["param_class_kernel"] == 1
-    assert names["record_expand_kernel"] == 0   # one topology per instance: the topology kernel's records are read as they are
+    assert names["stream_build_kernel"] == 1
     old = lib.dls_set_stream_path(0)
     try:
         slow = schedule_batch(batch, N.MASK_ALL).host()
