@@ -2,23 +2,29 @@
 """bench.py — DAG schedules/sec on 1k-task DAGs (BASELINE.json metric), one process per GPU.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--instances B_per_gpu] [--impl reference]
+                    [--workload random1k|cfg3|cfg4]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
 
-A step = one pass of the hot path (priority kernels + the four list-scheduling kernels) over one batch of
-synthetic random 1k-task DAG instances per GPU (config-5 shape: n=1000, K=8 nodes, memory regime 0.9, all four
-algorithms). Instances are sharded across ranks with no data-path collective; the only collective is the
-all-gather of the fixed-size per-instance result records, done inside every step when N>1.
+A step = one pass of the hot path (priority kernels, stream build, the four list-scheduling kernels, unpermute) over
+one batch of synthetic DAG instances per GPU. Default workload `random1k` = config-5 shape (n=1000, K=8 nodes, memory
+regime 0.9, all four algorithms, peak memory on); `cfg3` = GPT-2 DAG x 100,000 perturbed-duration instances on 8
+capped devices (one shared topology); `cfg4` = 48-layer x 205-head LLM DAG (9,986 tasks) x 512 instances. Instances
+are sharded across ranks with no data-path collective; the only collective is ONE all-gather of the fixed-size
+per-instance result records (makespan, peak memory, counters) after the last step of the sweep.
 
 value  = schedules/s with inputs resident in HBM (CUDA events, max over ranks).
-e2e    = the same through the public API with HOST inputs (PipelinedScheduler): pinned host->device copy of the
-         batch, the C-ABI calls, device->host copy of every result array, each step; chunks overlap on 3 streams.
+e2e    = the same through the public API with HOST inputs: pinned host->device copy of the batch, the C-ABI calls,
+         device->host copy of the results, each step (random1k: PipelinedScheduler, chunks overlapped on 3 streams).
 roofline = dominant kernel (largest share of the timed region, CUDA events recorded by the library on the launch
          stream): algorithmic bytes per launch (29n + 4(E+R) + 28K + 32 per schedule) / duration,
          against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
-cpu_baseline / --impl reference = the CPU oracle (C port of the reference's algorithm, oracle/dls_oracle.c) on all
-         host threads over a bounded sample of the same workload. The reference itself is CPython and does not
-         exist on the GPU box; its measured single-core numbers are in BASELINE.md section 2.
+parity = the CPU oracle's results for the first instances of the step (the cpu_baseline sample) compared field by
+         field, bit for bit, with what the GPU produced for the same instances (outside every timed region).
+cpu_baseline / --impl reference = the CPU oracle (C port of the reference's algorithm, oracle/dls_oracle.c) on the
+         host's threads over a bounded sample of THE SAME instances (same generator, seed and tie-break order; built
+         on the host by the numpy port of the generator kernels). The reference itself is CPython and does not exist
+         on the GPU box; its measured numbers are in BASELINE.md section 2.
 """
 from __future__ import annotations
 
@@ -37,8 +43,10 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 N_TASKS, K_NODES, REGIME = 1000, 8, 0.9
+SEED = 1000
 METRIC = "DAG schedules/sec (1k-task DAGs)"
 UNIT = "schedules/s"
+ALGO_LABEL = ("DFS", "Greedy", "Critical", "MRU_spec")
 
 
 def parse():
@@ -46,15 +54,34 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--instances", type=int, default=131072, help="DAG instances per GPU per step")
+    ap.add_argument("--instances", type=int, default=0, help="DAG instances per GPU per step (0 = the workload's default)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="random1k", choices=["random1k", "cfg3", "cfg4"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-peak", action="store_true", help="do not track peak memory (for the with/without comparison)")
+    ap.add_argument("--results", default="full", choices=["full", "summary"],
+                    help="what the end-to-end leg brings back to the host: every array, or the per-instance records, "
+                         "node finish times and task counts only")
     return ap.parse_args()
 
 
-def algorithmic_bytes(batch, per_schedule=True):
-    """B(n,E,R,K) = 29n + 4(E+R) + 28K + 32 bytes per (instance, algorithm), summed over the batch."""
-    return 29 * batch.nt_inst + 4 * (batch.e_total + batch.r_total) + 28 * batch.nk_inst + 32 * batch.B
+def tie_break_rank(n):
+    """pi is an input (the reference takes it from CPython's set order, which changes with the process's hash seed):
+    the bench fixes one permutation so that every rank, both arms and every run schedule the same instances."""
+    return np.random.default_rng(12345).permutation(n).astype(np.uint16)
+
+
+def algorithmic_bytes(batch):
+    """B(n,E,R,K) = 29n + 4(E+R) + 28K + 32 bytes per (instance, algorithm), summed over the batch.
+    Shared-topology batches (T == 1): per-instance unique bytes only — the perturbed durations 8n (+ 8n memory) and the
+    outputs 3n + 12K + 24 — plus the topology once."""
+    if batch.T == batch.B:
+        return 29 * batch.nt_inst + 4 * (batch.e_total + batch.r_total) + 28 * batch.nk_inst + 32 * batch.B
+    n = int(batch.task_off[1])
+    per_inst = 3 * n + 12 * batch.K_max + 24
+    per_inst += 8 * n * (bool(batch.flags & 1) + bool(batch.flags & 2))
+    once = 26 * n + 4 * (batch.e_total + batch.r_total) + 16 * batch.K_max + 8
+    return per_inst * batch.B + once
 
 
 def priority_bytes(batch):
@@ -129,55 +156,162 @@ class ClockSampler:
         return out
 
 
-def cpu_sample(oracle, batch, threads, target_s):
-    """Oracle (C port) on all host threads over a bounded sample; returns (schedules/s, sample description)."""
-    from dls_b200 import _native as N
-    pilot = batch.shard(0, min(batch.B, max(threads, 8)))
-    t0 = time.perf_counter()
-    oracle.schedule_batch(pilot, N.MASK_ALL, nthreads=threads)
-    dt = max(time.perf_counter() - t0, 1e-4)
-    per_inst = dt / pilot.B
-    m = int(min(batch.B, max(pilot.B, target_s / per_inst)))
-    m = max(threads, m // threads * threads)
-    sample = batch.shard(0, min(m, batch.B))
-    t0 = time.perf_counter()
-    oracle.schedule_batch(sample, N.MASK_ALL, nthreads=threads)
-    dt = time.perf_counter() - t0
-    return 4 * sample.B / dt, f"{sample.B} of the step's instances x 4 algorithms, {dt:.1f} s on {threads} threads", sample.B, dt
+# ---- workloads ----------------------------------------------------------------------------------------------------
+
+class Random1k:
+    """config 5 shape: every instance its own random 1k-task DAG (generate_random_dag's distribution)."""
+    name, default_B, mask = "random1k", 131072, 0xF
+
+    def describe(self):
+        return (f"random-1k (config-5 shape): n={N_TASKS} tasks, K={K_NODES} nodes, memory regime {REGIME}, algorithms "
+                f"DFS+Greedy+Critical+MRU_spec, counter-hash generator seed {SEED}+rank, fixed tie-break permutation")
+
+    def device_batch(self, B, rank_id, device):
+        from dls_b200.gen import random_dag_batch_device
+        return random_dag_batch_device(B, N_TASKS, K_NODES, REGIME, seed=SEED + rank_id, device=device, rank=tie_break_rank(N_TASKS))
+
+    def host_batch(self, B, rank_id, first=0):
+        from dls_b200.gen import random_dag_batch_counter
+        return random_dag_batch_counter(B, N_TASKS, K_NODES, REGIME, seed=SEED + rank_id, rank=tie_break_rank(N_TASKS), first=first)
+
+
+class SharedTopology:
+    """configs 3 and 4: one DAG, B instances with durations perturbed by +-10 % (T == 1, DLS_F_DUR_PER_INSTANCE)."""
+    mask = 0xF
+
+    def __init__(self, name):
+        from dls_b200 import gen
+        self.name = name
+        if name == "cfg3":  # GPT-2 small DAG of test_gpt2.py on the four laptops listed twice (SURVEY.md 8d)
+            self.dag, self.default_B = gen.gpt2_dag(), 100_000
+            self.cap = np.array([8.0, 8.0, 6.0, 6.0] * 2)
+            self.spd = np.array([1.0, 1.2, 0.8, 0.9] * 2)
+            self.text = "cfg3: GPT-2 small DAG (99 tasks, 1 shared param) on 8 capped devices"
+        else:               # 48 layers x 205 heads, create_nodes_with_memory_regime(total, 0.9, 8)
+            self.dag, self.default_B = gen.llm_dag(48, 205, 205), 512
+            npar = np.diff(self.dag.par_ptr.astype(np.int64))
+            total = np.array([(self.dag.mem + npar * 0.5).max() + self.dag.P * 0.5])
+            cap, spd = gen.node_sets(total, 0.9, 8, np.random.default_rng(SEED))
+            self.cap, self.spd = cap[0], spd[0]
+            self.text = "cfg4: 48-layer x 205-head LLM DAG (9,986 tasks) on 8 nodes at memory regime 0.9"
+        self.dag.rank = tie_break_rank(self.dag.n)
+
+    def describe(self):
+        return (f"{self.text}, durations perturbed +-10 % per instance (seed {SEED}+rank), one shared topology, algorithms "
+                "DFS+Greedy+Critical+MRU_spec, fixed tie-break permutation")
+
+    def host_batch(self, B, rank_id, first=0):
+        from dls_b200.gen import perturbed_durations
+        from dls_b200.lowering import DagBatch
+        dur = perturbed_durations(self.dag, first + B, 0.1, seed=SEED + rank_id)[first:]
+        return DagBatch.shared_topology(self.dag, self.cap, self.spd, B, dur=dur)
+
+    def device_batch(self, B, rank_id, device):
+        from dls_b200.batch import DeviceBatch
+        return DeviceBatch(self.host_batch(B, rank_id), device)
+
+
+def make_workload(name):
+    return Random1k() if name == "random1k" else SharedTopology(name)
+
+
+# ---- the CPU arm ----------------------------------------------------------------------------------------------------
+
+def oracle_time(oracle, sample, mask, threads, reps=1):
+    best = None
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        res = oracle.schedule_batch(sample, mask, nthreads=threads)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return best, res
+
+
+def cpu_sample_size(oracle, wl, rank_id, threads, target_s, cap):
+    """How many of the step's first instances ~target_s seconds of all-thread oracle time cover (all four algorithms)."""
+    pilot = wl.host_batch(min(cap, max(threads, 8)), rank_id)
+    dt, _ = oracle_time(oracle, pilot, wl.mask, threads)
+    per_inst = max(dt, 1e-4) / pilot.B
+    m = int(min(cap, max(pilot.B, target_s / per_inst)))
+    return max(threads, m // threads * threads) if cap >= threads else cap
+
+
+def cpu_baseline(oracle, wl, rank_id, threads, target_s, cap):
+    """The oracle over the first instances of this rank's step: all algorithms on all host threads (the blended
+    figure), each algorithm on its own (MRU is the slow one: per-eviction rescans of the pending set,
+    ref schedulers.py:396-400), and one thread alone. Returns (record, sample batch, oracle results of the blended run)."""
+    m = cpu_sample_size(oracle, wl, rank_id, threads, target_s * 0.55, cap)
+    sample = wl.host_batch(m, rank_id)
+    dt_all, res = oracle_time(oracle, sample, wl.mask, threads)
+    per_algo, per_algo_1 = {}, {}
+    small = sample.shard(0, max(1, min(m, max(threads, m // 4))))
+    for a in range(4):
+        dt, _ = oracle_time(oracle, small, 1 << a, threads)
+        per_algo[ALGO_LABEL[a]] = small.B / dt
+    one = sample.shard(0, max(1, min(m, max(2, m // (4 * threads)))))
+    for a in range(4):
+        dt, _ = oracle_time(oracle, one, 1 << a, 1)
+        per_algo_1[ALGO_LABEL[a]] = one.B / dt
+    rec = {"value": 4 * sample.B / dt_all, "unit": UNIT, "cores": threads, "kind": "port",
+           "sample": f"first {sample.B} instances of the step x 4 algorithms, {dt_all:.1f} s on {threads} threads "
+                     "(oracle/dls_oracle.c, C port of the reference's algorithm)",
+           "host_threads": os.cpu_count(),
+           "per_algorithm": {k: {"all_threads": v, "one_thread": per_algo_1[k]} for k, v in per_algo.items()},
+           "per_algorithm_sample": f"{small.B} instances on {threads} threads, {one.B} on one thread"}
+    return rec, sample, res
+
+
+def parity_check(res, want, m, n, K):
+    """Device results (BatchResult of the resident run) against the oracle's for the first m instances: node_of, seq_pos,
+    the whole per-instance record, cnt and the fp64 bits of fin / avail / peak. Returns the `parity` record."""
+    A = len(res.algos)
+    bits = lambda a: np.ascontiguousarray(a, np.float64).view(np.uint64)
+    bad = np.zeros((A, m), bool)
+    got_nodes = res.node_of[:, :m * n].cpu().numpy().reshape(A, m, n)
+    got_seq = res.seq_pos[:, :m * n].cpu().numpy().view(np.uint16).reshape(A, m, n)
+    bad |= (got_nodes != want.node_of.reshape(A, m, n)).any(2)
+    bad |= (got_seq != want.seq_pos.reshape(A, m, n)).any(2)
+    got_summ = res.summary[:, :m].cpu().numpy().view(want.summary.dtype).reshape(A, m)
+    fields = [f for f in want.summary.dtype.names if f != "peak" or res.peak is not None]
+    for f in fields:
+        g, w = got_summ[f], want.summary[f]
+        bad |= (bits(g) != bits(w)) if g.dtype.kind == "f" else (g != w)
+    bad |= (res.cnt[:, :m * K].cpu().numpy().reshape(A, m, K) != want.cnt.reshape(A, m, K)).any(2)
+    per_node = [("fin", want.fin), ("avail", want.avail)] + ([("peak", want.peak)] if res.peak is not None else [])
+    for f, w in per_node:
+        g = getattr(res, f)[:, :m * K].cpu().numpy()
+        bad |= (bits(g).reshape(A, m, K) != bits(w).reshape(A, m, K)).any(2)
+    return {"instances": int(m), "schedules": int(A * m), "mismatches": int(bad.sum()),
+            "compared": "node_of, seq_pos, summary record" + (" incl. peak" if res.peak is not None else "") +
+                        ", cnt, fin/avail" + ("/peak" if res.peak is not None else "") + " bits vs oracle/dls_oracle.c"}
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the CPU oracle port, all host threads, bounded sample per step. Rank 0 only."""
+    """--impl reference: the CPU oracle port on all host threads, each step a bounded sample of the GPU arm's own
+    instances (same generator, seed and tie-break order, built on the host). Rank 0 only."""
     if rank != 0:
         return
-    from dls_b200.gen import random_dag_batch
     from oracle import oracle
-    from dls_b200 import _native as N
     oracle.build()
+    wl = make_workload(args.workload)
     threads = os.cpu_count() or 1
-    batch = random_dag_batch(max(threads * 8, 256), N_TASKS, K_NODES, REGIME, seed=0)
-    # size one step to ~4 s of wall time
-    t0 = time.perf_counter()
-    oracle.schedule_batch(batch.shard(0, threads), N.MASK_ALL, nthreads=threads)
-    per_inst = (time.perf_counter() - t0) / threads
-    m = int(min(batch.B, max(threads, 4.0 / max(per_inst, 1e-6))))
-    m = max(threads, m // threads * threads)
-    sample = batch.shard(0, m)
+    B = args.instances or wl.default_B
+    m = cpu_sample_size(oracle, wl, 0, threads, 4.0, min(B, 4096))   # one step ~4 s of wall time
+    sample = wl.host_batch(m, 0)
     for _ in range(args.warmup):
-        oracle.schedule_batch(sample, N.MASK_ALL, nthreads=threads)
+        oracle.schedule_batch(sample, wl.mask, nthreads=threads)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        oracle.schedule_batch(sample, N.MASK_ALL, nthreads=threads)
+        oracle.schedule_batch(sample, wl.mask, nthreads=threads)
     dt = time.perf_counter() - t0
     val = 4 * sample.B * args.steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"random-1k (config-5 shape): n={N_TASKS}, K={K_NODES}, regime {REGIME}, DFS+Greedy+Critical+MRU; "
-                               f"bounded sample of {sample.B} instances per step on the host CPU"},
+        "config": {"workload": wl.describe(), "sample": f"first {sample.B} instances of rank 0's step, per step, on the host CPU"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{sample.B} instances x 4 algorithms per step, oracle/dls_oracle.c (C port of the "
+                         "sample": f"first {sample.B} instances x 4 algorithms per step, oracle/dls_oracle.c (C port of the "
                                    "reference's algorithm; the CPython reference cannot run on this box)"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -197,9 +331,8 @@ def main():
     import torch
     import torch.distributed as dist
     from dls_b200 import _native as N
-    from dls_b200.batch import BatchResult, DeviceBatch, pin_batch, schedule_batch
+    from dls_b200.batch import BatchResult, DeviceBatch, PipelinedScheduler, schedule_batch
     from dls_b200.dist import gather_summaries
-    from dls_b200.gen import random_dag_batch_device
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the scheduling path has no CPU implementation")
@@ -208,21 +341,21 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     lib = N.load()
+    wl = make_workload(args.workload)
+    B = args.instances or wl.default_B
+    peak = not args.no_peak
 
-    B = args.instances
-    # this rank's shard of the sweep, built on the device by the library's generator kernels;
-    # the host copy feeds the end-to-end leg (pinned host inputs) and the CPU baseline sample
-    dev = random_dag_batch_device(B, N_TASKS, K_NODES, REGIME, seed=1000 + rank, device=device)
-    host = dev.to_host()
-    res = BatchResult(host, N.MASK_ALL, device, peak=False, cached=False)
-    ws = torch.empty(int(lib.dls_workspace_bytes(C.byref(dev.struct), N.MASK_ALL)), dtype=torch.uint8, device=device)
+    # this rank's shard of the sweep (random1k: built on the device by the library's generator kernels);
+    # the host copy feeds the end-to-end leg (pinned host inputs)
+    dev = wl.device_batch(B, rank, device)
+    host = dev.to_host() if wl.name == "random1k" else dev.host
+    n, K = int(host.task_off[1] - host.task_off[0]), host.K_max
+    res = BatchResult(host, wl.mask, device, peak=peak, cached=False)
+    ws = torch.empty(int(lib.dls_workspace_bytes(C.byref(dev.struct), wl.mask)), dtype=torch.uint8, device=device)
     gathered = None
 
     def step_resident():
-        nonlocal gathered
-        schedule_batch(dev, N.MASK_ALL, workspace=ws, result=res)
-        if world > 1:
-            gathered = gather_summaries(res.summary, world)
+        schedule_batch(dev, wl.mask, workspace=ws, result=res)
 
     def barrier():
         if world > 1:
@@ -232,6 +365,8 @@ def main():
     # ---- resident-input timing -----------------------------------------------------------------------------------
     for _ in range(args.warmup):
         step_resident()
+    if world > 1:
+        gathered = gather_summaries(res.summary, world)  # (warm-up of the collective as well)
     barrier()
     clocks = ClockSampler(local) if rank == 0 else None
     lib.dls_profile_enable(1)
@@ -246,6 +381,8 @@ def main():
     ev0.record()
     for _ in range(args.steps):
         step_resident()
+    if world > 1:  # the sweep's one collective: every rank's per-instance records (makespan, peak memory, counters)
+        gathered = gather_summaries(res.summary, world)
     ev1.record()
     barrier()
     launches = int(lib.dls_launch_count() - launches0)
@@ -257,17 +394,33 @@ def main():
     ms_total = float(elapsed.item())
 
     # ---- end-to-end timing: host inputs in, host results out, every step -------------------------------------------
-    # Public API for host batches: PipelinedScheduler cuts the batch into chunks and overlaps the pinned
-    # host->device copy, the kernels and the device->host copy of the results on three streams.
-    from dls_b200.batch import PipelinedScheduler
-    pipe = PipelinedScheduler(host, N.MASK_ALL, device, chunks=24, nstreams=3)
+    if wl.name == "random1k":
+        # Public API for host batches: PipelinedScheduler cuts the batch into chunks and overlaps the pinned
+        # host->device copy, the kernels and the device->host copy of the results on three streams.
+        pipe = PipelinedScheduler(host, wl.mask, device, chunks=24, nstreams=3, results=args.results)
 
-    def step_e2e():
-        nonlocal gathered
-        pipe.run().synchronize()
-        if world > 1:
-            gathered = gather_summaries(pipe.out["summary"].to(device, non_blocking=True), world)
+        def step_e2e():
+            pipe.run().synchronize()
 
+        e2e_bytes = lambda: (pipe.h2d_bytes, pipe.d2h_bytes)
+        e2e_summary = lambda: pipe.result().summary
+        e2e_api = f"PipelinedScheduler(chunks=24, nstreams=3, results='{args.results}')"
+    else:
+        # one shared topology: a single schedule_batch call on a pinned host batch, every result array back
+        from dls_b200.batch import pin_batch
+        pinned = pin_batch(host)
+        state = {}
+
+        def step_e2e():
+            d = DeviceBatch(host, device, pinned=pinned)
+            r = schedule_batch(d, wl.mask, workspace=ws, peak=peak)
+            state["h2d"] = d.h2d_bytes
+            state["res"] = r.host() if args.results == "full" else r.summary_host()
+            state["d2h"] = r.d2h_bytes(full=args.results == "full")
+
+        e2e_bytes = lambda: (state["h2d"], state["d2h"])
+        e2e_summary = lambda: state["res"].summary if args.results == "full" else state["res"]
+        e2e_api = f"schedule_batch(pinned host DagBatch) + {'BatchResult.host()' if args.results == 'full' else 'summary_host()'}"
     step_e2e()
     barrier()
     t_wall0 = time.perf_counter()
@@ -279,14 +432,15 @@ def main():
     if world > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
     clk = clocks.stop() if clocks else None
-    h2d = pipe.h2d_bytes
-    d2h = pipe.d2h_bytes
-    e2e_summ = pipe.result().summary
+    h2d, d2h = e2e_bytes()
 
     # sanity: every instance scheduled, statuses clean (not part of any timed region)
     summ = res.summary_host()
-    assert (summ["status"] == 0).all() and (summ["completed"] + summ["failed"] + summ["pending"] == N_TASKS).all()
-    assert (e2e_summ == summ).all(), "pipelined end-to-end results differ from the resident run"
+    assert (summ["status"] == 0).all() and (summ["completed"] + summ["failed"] + summ["pending"] == n).all()
+    e2e_summ = e2e_summary()
+    for f in summ.dtype.names:
+        if f != "peak" or wl.name != "random1k":  # (the pipelined leg does not ask for peaks)
+            assert (e2e_summ[f] == summ[f]).all(), f"end-to-end results differ from the resident run in {f}"
     if world > 1:
         assert gathered is not None and gathered.shape[0] == world
 
@@ -303,23 +457,22 @@ def main():
     ksum = sum(v[0] for v in shares.values())
     dom = max(shares, key=lambda k: shares[k][0])
     dom_ms = shares[dom][0] / shares[dom][1]
-    alg = priority_bytes(host) if dom.startswith("priority") else algorithmic_bytes(host)
-    peak, peak_src = measured_peak()
-    achieved = alg / (dom_ms * 1e-3) / 1e9
+    alg_of = lambda k: priority_bytes(host) if k.startswith("priority") else algorithmic_bytes(host)
+    peak_bw, peak_src = measured_peak()
+    achieved = alg_of(dom) / (dom_ms * 1e-3) / 1e9
+    step_alg = 4 * algorithmic_bytes(host)
     roofline = {
-        "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": ncu_traffic(dom, B), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
-        "kernel_ms": dom_ms, "share_of_step": shares[dom][0] / ksum,
+        "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak_bw, "unit": "GB/s", "frac": achieved / peak_bw,
+        "traffic": ncu_traffic(dom, B) if wl.name == "random1k" else None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": alg_of(dom), "kernel_ms": dom_ms, "share_of_step": shares[dom][0] / ksum,
         # the step as a whole: four schedules per instance, every kernel of the step, against the same peak
-        "step": {"algorithmic_bytes": 4 * algorithmic_bytes(host),
-                 "achieved": 4 * algorithmic_bytes(host) / (ms_total / args.steps * 1e-3) / 1e9,
-                 "frac": 4 * algorithmic_bytes(host) / (ms_total / args.steps * 1e-3) / 1e9 / peak},
+        "step": {"algorithmic_bytes": step_alg, "achieved": step_alg / (ms_total / args.steps * 1e-3) / 1e9,
+                 "frac": step_alg / (ms_total / args.steps * 1e-3) / 1e9 / peak_bw},
         # per kernel: share of the step and, for kernels doing real work, algorithmic GB/s over the measured peak
         # (sched_* kernels of the general path only pick up routed instances here: a few tens of microseconds;
         # param_class and unpermute touch a fraction of a schedule's bytes: no figure)
         "kernels": {k: {"ms_per_launch": v[0] / v[1], "share": v[0] / ksum,
-                        "frac": (((priority_bytes(host) if k.startswith("priority") else algorithmic_bytes(host))
-                                  / (v[0] / v[1] * 1e-3) / 1e9) / peak)
+                        "frac": ((alg_of(k) / (v[0] / v[1] * 1e-3) / 1e9) / peak_bw)
                         if v[0] / ksum > 0.01 and k.startswith(("priority", "sched_", "stream_build")) else None}
                     for k, v in shares.items()},
     }
@@ -327,14 +480,15 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"random-1k (config-5 shape): {B} DAG instances per GPU per step, n={N_TASKS} tasks, "
-                               f"K={K_NODES} nodes, memory regime {REGIME}, algorithms DFS+Greedy+Critical+MRU_spec",
-                   "instances_per_gpu": B, "schedules_per_step": 4 * B * world,
-                   "l2": f"inputs {host.input_bytes() / 1e6:.0f} MB per GPU > 126 MB L2 (no flush needed)",
-                   "collective": "all_gather of 40-byte per-instance records each step" if world > 1 else "none (1 GPU)"},
+        "config": {"workload": wl.describe(), "instances_per_gpu": B, "schedules_per_step": 4 * B * world,
+                   "peak_memory_tracked": peak,
+                   "l2": f"inputs {host.input_bytes() / 1e6:.0f} MB per GPU > 126 MB L2 (no flush needed)"
+                         if host.input_bytes() > 126e6 else
+                         f"inputs {host.input_bytes() / 1e6:.0f} MB + {ws.numel() / 1e6:.0f} MB of scratch rewritten per step",
+                   "collective": "one all_gather of the 48-byte per-instance records after the last step" if world > 1 else "none (1 GPU)"},
         "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": float(e2e_ms.item()) / args.steps},
+                "ms_per_step": float(e2e_ms.item()) / args.steps, "api": e2e_api},
         "gpu_launches": launches,
         "clocks": clk,
     }
@@ -342,11 +496,14 @@ def main():
         from oracle import oracle
         oracle.build()
         threads = os.cpu_count() or 1
-        v, desc, _, _ = cpu_sample(oracle, host, threads, args.cpu_seconds)
-        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
+        rec, sample, want = cpu_baseline(oracle, wl, rank, threads, args.cpu_seconds, min(B, 8192))
+        line["cpu_baseline"] = rec
+        line["parity"] = parity_check(res, want, sample.B, n, K)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if line.get("parity", {}).get("mismatches", 0):
+        raise SystemExit("parity gate: the GPU results differ from the oracle's; the timings above do not count")
 
 
 if __name__ == "__main__":

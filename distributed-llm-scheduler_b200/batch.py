@@ -26,12 +26,12 @@ def algos_of(mask: int) -> List[int]:
 class ResultArrays:
     """Host (numpy) image of dls_result_t for `algos` (slot order)."""
     algos: List[int]
-    node_of: np.ndarray   # i8  [A, NT]
-    seq_pos: np.ndarray   # u16 [A, NT]
+    node_of: Optional[np.ndarray]   # i8  [A, NT]   (None in a summary-only result of PipelinedScheduler)
+    seq_pos: Optional[np.ndarray]   # u16 [A, NT]   (likewise)
     summary: np.ndarray   # structured [A, B]
     fin: np.ndarray       # f64 [A, NK]
     cnt: np.ndarray       # i32 [A, NK]
-    avail: np.ndarray     # f64 [A, NK]
+    avail: Optional[np.ndarray]     # f64 [A, NK]   (likewise)
     peak: Optional[np.ndarray]    # f64 [A, NK]
     cached: Optional[np.ndarray]  # u32 [A, NP]
     tfin: Optional[np.ndarray] = None  # f64 [A, NK] extension: node finish times on the dependency-aware timeline
@@ -331,11 +331,18 @@ class PipelinedScheduler:
     """
 
     def __init__(self, host: DagBatch, algo_mask: int = N.MASK_ALL, device=None, chunks: int = 8, nstreams: int = 3,
-                 compact: bool = True):
+                 compact: bool = True, results: str = "full"):
+        """`results`: "full" brings every result array back to the host; "summary" only what a sweep's result table
+        is made of — the per-instance records, node finish times and task counts (what evaluate_batch reads; 544 bytes
+        per 8-node instance and algorithm instead of 3.2 KB for a 1k-task DAG) — per-task outputs stay on the device
+        ("per-task outputs stay sharded unless requested")."""
         torch = _torch()
         lib = N.load()
         if host.T != host.B:
             raise ValueError("pipelining shards by instance: needs one topology per instance (T == B)")
+        if results not in ("full", "summary"):
+            raise ValueError("results must be 'full' or 'summary'")
+        self.results = results
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.mask, self.algos = algo_mask, algos_of(algo_mask)
         A = len(self.algos)
@@ -391,9 +398,11 @@ class PipelinedScheduler:
                 if a is not None:
                     size[f] = max(size.get(f, 0), int(a.size))
         pin = lambda shape, dt: torch.empty(shape, dtype=dt).pin_memory()
-        self.out = {"node_of": pin((A, host.nt_inst), torch.int8), "seq_pos": pin((A, host.nt_inst), torch.int16),
-                    "summary": pin((A, host.B, N.SUMMARY_BYTES), torch.uint8), "fin": pin((A, host.nk_inst), torch.float64),
-                    "cnt": pin((A, host.nk_inst), torch.int32), "avail": pin((A, host.nk_inst), torch.float64)}
+        self.out = {"summary": pin((A, host.B, N.SUMMARY_BYTES), torch.uint8), "fin": pin((A, host.nk_inst), torch.float64),
+                    "cnt": pin((A, host.nk_inst), torch.int32)}
+        if results == "full":
+            self.out.update({"node_of": pin((A, host.nt_inst), torch.int8), "seq_pos": pin((A, host.nt_inst), torch.int16),
+                             "avail": pin((A, host.nk_inst), torch.float64)})
         need = 0
         for _, _, part in parts:
             need = max(need, int(lib.dls_workspace_bytes(C.byref(part.as_struct(lambda f, a: None)), algo_mask)))
@@ -455,13 +464,14 @@ class PipelinedScheduler:
             for a in range(A):  # one contiguous async copy per array and algorithm slot (strided copies would be staged)
                 res = buf["_res"]
                 nt, nb, nk = part.nt_inst, part.B, part.nk_inst
-                back.append((self.out["node_of"][a, t0:t1], res["node_of"][a * nt:(a + 1) * nt]))
-                back.append((self.out["seq_pos"][a, t0:t1], res["seq_pos"][a * nt:(a + 1) * nt]))
+                if results == "full":
+                    back.append((self.out["node_of"][a, t0:t1], res["node_of"][a * nt:(a + 1) * nt]))
+                    back.append((self.out["seq_pos"][a, t0:t1], res["seq_pos"][a * nt:(a + 1) * nt]))
+                    back.append((self.out["avail"][a, k0:k1], res["avail"][a * nk:(a + 1) * nk]))
                 back.append((self.out["summary"][a, lo:hi].view(-1),
                              res["summary"][a * nb * N.SUMMARY_BYTES:(a + 1) * nb * N.SUMMARY_BYTES]))
                 back.append((self.out["fin"][a, k0:k1], res["fin"][a * nk:(a + 1) * nk]))
                 back.append((self.out["cnt"][a, k0:k1], res["cnt"][a * nk:(a + 1) * nk]))
-                back.append((self.out["avail"][a, k0:k1], res["avail"][a * nk:(a + 1) * nk]))
             self._plan.append((c % S, copies, expand, struct, back))
         self.h2d_bytes = h2d
         self.d2h_bytes = sum(t.numel() * t.element_size() for t in self.out.values())
@@ -496,7 +506,9 @@ class PipelinedScheduler:
     def result(self) -> ResultArrays:
         self.synchronize()
         o = self.out
+        full = self.results == "full"
         return ResultArrays(
-            algos=self.algos, node_of=o["node_of"].numpy(), seq_pos=o["seq_pos"].numpy().view(np.uint16),
+            algos=self.algos, node_of=o["node_of"].numpy() if full else None,
+            seq_pos=o["seq_pos"].numpy().view(np.uint16) if full else None,
             summary=o["summary"].numpy().view(np.dtype(N.SUMMARY_DTYPE)).reshape(len(self.algos), self.host.B),
-            fin=o["fin"].numpy(), cnt=o["cnt"].numpy(), avail=o["avail"].numpy(), peak=None, cached=None)
+            fin=o["fin"].numpy(), cnt=o["cnt"].numpy(), avail=o["avail"].numpy() if full else None, peak=None, cached=None)

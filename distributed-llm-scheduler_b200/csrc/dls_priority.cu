@@ -21,9 +21,17 @@ namespace dls {
 
 namespace {
 
+// 11 CTAs per SM is what the topology kernel's shared memory allows at 1k tasks; without the bound ptxas takes 56-64
+// registers (8-9 CTAs): 4.65 ms instead of 4.01 ms per 131k instances (round 2c)
+#ifndef DLS_TOPO_MINB
+#define DLS_TOPO_MINB 11
+#endif
+#ifndef DLS_CRIT_MINB
+#define DLS_CRIT_MINB 1
+#endif
 constexpr int kThreadsP = 128;   // measured r1d: 64 and 256 threads per CTA are both slower for the topology kernel
 
-__global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru, int stage,
+__global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_kernel(dls_batch_t b, Workspace w, int want_mru, int stage,
                                                                       int check_params) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ uint32_t s_part[33];
@@ -193,7 +201,14 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
   }
   const int maxd = s_maxd, maxdeg = s_maxdeg;
   // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
-  stable_counting_sort(s_ord, s_tmp, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, n + 2, s_part);
+  auto by_depth = [&](int i) { return (uint32_t)s_depth[i]; };
+#ifdef DLS_SORT_CHUNKED
+  const bool chunked_d = chunk_sort_fits(n, maxd + 1, n + 2);
+#else
+  const bool chunked_d = false;
+#endif
+  if (chunked_d) chunk_counting_sort(s_ord, s_tmp, n, maxd + 1, by_depth, s_hist, s_part);
+  else stable_counting_sort(s_ord, s_tmp, n, maxd + 1, by_depth, s_hist, n + 2, s_part);
   for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = s_tmp[q];
   __syncthreads();
   if (want_mru) {
@@ -202,8 +217,11 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
     strided_for<8>(n, [&](int i) { s_deg[i] = g_outdeg[i]; });
     __syncthreads();
     // (one pass on the combined key (depth, degree) needs ~200 x 4 counters and was measured slower than these two)
-    if (maxdeg + 2 <= n + 2) {
-      stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, [&](int i) { return (uint32_t)maxdeg - s_deg[i]; }, s_hist, n + 2, s_part);
+    auto by_degree = [&](int i) { return (uint32_t)maxdeg - s_deg[i]; };
+    if (chunked_d && chunk_sort_fits(n, maxdeg + 1, n + 2)) {
+      chunk_counting_sort(s_ord, s_tmp, n, maxdeg + 1, by_degree, s_hist, s_part);
+    } else if (maxdeg + 2 <= n + 2) {
+      stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, by_degree, s_hist, n + 2, s_part);
     } else {
       // duplicate dependency entries can push an out-degree beyond n: more keys than the histogram holds.
       // Rare, so place by counting: position = #(larger degree) + #(equal degree earlier in pi order).
@@ -218,7 +236,8 @@ __global__ void __launch_bounds__(kThreadsP) priority_topology_kernel(dls_batch_
       }
       __syncthreads();
     }
-    stable_counting_sort(s_tmp, s_ord, n, maxd + 1, [&](int i) { return (uint32_t)s_depth[i]; }, s_hist, n + 2, s_part);
+    if (chunked_d) chunk_counting_sort(s_tmp, s_ord, n, maxd + 1, by_depth, s_hist, s_part);
+    else stable_counting_sort(s_tmp, s_ord, n, maxd + 1, by_depth, s_hist, n + 2, s_part);
     for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_ord[q];
   }
 }
@@ -271,7 +290,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   if (tid == 0) w.nshared[t] = (int)nsh;
 }
 
-__global__ void __launch_bounds__(kThreadsP) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key) {
+__global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
   __shared__ uint32_t s_part[33];

@@ -260,8 +260,8 @@ struct ThreadOut {
 };
 
 // amin_base >= 0: the slab holds, per node, the smallest available memory seen right after a task's own memory was
-// taken (between ref schedulers.py:95 and :126) and the node's capacity. Rounding is monotone, so the largest
-// fl(cap - avail) over those moments — what the warp-per-DAG kernels and the oracle accumulate — is fl(cap - smallest).
+// taken (between ref schedulers.py:95 and :126). Rounding is monotone, so the largest fl(cap - avail) over those
+// moments — what the warp-per-DAG kernels and the oracle accumulate — is fl(cap - smallest).
 template <int KMAX>
 __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int slot,
                                               int inst, const Inst& v, const double (&avail)[KMAX], const Slab& sl,
@@ -279,7 +279,7 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
       r.avail[ko + k] = avail[k];
       if (c > 0 && (!any || f > mk)) { mk = f; any = true; }
       if (amin_base >= 0) {
-        const double p = fmax(0.0, __dsub_rn(sl.f(amin_base + KMAX + k), sl.f(amin_base + k)));
+        const double p = fmax(0.0, __dsub_rn(v.cap[k], sl.f(amin_base + k)));
         r.peak[ko + k] = p;
         pk = fmax(pk, p);
       }
@@ -308,9 +308,9 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
                                                        int twin_mode, int twin_slot, int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab layout per warp: doubles fin[KMAX], spd[KMAX] (+ amin[KMAX], cap[KMAX]); words smask[kSharedCap/4], cnt[KMAX],
+  // slab layout per warp: doubles fin[KMAX], spd[KMAX] (+ amin[KMAX]); words smask[kSharedCap/4], cnt[KMAX],
   // done-bits[bm_words]
-  constexpr int kD = (PEAK ? 4 : 2) * KMAX;
+  constexpr int kD = (PEAK ? 3 : 2) * KMAX;
   const int kW = kSharedCap / 4 + KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
@@ -371,10 +371,7 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
     sl.f(FIN + k) = 0.0;
     sl.f(SPD + k) = sp;
     sl.w(CNT + k) = 0;
-    if constexpr (PEAK) {
-      sl.f(AMIN + k) = INFINITY;
-      sl.f(AMIN + KMAX + k) = on ? v.cap[k] : 0.0;
-    }
+    if constexpr (PEAK) sl.f(AMIN + k) = INFINITY;
   }
   if constexpr (ALGO == DLS_ALGO_CRITICAL) {
 #pragma unroll
@@ -574,9 +571,9 @@ __global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls
                                                                  int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX] (+ amin[KMAX], cap[KMAX]); words cnt[KMAX], ncached[KMAX],
+  // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX] (+ amin[KMAX]); words cnt[KMAX], ncached[KMAX],
   // done-bits[bm_words]
-  constexpr int kD = (PEAK ? 5 : 3) * KMAX;
+  constexpr int kD = (PEAK ? 4 : 3) * KMAX;
   const int kW = 2 * KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
@@ -618,10 +615,7 @@ __global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls
     sl.f(HCNT + k) = 0.0;
     sl.w(CNT + k) = 0;
     sl.w(NC + k) = 0;  // len(node.cached_params)
-    if constexpr (PEAK) {
-      sl.f(AMIN + k) = INFINITY;
-      sl.f(AMIN + KMAX + k) = on ? v.cap[k] : 0.0;
-    }
+    if constexpr (PEAK) sl.f(AMIN + k) = INFINITY;
   }
   for (int x = 0; x < bm_words; ++x) sl.w(BM + x) = 0;
 
@@ -835,11 +829,11 @@ int bitmap_words(int n_max) {
 }
 template <int KMAX>
 size_t smem_simple(bool peak, int bm_words) {
-  return (size_t)(kTPB / 32) * ((size_t)(peak ? 4 : 2) * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX + bm_words) * 32 * 4);
+  return (size_t)(kTPB / 32) * ((size_t)(peak ? 3 : 2) * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX + bm_words) * 32 * 4);
 }
 template <int KMAX>
 size_t smem_mru(bool peak, int bm_words) {
-  return (size_t)(kTPBM / 32) * ((size_t)(peak ? 5 : 3) * KMAX * 32 * 8 + (size_t)(2 * KMAX + bm_words) * 32 * 4);
+  return (size_t)(kTPBM / 32) * ((size_t)(peak ? 4 : 3) * KMAX * 32 * 8 + (size_t)(2 * KMAX + bm_words) * 32 * 4);
 }
 
 }  // namespace

@@ -2,7 +2,7 @@
 
 The path is embarrassingly parallel over DAG instances: rank g of G takes the contiguous range
 [g*B/G, (g+1)*B/G), runs it with no data-path collective, and the ranks exchange only the fixed-size
-dls_summary_t records (40 bytes per instance and algorithm). Per-task outputs stay sharded.
+dls_summary_t records (48 bytes per instance and algorithm: makespan, peak memory, counters). Per-task outputs stay sharded.
 """
 from __future__ import annotations
 
@@ -20,7 +20,7 @@ def shard_bounds(B: int, world: int, rank: int) -> Tuple[int, int]:
 
 
 def gather_summaries(summary, world: int):
-    """all_gather of this rank's [A, B_local, 40]-byte record tensor -> [world, A, B_max, 40].
+    """all_gather of this rank's [A, B_local, 48]-byte record tensor -> [world, A, B_max, 48].
 
     Shards may differ by one instance; they are padded to the largest shard before the collective.
     Works on CUDA tensors under NCCL and on CPU tensors under gloo.
@@ -32,12 +32,10 @@ def gather_summaries(summary, world: int):
     A, b_local = summary.shape[0], summary.shape[1]
     sizes = torch.tensor([b_local], dtype=torch.int64, device=summary.device)
     all_sizes = [torch.zeros_like(sizes) for _ in range(world)]
-    if getattr(gather_summaries, "_equal", None) != (world, b_local):
-        dist.all_gather(all_sizes, sizes)
-        b_max = int(max(int(s.item()) for s in all_sizes))
-        gather_summaries._equal = (world, b_local) if all(int(s.item()) == b_local for s in all_sizes) else None
-    else:
-        b_max = b_local
+    # (8 bytes per rank, every call: a cached "shards are equal" would let ranks disagree on which collective comes next
+    # as soon as one call has even shards and the next has not)
+    dist.all_gather(all_sizes, sizes)
+    b_max = int(max(int(s.item()) for s in all_sizes))
     if b_max != b_local:
         pad = torch.zeros((A, b_max - b_local, summary.shape[2]), dtype=summary.dtype, device=summary.device)
         summary = torch.cat([summary, pad], 1)
@@ -51,7 +49,7 @@ def gather_summaries(summary, world: int):
 
 
 def merge_gathered(gathered, B: int, world: int) -> np.ndarray:
-    """[world, A, B_max, 40] bytes -> structured numpy [A, B] in global instance order."""
+    """[world, A, B_max, 48] bytes -> structured numpy [A, B] in global instance order."""
     g = gathered.cpu().numpy()
     A = g.shape[1]
     out = np.zeros((A, B), np.dtype(N.SUMMARY_DTYPE))

@@ -108,6 +108,95 @@ def random_dag_batch(B: int, n: int, K: int = 8, regime: float = 0.9, seed: int 
         node_off=off(np.full(B, K, np.int64)), cap=cap.reshape(-1), spd=spd.reshape(-1), dags=None)
 
 
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def _mix64(x: np.ndarray) -> np.ndarray:
+    """splitmix64 finaliser on uint64 arrays (wrap-around arithmetic), as csrc/dls_gen.cu::mix64."""
+    with np.errstate(over="ignore"):
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+
+
+def _u01(seed: int, inst: np.ndarray, task: np.ndarray, draw: int) -> np.ndarray:
+    """uniform double in [0, 1) for (instance, task, draw): csrc/dls_gen.cu::u01."""
+    with np.errstate(over="ignore"):
+        key = np.uint64(seed) ^ ((inst.astype(np.uint64) << np.uint64(32)) | task.astype(np.uint64))
+        h = _mix64(_mix64(key) + np.uint64(draw))
+    return (h >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def random_dag_batch_counter(B: int, n: int, K: int = 8, regime: float = 0.9, seed: int = 0, max_deps: int = 3,
+                             rank: Optional[np.ndarray] = None, first: int = 0) -> DagBatch:
+    """Instances first .. first+B-1 of the DEVICE generator's stream (dls_generate_counts / dls_generate_fill), built
+    on the host with numpy: the same counter-based hash of (seed, instance, task, draw), the same arithmetic, bit for
+    bit (tests/test_gpu_parity.py::test_device_generator_equals_its_host_port). What the CPU arm of bench.py schedules,
+    so that both arms time the same instances without the CPU arm touching the GPU."""
+    inst = (np.arange(B, dtype=np.uint64) + np.uint64(first))[:, None]
+    task = np.arange(n, dtype=np.uint64)[None, :]
+    inst_b, task_b = np.broadcast_arrays(inst, task)
+    idx = np.arange(n)
+    hi = np.minimum(max_deps, idx)
+    nd = np.minimum((_u01(seed, inst_b, task_b, 0) * (hi + 1)).astype(np.int64), hi)
+    npar = np.where(_u01(seed, inst_b, task_b, 1) < 0.5, 1, 2)
+    mem = 0.1 + (0.5 - 0.1) * _u01(seed, inst_b, task_b, 2)
+    dur = 0.05 + (0.15 - 0.05) * _u01(seed, inst_b, task_b, 3)
+    picks = []
+    for j in range(max_deps):
+        span = np.maximum(idx - j, 1)
+        r = np.minimum((_u01(seed, inst_b, task_b, 8 + j) * span).astype(np.int64), span - 1)
+        if picks:
+            prev = np.sort(np.stack(picks, 0), 0)
+            for q in range(prev.shape[0]):
+                r = r + (r >= prev[q])
+        picks.append(r)
+    picks = np.stack(picks, 2) if picks else np.zeros((B, n, 0), np.int64)
+    keep = np.arange(max_deps)[None, None, :] < nd[:, :, None]
+    pred_idx = picks[keep].astype(np.uint16)
+    pred_ptr = np.zeros((B, n + 1), np.uint32)
+    pred_ptr[:, 1:] = np.cumsum(nd, 1)
+    e_per = pred_ptr[:, -1].astype(np.int64)
+    present = np.zeros((B, n, 2), bool)
+    present[:, :, 0] = True
+    present[:, :, 1] = npar == 2
+    pos = _param_name_order(n)
+    by_name = np.zeros((B, 2 * n), bool)
+    by_name[:, pos] = present.reshape(B, 2 * n)
+    ids = (np.cumsum(by_name, 1) - by_name)[:, pos].reshape(B, n, 2)  # exclusive count = id in name order
+    lo = np.where(present[:, :, 1], np.minimum(ids[:, :, 0], ids[:, :, 1]), ids[:, :, 0])
+    pair = np.stack([lo, np.maximum(ids[:, :, 0], ids[:, :, 1])], 2)
+    par_idx = pair[present].astype(np.uint16)
+    par_ptr = np.zeros((B, n + 1), np.uint32)
+    par_ptr[:, 1:] = np.cumsum(npar, 1)
+    r_per = par_ptr[:, -1].astype(np.int64)
+    total = (mem + npar * 0.5).max(1) + r_per * 0.5
+    available = total * regime
+    if K == 2:
+        cap = np.stack([available * 0.6, available * 0.4], 1)
+        spd = np.tile(np.array([1.2, 1.0]), (B, 1))
+    elif K == 4:
+        cap = np.stack([available * f for f in (0.35, 0.25, 0.25, 0.15)], 1)
+        spd = np.tile(np.array([1.2, 1.0, 1.0, 0.8]), (B, 1))
+    else:
+        cap = np.repeat((available / K)[:, None], K, 1)
+        kk = np.arange(K, dtype=np.uint64)[None, :]
+        inst_k, _ = np.broadcast_arrays(inst, kk)
+        spd = np.stack([0.7 + (1.3 - 0.7) * _u01(seed, inst_k[:, k], np.full(B, 0xFFFFFFFF, np.uint64), k) for k in range(K)], 1)
+    if rank is None:
+        rank = task_rank(n)
+    off = lambda per: np.concatenate([[0], np.cumsum(per)]).astype(np.int64)
+    return DagBatch(
+        B=B, T=B, n_max=n, K_max=K, P_max=int(r_per.max()), E_max=int(e_per.max()), R_max=int(r_per.max()), flags=0,
+        task_off=off(np.full(B, n, np.int64)), pred_off=off(e_per), par_off=off(r_per), pid_off=off(r_per),
+        pred_ptr=np.ascontiguousarray(pred_ptr.reshape(-1)), pred_idx=pred_idx,
+        par_ptr=np.ascontiguousarray(par_ptr.reshape(-1)), par_idx=par_idx,
+        rank=np.tile(np.asarray(rank, np.uint16), B), mem=np.ascontiguousarray(mem.reshape(-1)),
+        dur=np.ascontiguousarray(dur.reshape(-1)), node_off=off(np.full(B, K, np.int64)),
+        cap=np.ascontiguousarray(cap.reshape(-1), np.float64), spd=np.ascontiguousarray(spd.reshape(-1), np.float64), dags=None)
+
+
 def random_shared_param_batch(B: int, n: int, K: int, pool: int, regime: float = 0.7, seed: int = 0,
                               max_deps: int = 4, max_params: int = 3) -> DagBatch:
     """Random DAGs whose tasks draw 0..max_params params from a pool of `pool` names, so params are SHARED between

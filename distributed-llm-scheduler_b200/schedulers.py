@@ -185,12 +185,26 @@ class MRUScheduler(BaseScheduler):
         self.time_step = 0
 
     def _lift(self, batch, res, dag, node_list):
+        step0 = self.time_step
         super()._lift(batch, res, dag, node_list)
         self.time_step += int(res.summary[0, 0]["rounds"])
-        for t in self._added:
-            if t.completed:
-                for p in t.params_needed:
-                    self.param_usage_count[p] += 1
+        # usage counts and last-used steps (ref schedulers.py:514-516): a task of depth d is assigned in round d + 1
+        pp, pi = dag.pred_ptr, dag.pred_idx
+        depth = np.zeros(len(self._added), np.int64)
+        changed = True  # (tasks may be listed in any order: relax until stable)
+        while changed:
+            changed = False
+            for i in range(len(self._added)):
+                if pp[i + 1] > pp[i]:
+                    d = int(depth[pi[pp[i]:pp[i + 1]]].max()) + 1
+                    if d != depth[i]:
+                        depth[i] = d
+                        changed = True
+        order, _ = sequence_of(batch, res, 0, 0)
+        for i in order.tolist():
+            for p in self._added[i].params_needed:
+                self.param_usage_count[p] += 1
+                self.param_last_used[p] = step0 + int(depth[i]) + 1
 
 
 SCHEDULERS = {"DFS": DFSScheduler, "Greedy": GreedyScheduler, "Critical": CriticalPathScheduler,

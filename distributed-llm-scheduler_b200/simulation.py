@@ -100,24 +100,34 @@ class DAGGenerator:
 
 def evaluate_batch(batch: DagBatch, res: ResultArrays, slot: int) -> Dict[str, np.ndarray]:
     """TestResult's derived metrics for every instance of a scheduled batch, from the device records
-    (ref simulation.py:271-302,339-347). Vectorised; fin[] already holds simulate_execution's per-node sums."""
+    (ref simulation.py:271-302,339-347), with no per-instance Python: segment reductions over the per-node arrays.
+    fin[] already holds simulate_execution's per-node sums; nodes with cnt == 0 are absent from the schedule dict."""
     B = batch.B
     summ = res.summary[slot]
     makespan = summ["makespan"].astype(np.float64)
-    util = np.zeros(B)
-    balance = np.zeros(B)
-    for b in range(B):
-        ks = batch.node_slice(b)
-        fin, cnt = res.fin[slot, ks], res.cnt[slot, ks]
-        loads = fin[cnt > 0]  # nodes present in the schedule dict
-        if loads.size == 0:
-            continue
-        if makespan[b] > 0:
-            util[b] = np.mean(loads / makespan[b])  # node_utilization[n] /= makespan ; np.mean (ref :274-276,344)
-        if loads.max() != 0:
-            avg, std = np.mean(loads), np.std(loads)
-            if avg > 0:
-                balance[b] = 1 / (1 + std / avg)  # ref :295-301
+    fin, cnt = res.fin[slot], res.cnt[slot]
+    if batch.node_off is None:
+        seg = np.repeat(np.arange(B), batch.K_max)
+        fin, cnt = fin[:B * batch.K_max], cnt[:B * batch.K_max]
+    else:
+        seg = np.repeat(np.arange(B), np.diff(batch.node_off))
+    used = cnt > 0
+    loads = np.where(used, fin, 0.0)
+    k_used = np.bincount(seg, weights=used, minlength=B)
+    total = np.bincount(seg, weights=loads, minlength=B)
+    have = k_used > 0
+    mean = np.divide(total, k_used, out=np.zeros(B), where=have)
+    # np.mean(loads / makespan) (ref :274-276,344)
+    ms_safe = np.where(makespan > 0, makespan, 1.0)
+    util = np.divide(np.bincount(seg, weights=loads / ms_safe[seg], minlength=B), k_used, out=np.zeros(B),
+                     where=have & (makespan > 0))
+    # 1 / (1 + np.std(loads) / np.mean(loads)), ddof 0, over the used nodes (ref :295-301)
+    dev2 = np.where(used, (fin - mean[seg]) ** 2, 0.0)
+    std = np.sqrt(np.divide(np.bincount(seg, weights=dev2, minlength=B), k_used, out=np.zeros(B), where=have))
+    lmax = np.full(B, -np.inf)
+    np.maximum.at(lmax, seg[used], fin[used])
+    ok = have & (lmax != 0) & (mean > 0)
+    balance = np.divide(1.0, 1.0 + np.divide(std, mean, out=np.zeros(B), where=ok), out=np.zeros(B), where=ok)
     n_tasks = np.diff(batch.task_off) if batch.T == batch.B else np.full(B, int(batch.task_off[1]))
     completed = summ["completed"].astype(np.int64)
     rate = np.where(n_tasks > 0, completed / np.maximum(n_tasks, 1) * 100, 0.0)
@@ -159,20 +169,45 @@ class ImprovedSchedulerEvaluator:
         return max_concurrent + len(all_params) * 0.5
 
     def simulate_execution(self, scheduler: BaseScheduler, schedule: Dict[str, List[str]]) -> Tuple[float, Dict]:
-        """ref simulation.py:216-278. The device already produced these numbers in the scheduling kernel's epilogue;
-        this returns them in the reference's shape for the schedule that `scheduler.schedule()` just returned."""
+        """ref simulation.py:216-278. For the schedule that `scheduler.schedule()` just returned the device already
+        produced these numbers in the scheduling kernel's epilogue; any other (scheduler, schedule) pair — the reference
+        accepts whatever dict it is handed — is replayed here the way the reference does it."""
         if not schedule:
             return 0.0, {"param_cache_hits": 0, "param_cache_misses": 0, "node_utilization": {}}
         rec = getattr(scheduler, "last_device_result", None)
-        if rec is None or rec["schedule"] != schedule:
-            raise NotImplementedError("simulate_execution is computed on the device for the schedule returned by "
-                                      "scheduler.schedule(); there is no host replay of foreign schedules")
-        makespan = float(rec["makespan"])
-        util = {}
-        for nid in schedule:
-            util[nid] = rec["fin"][nid] / makespan if makespan > 0 else rec["fin"][nid]
-        return makespan, {"param_cache_hits": int(rec["hits"]), "param_cache_misses": int(rec["misses"]),
-                          "node_utilization": util}
+        if rec is not None and rec["schedule"] == schedule:
+            makespan = float(rec["makespan"])
+            util = {}
+            for nid in schedule:
+                util[nid] = rec["fin"][nid] / makespan if makespan > 0 else rec["fin"][nid]
+            return makespan, {"param_cache_hits": int(rec["hits"]), "param_cache_misses": int(rec["misses"]),
+                              "node_utilization": util}
+        hits = misses = 0
+        finish, util = {}, {}
+        for node_id, task_ids in schedule.items():
+            if node_id not in scheduler.nodes:
+                continue
+            node = scheduler.nodes[node_id]
+            now, seen = 0, set()
+            for task_id in task_ids:
+                if task_id not in scheduler.tasks:
+                    continue
+                task = scheduler.tasks[task_id]
+                for param in task.params_needed:  # per-node seen-set replay, evictions ignored (ref :253-258)
+                    if param in seen:
+                        hits += 1
+                    else:
+                        misses += 1
+                        seen.add(param)
+                dur = task.compute_time / node.compute_speed
+                now += dur
+                util[node_id] = util.get(node_id, 0.0) + dur
+            finish[node_id] = now
+        makespan = max(finish.values()) if finish else 0
+        if makespan > 0:
+            for node_id in util:
+                util[node_id] /= makespan
+        return makespan, {"param_cache_hits": hits, "param_cache_misses": misses, "node_utilization": util}
 
     def calculate_load_balance(self, scheduler: BaseScheduler, schedule: Dict[str, List[str]]) -> float:
         """ref simulation.py:280-302 (a derived metric of the lifted schedule; Python's sum() is kept because its

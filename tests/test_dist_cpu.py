@@ -40,39 +40,45 @@ def test_shard_is_selfcontained(oracle_mod):
             np.testing.assert_array_equal(part.seq_pos, full.seq_pos[:, t0:t1])
 
 
-def _worker(rank, world, port, B, q):
+def _batch(B):
+    # the tie-break order pi is an INPUT (it depends on the hash seed of the process that built the task set):
+    # fix it explicitly so parent and spawned workers schedule the same instances
+    return random_dag_batch(B, 30, 4, 0.7, seed=9, rank=np.arange(30, dtype=np.uint16)[::-1].copy())
+
+
+def _worker(rank, world, port, sizes, q):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from oracle import oracle
-        batch = random_dag_batch(B, 30, 4, 0.7, seed=9, rank=np.arange(30, dtype=np.uint16)[::-1].copy())
-        lo, hi = shard_bounds(B, world, rank)
-        local = oracle.schedule_batch(batch.shard(lo, hi), N.MASK_ALL)
-        rec = torch.from_numpy(np.ascontiguousarray(local.summary).view(np.uint8).reshape(4, hi - lo, N.SUMMARY_BYTES))
-        merged = merge_gathered(gather_summaries(rec, world), B, world)
-        q.put((rank, merged.tobytes()))
+        out = []
+        for B in sizes:  # several gathers in ONE process group: even shards, then uneven ones, then even again
+            batch = _batch(B)
+            lo, hi = shard_bounds(B, world, rank)
+            local = oracle.schedule_batch(batch.shard(lo, hi), N.MASK_ALL)
+            rec = torch.from_numpy(np.ascontiguousarray(local.summary).view(np.uint8).reshape(4, hi - lo, N.SUMMARY_BYTES))
+            out.append(merge_gathered(gather_summaries(rec, world), B, world).tobytes())
+        q.put((rank, out))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("B", [8, 9])
-def test_two_rank_gather_matches_single_process(oracle_mod, B):
+@pytest.mark.parametrize("sizes", [(8,), (9,), (8, 9, 8, 11)])
+def test_two_rank_gather_matches_single_process(oracle_mod, sizes):
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, B, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, sizes, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = dict(q.get(timeout=120) for _ in range(2))
+    got = dict(q.get(timeout=180) for _ in range(2))
     for p in procs:
         p.join(60)
         assert p.exitcode == 0
-    # the tie-break order pi is an INPUT (it depends on the hash seed of the process that built the task set):
-    # fix it explicitly so parent and spawned workers schedule the same instances
-    want = oracle_mod.schedule_batch(random_dag_batch(B, 30, 4, 0.7, seed=9, rank=np.arange(30, dtype=np.uint16)[::-1].copy()),
-                                     N.MASK_ALL).summary
-    for r in range(2):
-        np.testing.assert_array_equal(np.frombuffer(got[r], dtype=want.dtype).reshape(want.shape), want)
+    for k, B in enumerate(sizes):
+        want = oracle_mod.schedule_batch(_batch(B), N.MASK_ALL).summary
+        for r in range(2):
+            np.testing.assert_array_equal(np.frombuffer(got[r][k], dtype=want.dtype).reshape(want.shape), want)

@@ -63,6 +63,26 @@ class _OrderedPending(list):
             self.remove(x)
 
 
+@pytest.mark.parametrize("fname,label", [("cfg1_example_and_edges.npz", "example4"), ("cfg3_gpt2.npz", "gpt2|4laptops")])
+def test_mru_bookkeeping_after_schedule(fname, label):
+    """MRUScheduler's own state after schedule() — time_step, param_usage_count, param_last_used
+    (ref schedulers.py:453,514-516) — equals what the reference leaves (tests/golden/mru_state.json, frozen from the
+    unmodified reference by tests/golden/make_mru_state.py with the same tie-break order)."""
+    import json
+    import os
+    want = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "mru_state.json")))[label]
+    case = [c for c in golden_io.load(fname) if c.label == label][0]
+    tasks, nodes, pi = _objects(case)
+    s = MRUScheduler(nodes)
+    for t in tasks:
+        s.add_task(t)
+    s.pending_tasks = _OrderedPending(pi)
+    s.schedule()
+    assert len(s.completed_tasks) == want["completed"] and s.time_step == want["time_step"]
+    assert dict(s.param_usage_count) == want["param_usage_count"]
+    assert dict(s.param_last_used) == want["param_last_used"]
+
+
 def test_live_set_order_is_used():
     """Without any override the tie-break is this process's set order, exactly as in the reference."""
     from dls_b200.lowering import set_order

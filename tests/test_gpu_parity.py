@@ -208,6 +208,26 @@ def test_device_generator_parity_and_shape(oracle_mod):
             assert_results_equal(res, want, f"{path} device-generated n={n} K={K}")
 
 
+def test_device_generator_equals_its_host_port():
+    """gen.random_dag_batch_counter restates the generator kernels in numpy (same counter hash, same arithmetic): the
+    CPU arm of bench.py schedules the instances the GPU arm schedules without touching the GPU. Every array, bit for bit,
+    for K = 2, 4 (fixed node sets) and 8 (drawn speeds), and for a window of instances out of the middle."""
+    from dls_b200.gen import random_dag_batch_counter, random_dag_batch_device
+    for n, K, regime, seed in ((300, 8, 0.9, 5), (64, 4, 0.7, 1000), (1000, 2, 0.8, 7), (1000, 8, 0.9, 1000)):
+        rank = np.random.default_rng(n).permutation(n).astype(np.uint16)
+        dev = random_dag_batch_device(40, n, K, regime, seed=seed, rank=rank).to_host()
+        host = random_dag_batch_counter(40, n, K, regime, seed=seed, rank=rank)
+        for f in ("task_off", "pred_off", "par_off", "pid_off", "node_off", "pred_ptr", "pred_idx", "par_ptr", "par_idx", "rank"):
+            np.testing.assert_array_equal(getattr(dev, f), getattr(host, f), err_msg=f)
+        for f in ("mem", "dur", "cap", "spd"):
+            np.testing.assert_array_equal(getattr(dev, f).view(np.uint64), getattr(host, f).view(np.uint64), err_msg=f)
+        assert (dev.E_max, dev.R_max, dev.P_max) == (host.E_max, host.R_max, host.P_max)
+        window = random_dag_batch_counter(7, n, K, regime, seed=seed, rank=rank, first=21)
+        np.testing.assert_array_equal(window.mem, host.mem[21 * n: 28 * n])
+        np.testing.assert_array_equal(window.pred_idx, host.pred_idx[host.pred_off[21]: host.pred_off[28]])
+        np.testing.assert_array_equal(window.cap, host.cap[21 * K: 28 * K])
+
+
 def test_pipelined_host_path_matches_single_call(oracle_mod):
     """The chunked, multi-stream end-to-end path (host in, host out) returns exactly what one call returns."""
     from dls_b200.batch import PipelinedScheduler
@@ -221,6 +241,15 @@ def test_pipelined_host_path_matches_single_call(oracle_mod):
     for p in (pipe, full):
         for _ in range(2):  # buffers are reused across runs
             assert_results_equal(p.run().result(), want, "pipelined")
+    # summary mode: only the per-instance records, node finish times and task counts come back
+    brief = PipelinedScheduler(batch, N.MASK_ALL, chunks=7, nstreams=3, results="summary")
+    got = brief.run().result()
+    assert got.node_of is None and got.seq_pos is None and brief.d2h_bytes < 0.3 * pipe.d2h_bytes
+    for f in want.summary.dtype.names:
+        if f != "peak":
+            np.testing.assert_array_equal(got.summary[f], want.summary[f], err_msg=f)
+    np.testing.assert_array_equal(got.fin, want.fin)
+    np.testing.assert_array_equal(got.cnt, want.cnt)
 
 
 def test_pipelined_compact_transfer_ragged_and_fallback(oracle_mod):

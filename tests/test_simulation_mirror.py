@@ -70,14 +70,7 @@ def test_generators_match_live_reference():
                    [(t.id, t.memory_required, t.compute_time, t.dependencies, t.params_needed) for t in b]
 
 
-@pytest.mark.gpu
-def test_evaluate_batch_reproduces_reference_testresults():
-    """All 648 TestResults of the default sweep: counts and cache statistics exact, makespan bit-equal,
-    utilisation / load balance / completion rate within 1e-6 relative (north-star tolerance)."""
-    from dls_b200.batch import schedule_batch
-    cases = golden_io.load("cfg2_sweep_seed0.npz")
-    batch = golden_io.batch_of(cases)
-    res = schedule_batch(batch, N.MASK_ALL).host()
+def _check_metrics(batch, res, cases):
     for a in range(4):
         m = evaluate_batch(batch, res, res.slot(a))
         for b, c in enumerate(cases):
@@ -88,6 +81,59 @@ def test_evaluate_batch_reproduces_reference_testresults():
             assert m["makespan"][b] == e["makespan"]
             for f in ("avg_node_utilization", "load_balance_score", "completion_rate"):
                 np.testing.assert_allclose(m[f][b], e[f], rtol=1e-6, atol=1e-12, err_msg=f"{c.label} algo {a} {f}")
+
+
+def test_evaluate_batch_on_oracle_records(oracle_mod):
+    """The result-format emitter alone (host logic, no GPU): the oracle's records of the default sweep, pushed through
+    evaluate_batch's segment reductions, give the reference's 648 TestResults; and a ragged batch with unused nodes,
+    empty schedules and zero makespans goes through the same code as a plain per-instance loop would."""
+    cases = golden_io.load("cfg2_sweep_seed0.npz")
+    batch = golden_io.batch_of(cases)
+    res = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=4)
+    _check_metrics(batch, res, cases)
+    # against the definition, instance by instance (ref simulation.py:271-302,339-347)
+    for slot in range(4):
+        m = evaluate_batch(batch, res, slot)
+        for b in range(0, batch.B, 7):
+            ks = batch.node_slice(b)
+            loads = res.fin[slot, ks][res.cnt[slot, ks] > 0]
+            mk = res.summary[slot, b]["makespan"]
+            util = np.mean(loads / mk) if loads.size and mk > 0 else 0.0
+            bal = 1 / (1 + np.std(loads) / np.mean(loads)) if loads.size and loads.max() != 0 and np.mean(loads) > 0 else 0.0
+            np.testing.assert_allclose([m["avg_node_utilization"][b], m["load_balance_score"][b]], [util, bal], rtol=1e-12)
+
+
+@pytest.mark.skipif(not rh.available(), reason="needs the reference checkout (build container only)")
+def test_simulate_execution_replays_any_schedule_like_the_reference():
+    """simulate_execution accepts ANY (scheduler, schedule) pair in the reference (simulation.py:216-278): hand both
+    implementations the same foreign schedule — shuffled, with an unknown node and an unknown task in it."""
+    sch, sim = rh.ref_modules()
+    random.seed(3)
+    tasks = sim.DAGGenerator.generate_pipeline_dag(4, 3)
+    nodes = [sch.Node("a", 8.0, 1.2), sch.Node("b", 6.0, 0.8), sch.Node("c", 6.0, 1.0)]
+    s = sch.GreedyScheduler(nodes)
+    for t in tasks:
+        s.add_task(t)
+    ids = [t.id for t in tasks]
+    random.shuffle(ids)
+    schedule = {"b": ids[:5] + ["ghost_task"], "nowhere": ids[5:7], "a": ids[7:], "c": []}
+    want = sim.ImprovedSchedulerEvaluator({}).simulate_execution(s, schedule)
+    got = ImprovedSchedulerEvaluator({}).simulate_execution(s, schedule)
+    assert got[0] == want[0]
+    assert (got[1]["param_cache_hits"], got[1]["param_cache_misses"]) == (want[1]["param_cache_hits"], want[1]["param_cache_misses"])
+    assert dict(got[1]["node_utilization"]) == dict(want[1]["node_utilization"])
+    assert ImprovedSchedulerEvaluator({}).simulate_execution(s, {}) == sim.ImprovedSchedulerEvaluator({}).simulate_execution(s, {})
+
+
+@pytest.mark.gpu
+def test_evaluate_batch_reproduces_reference_testresults():
+    """All 648 TestResults of the default sweep: counts and cache statistics exact, makespan bit-equal,
+    utilisation / load balance / completion rate within 1e-6 relative (north-star tolerance)."""
+    from dls_b200.batch import schedule_batch
+    cases = golden_io.load("cfg2_sweep_seed0.npz")
+    batch = golden_io.batch_of(cases)
+    res = schedule_batch(batch, N.MASK_ALL).host()
+    _check_metrics(batch, res, cases)
 
 
 @pytest.mark.gpu

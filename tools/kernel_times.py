@@ -19,8 +19,12 @@ if os.environ.get("DLS_L2_FETCH"):   # cudaLimitMaxL2FetchGranularity (0x05): 32
     cu.cuCtxGetLimit(C.byref(new), 5)
     print("L2 fetch granularity", old.value, "->", new.value, "rc", rc)
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 131072
-dev = random_dag_batch_device(B, 1000, 8, 0.9, seed=1000)
-res = schedule_batch(dev, 0xF)
+PEAK = bool(int(os.environ.get("DLS_PEAK", "0")))
+rank = None
+if os.environ.get("DLS_RANK_PERM"):
+    rank = np.random.default_rng(12345).permutation(1000).astype(np.uint16)
+dev = random_dag_batch_device(B, 1000, 8, 0.9, seed=1000, rank=rank)
+res = schedule_batch(dev, 0xF, peak=PEAK)
 torch.cuda.synchronize()
 lib.dls_profile_enable(1)
 ms = (C.c_double * N.NUM_KERNELS)(); cnt = (C.c_int64 * N.NUM_KERNELS)()

@@ -21,9 +21,9 @@ def main():
     for r in rows:
         if not r:
             continue
-        if r[0] == "File Name":
+        if r[0] in ("File Name", "File Path"):
             fname = r[1].split("/")[-1]
-        elif r[0] == "Kernel Name":
+        elif r[0] in ("Kernel Name", "Function Name"):
             print("kernel:", r[1])
         elif r[0] == "Line No":
             hdr = r
