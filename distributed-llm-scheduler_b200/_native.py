@@ -82,13 +82,13 @@ class DlsPrio(C.Structure):
 # Every symbol include/dls.h declares; tests check the built library exports all of them.
 EXPORTED_SYMBOLS = (
     "dls_version", "dls_last_error", "dls_workspace_bytes", "dls_schedule_batch", "dls_priorities",
-    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path", "dls_generate_counts", "dls_generate_fill", "dls_aggregate", "dls_rows_from_degrees", "dls_repeat_rank_row",
+    "dls_launch_count", "dls_profile_enable", "dls_profile_read", "dls_kernel_name", "dls_schedule_batch_static", "dls_set_stream_path", "dls_set_replay_path", "dls_generate_counts", "dls_generate_fill", "dls_aggregate", "dls_rows_from_degrees", "dls_repeat_rank_row",
 )
 STATIC_SCRATCH_BYTES = 32 << 20
 AGG_FIELDS = 8
 AGG_NAMES = ("count", "completion_rate", "makespan", "avg_node_utilization", "load_balance_score",
              "param_cache_hits", "param_cache_misses", "with_completed")
-NUM_KERNELS = 13
+NUM_KERNELS = 14
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -165,6 +165,8 @@ def load() -> C.CDLL:
                                       C.c_void_p, C.c_void_p]
         lib.dls_set_stream_path.restype = C.c_int
         lib.dls_set_stream_path.argtypes = [C.c_int]
+        lib.dls_set_replay_path.restype = C.c_int
+        lib.dls_set_replay_path.argtypes = [C.c_int]
         lib.dls_priorities.restype = C.c_int
         lib.dls_priorities.argtypes = [C.POINTER(DlsBatch), C.POINTER(DlsPrio), C.c_void_p, C.c_size_t, C.c_void_p]
         lib.dls_launch_count.restype = C.c_int64

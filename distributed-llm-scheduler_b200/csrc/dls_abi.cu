@@ -21,7 +21,7 @@ const char* const kKernelNames[DLS_NUM_KERNELS] = {"priority_topology_kernel", "
                                                    "param_class_kernel", "stream_build_kernel",
                                                    "sched_stream_kernel<DFS>", "sched_stream_kernel<Greedy>",
                                                    "sched_stream_kernel<Critical>", "sched_stream_mru_kernel",
-                                                   "unpermute_kernel"};
+                                                   "unpermute_kernel", "replay_kernel"};
 
 int fail(int code, const std::string& msg) {
   g_err = msg;
@@ -145,7 +145,8 @@ int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
   return DLS_OK;
 }
 
-bool g_stream_enabled = true;
+std::atomic<bool> g_stream_enabled{true};
+std::atomic<bool> g_replay_enabled{true};
 
 int cuda_fail(cudaError_t e, const char* why) {
   return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
@@ -179,10 +180,10 @@ int static_scratch_address(void** out) {
   return DLS_OK;
 }
 
-// Enqueue everything for one batch. `ws_bytes` is what the caller provided; the streamed (thread-per-DAG) path is
-// used when the batch qualifies and its larger scratch fits, otherwise the warp-per-DAG kernels do all the work.
-int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace, size_t ws_bytes,
-                 void* cuda_stream, bool clear_status) {
+// Enqueue everything for one batch on `ctx`. `ws_bytes` is what the caller provided; the streamed (thread-per-DAG) path
+// is used when the batch qualifies and its larger scratch fits, otherwise the warp-per-DAG kernels do all the work.
+int enqueue_schedule(const dls_batch_t* batch, const dls_result_t* result, int algo_mask, void* workspace, size_t ws_bytes,
+                     dls::LaunchCtx& ctx, bool clear_status) {
   const int lim = smem_limit();
   if (result->tfin) {  // the timeline extension keeps one finish time per task next to the rest of the per-DAG state
     size_t need = 0;
@@ -191,7 +192,7 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
     need = ((need + 15) & ~(size_t)15) + (((size_t)batch->n_max * sizeof(double) + 15) & ~(size_t)15);
     if (need > (size_t)lim) return fail(DLS_ERR_TOO_LARGE, "per-DAG state plus the timeline's finish times exceed shared memory");
   }
-  bool stream = g_stream_enabled && dls::stream_path_possible(*batch, result, lim);
+  bool stream = g_stream_enabled.load() && dls::stream_path_possible(*batch, result, lim);
   Layout L = layout_of(*batch, algo_mask, stream);
   if (stream && ws_bytes < L.total) {
     stream = false;
@@ -204,9 +205,6 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
   }
   if (reinterpret_cast<uintptr_t>(workspace) % kAlign) return fail(DLS_ERR_WORKSPACE, "workspace must be 256-byte aligned");
   const dls::Workspace w = carve(workspace, L);
-  dls::LaunchCtx ctx;
-  ctx.st = static_cast<cudaStream_t>(cuda_stream);
-  ctx.prof = g_prof.on ? &g_prof : nullptr;
   cudaError_t e = cudaSuccess;
   if (clear_status) {
     e = cudaMemsetAsync(w.topo_status, 0, (size_t)batch->T * sizeof(int32_t), ctx.st);
@@ -216,10 +214,122 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
   if (e == cudaSuccess && stream) e = dls::launch_stream_build(*batch, w, algo_mask, ctx);
   if (e == cudaSuccess && stream) e = dls::launch_stream_sched(*batch, *result, w, algo_mask, ctx);
   if (e == cudaSuccess) e = dls::launch_schedule(*batch, *result, w, algo_mask, ctx);
-  g_launches += ctx.launches;
   if (e != cudaSuccess) return cuda_fail(e, ctx.why);
-  g_err.clear();
   return DLS_OK;
+}
+
+// ---- one schedule for all instances (see dls_replay.cu) ------------------------------------------------------------
+constexpr int kDurationFree = (1 << DLS_ALGO_DFS) | (1 << DLS_ALGO_GREEDY) | (1 << DLS_ALGO_MRU);
+
+bool replay_applies(const dls_batch_t& b, const dls_result_t* r, int algo_mask) {
+  return g_replay_enabled.load() && b.T == 1 && b.B > 1 && b.flags == DLS_F_DUR_PER_INSTANCE && !b.node_off &&
+         (algo_mask & kDurationFree) && !(r && r->tfin);  // (the timeline extension is made of durations)
+}
+
+dls_batch_t template_batch(const dls_batch_t& b) {
+  dls_batch_t t = b;
+  t.B = 1;
+  t.nt_inst = b.nt_topo;
+  t.nk_inst = b.K_max;
+  t.np_inst = b.np_inst / b.B;
+  return t;
+}
+
+// Scratch of the template run behind the caller-visible layout: its own workspace, its result arrays, the sequence.
+struct TemplateLayout {
+  size_t off_ws, ws_bytes, off_node_of, off_seq_pos, off_summary, off_fin, off_cnt, off_avail, off_peak, off_cached,
+      off_seq_task, off_seq_node, total;
+};
+
+TemplateLayout template_layout(const dls_batch_t& b, int tmask, size_t base) {
+  const dls_batch_t t = template_batch(b);
+  const size_t A = (size_t)count_bits(tmask), n = (size_t)t.nt_inst, K = (size_t)t.K_max, P = (size_t)t.np_inst;
+  TemplateLayout T;
+  size_t o = align_up(base);
+  T.off_ws = o;
+  T.ws_bytes = layout_of(t, tmask, dls::stream_path_possible(t, nullptr, 227 * 1024)).total;
+  o = align_up(o + T.ws_bytes);
+  T.off_node_of = o;  o = align_up(o + A * n);
+  T.off_seq_pos = o;  o = align_up(o + A * n * sizeof(uint16_t));
+  T.off_summary = o;  o = align_up(o + A * sizeof(dls_summary_t));
+  T.off_fin = o;      o = align_up(o + A * K * sizeof(double));
+  T.off_cnt = o;      o = align_up(o + A * K * sizeof(int32_t));
+  T.off_avail = o;    o = align_up(o + A * K * sizeof(double));
+  T.off_peak = o;     o = align_up(o + A * K * sizeof(double));
+  T.off_cached = o;   o = align_up(o + A * P * sizeof(uint32_t));
+  T.off_seq_task = o; o = align_up(o + A * n * sizeof(uint16_t));
+  T.off_seq_node = o; o = align_up(o + A * n);
+  T.total = o;
+  return T;
+}
+
+int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace, size_t ws_bytes,
+                 void* cuda_stream, bool clear_status, bool allow_replay) {
+  dls::LaunchCtx ctx;
+  ctx.st = static_cast<cudaStream_t>(cuda_stream);
+  ctx.prof = g_prof.on ? &g_prof : nullptr;
+  int rc;
+  if (allow_replay && replay_applies(*batch, result, algo_mask)) {
+    const int tmask = algo_mask & kDurationFree, cmask = algo_mask & ~kDurationFree;
+    const size_t main_bytes = cmask ? layout_of(*batch, cmask, dls::stream_path_possible(*batch, result, 227 * 1024)).total : 0;
+    const TemplateLayout T = template_layout(*batch, tmask, main_bytes);
+    if (workspace && ws_bytes >= T.total && reinterpret_cast<uintptr_t>(workspace) % kAlign == 0) {
+      char* p = static_cast<char*>(workspace);
+      const dls_batch_t tb = template_batch(*batch);
+      dls_result_t tr;
+      tr.node_of = reinterpret_cast<int8_t*>(p + T.off_node_of);
+      tr.seq_pos = reinterpret_cast<uint16_t*>(p + T.off_seq_pos);
+      tr.summary = reinterpret_cast<dls_summary_t*>(p + T.off_summary);
+      tr.fin = reinterpret_cast<double*>(p + T.off_fin);
+      tr.cnt = reinterpret_cast<int32_t*>(p + T.off_cnt);
+      tr.avail = reinterpret_cast<double*>(p + T.off_avail);
+      tr.peak = result->peak ? reinterpret_cast<double*>(p + T.off_peak) : nullptr;
+      tr.cached = result->cached ? reinterpret_cast<uint32_t*>(p + T.off_cached) : nullptr;
+      tr.tfin = nullptr;
+      rc = enqueue_schedule(&tb, &tr, tmask, p + T.off_ws, T.ws_bytes, ctx, true);
+      if (rc == DLS_OK && cmask) {
+        // Critical for every instance, written to its own slot of the caller's arrays
+        int cslot = 0;
+        for (int a = 0; a < DLS_ALGO_CRITICAL; ++a) cslot += (algo_mask >> a) & 1;
+        dls_result_t cr = *result;
+        cr.node_of += (int64_t)cslot * batch->nt_inst;
+        cr.seq_pos += (int64_t)cslot * batch->nt_inst;
+        cr.summary += (int64_t)cslot * batch->B;
+        cr.fin += (int64_t)cslot * batch->nk_inst;
+        cr.cnt += (int64_t)cslot * batch->nk_inst;
+        cr.avail += (int64_t)cslot * batch->nk_inst;
+        if (cr.peak) cr.peak += (int64_t)cslot * batch->nk_inst;
+        if (cr.cached) cr.cached += (int64_t)cslot * batch->np_inst;
+        rc = enqueue_schedule(batch, &cr, cmask, workspace, main_bytes, ctx, true);
+      }
+      if (rc == DLS_OK) {
+        dls::ReplayArgs a;
+        a.nslots = count_bits(tmask);
+        a.n = (int)tb.nt_inst;
+        int ts = 0, fs = 0;
+        for (int al = 0; al < DLS_NUM_ALGOS; ++al) {
+          if (!((algo_mask >> al) & 1)) continue;
+          if ((tmask >> al) & 1) a.full_slot[ts++] = fs;
+          ++fs;
+        }
+        for (; ts < 4; ++ts) a.full_slot[ts] = 0;
+        a.t_node_of = tr.node_of; a.t_seq_pos = tr.seq_pos; a.t_summary = tr.summary; a.t_cnt = tr.cnt;
+        a.t_avail = tr.avail; a.t_peak = tr.peak; a.t_cached = tr.cached;
+        a.seq_task = reinterpret_cast<uint16_t*>(p + T.off_seq_task);
+        a.seq_node = reinterpret_cast<int8_t*>(p + T.off_seq_node);
+        cudaError_t e = dls::launch_replay(*batch, *result, a, ctx);
+        if (e != cudaSuccess) rc = cuda_fail(e, ctx.why);
+      }
+      g_launches += ctx.launches;
+      if (rc == DLS_OK) g_err.clear();
+      return rc;
+    }
+    // (scratch too small for the template's extra arrays: every instance is scheduled the ordinary way)
+  }
+  rc = enqueue_schedule(batch, result, algo_mask, workspace, ws_bytes, ctx, clear_status);
+  g_launches += ctx.launches;
+  if (rc == DLS_OK) g_err.clear();
+  return rc;
 }
 
 }  // namespace
@@ -236,7 +346,10 @@ size_t dls_workspace_bytes(const dls_batch_t* batch, int algo_mask) {
   if (!batch) return 0;
   // Size for the larger of the two paths; which one runs is decided per call (see run_schedule).
   const bool stream = dls::stream_path_possible(*batch, nullptr, 227 * 1024);
-  return layout_of(*batch, algo_mask, stream).total;
+  const size_t plain = layout_of(*batch, algo_mask, stream).total;
+  if (!replay_applies(*batch, nullptr, algo_mask)) return plain;
+  // room for the one-instance template run behind the ordinary layout (whichever path a call then takes)
+  return std::max(plain, template_layout(*batch, algo_mask & kDurationFree, plain).total);
 }
 
 int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace,
@@ -245,7 +358,7 @@ int dls_schedule_batch(const dls_batch_t* batch, dls_result_t* result, int algo_
   if (rc != DLS_OK) return rc;
   if (!result || !result->node_of || !result->seq_pos || !result->summary || !result->fin || !result->cnt || !result->avail)
     return fail(DLS_ERR_BAD_ARG, "NULL required output in result");
-  return run_schedule(batch, result, algo_mask, workspace, workspace_bytes, cuda_stream, false);
+  return run_schedule(batch, result, algo_mask, workspace, workspace_bytes, cuda_stream, false, true);
 }
 
 // See include/dls.h. Same work as dls_schedule_batch; the only difference is where the scratch lives.
@@ -267,7 +380,7 @@ int dls_schedule_batch_static(const dls_batch_t* batch, dls_result_t* result, in
   if (rc != DLS_OK) return rc;
   // The array still holds whatever the previous call left. The per-topology status words are the one region the
   // scheduling kernels trust before looking at anything else, so run_schedule clears them on the stream first.
-  return run_schedule(batch, result, algo_mask, base, (size_t)DLS_STATIC_SCRATCH_BYTES, cuda_stream, true);
+  return run_schedule(batch, result, algo_mask, base, (size_t)DLS_STATIC_SCRATCH_BYTES, cuda_stream, true, false);
 }
 
 static int check_gen(const dls_gen_t* g) {
@@ -345,11 +458,9 @@ int dls_repeat_rank_row(const uint16_t* row, int32_t n, int32_t T, uint16_t* out
 
 /* Test/measurement switch (no reference counterpart): 0 forces the general warp-per-DAG kernels for every
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
-int dls_set_stream_path(int enabled) {
-  const int old = g_stream_enabled ? 1 : 0;
-  g_stream_enabled = enabled != 0;
-  return old;
-}
+int dls_set_stream_path(int enabled) { return g_stream_enabled.exchange(enabled != 0) ? 1 : 0; }
+
+int dls_set_replay_path(int enabled) { return g_replay_enabled.exchange(enabled != 0) ? 1 : 0; }
 
 int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, size_t workspace_bytes, void* cuda_stream) {
   int rc = validate(batch, DLS_MASK_ALL, true);

@@ -253,7 +253,24 @@ struct LaunchCtx {
   Profiler* prof = nullptr;
 };
 
+// What replay_kernel (dls_replay.cu) reads: the results of the one-instance "template" run, per template slot.
+struct ReplayArgs {
+  int nslots;            // template slots (DFS / Greedy / MRU among the algorithms asked for)
+  int n;                 // tasks of the shared topology
+  int full_slot[4];      // template slot -> slot in the caller's result arrays
+  const int8_t* t_node_of;     // [nslots][n]
+  const uint16_t* t_seq_pos;   // [nslots][n]
+  const dls_summary_t* t_summary;  // [nslots]
+  const int32_t* t_cnt;        // [nslots][K]
+  const double* t_avail;       // [nslots][K]
+  const double* t_peak;        // [nslots][K] (with the peak output)
+  const uint32_t* t_cached;    // [nslots][P] (with the cached output)
+  uint16_t* seq_task;          // [nslots][n] scratch: task assigned q-th
+  int8_t* seq_node;            // [nslots][n] scratch: its node
+};
+
 // Host-side launchers (one translation unit each).
+cudaError_t launch_replay(const dls_batch_t& b, const dls_result_t& r, const ReplayArgs& a, LaunchCtx& ctx);
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);
 cudaError_t launch_schedule(const dls_batch_t& b, const dls_result_t& r, const Workspace& w, int algo_mask,
                             LaunchCtx& ctx);

@@ -475,16 +475,20 @@ size_t priority_smem_inst(int n_max, bool with_key) {
   return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (n + 2) * sizeof(uint32_t) + (with_key ? 3 : 2) * n_al * sizeof(uint16_t);
 }
 
+// Small DAGs (GPT-2: 99 tasks) leave most of a 128-thread CTA idle at every barrier: one or two warps then.
+static int threads_for(int n_max) { return n_max <= 128 ? 32 : n_max <= 384 ? 64 : kThreadsP; }
+
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx) {
   cudaError_t e;
   int rec;
+  const int threads = threads_for(b.n_max);
   if (w.par_sid) {
     size_t smp = priority_smem_param(b.n_max, b.P_max);
     ctx.why = "cudaFuncSetAttribute(param_class_kernel)";
     e = cudaFuncSetAttribute(param_class_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp);
     if (e != cudaSuccess) return e;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PARAM_CLASS, ctx.st) : -1;
-    param_class_kernel<<<b.T, kThreadsP, smp, ctx.st>>>(b, w);
+    param_class_kernel<<<b.T, threads_for(b.P_max), smp, ctx.st>>>(b, w);
     if (ctx.prof) ctx.prof->end(rec, ctx.st);
     ++ctx.launches;
     ctx.why = "param_class_kernel launch";
@@ -497,7 +501,7 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
   e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   if (e != cudaSuccess) return e;
   rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
-  priority_topology_kernel<<<b.T, kThreadsP, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage,
+  priority_topology_kernel<<<b.T, threads, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage,
                                                             w.par_sid ? 0 : 1);
   if (ctx.prof) ctx.prof->end(rec, ctx.st);
   ++ctx.launches;
@@ -513,7 +517,7 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     if (e != cudaSuccess) return e;
     int grid = w.cp_per_instance ? b.B : 1;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;
-    priority_critical_kernel<<<grid, kThreadsP, sm2, ctx.st>>>(b, w, use_key);
+    priority_critical_kernel<<<grid, threads, sm2, ctx.st>>>(b, w, use_key);
     if (ctx.prof) ctx.prof->end(rec, ctx.st);
     ++ctx.launches;
     ctx.why = "priority_critical_kernel launch";

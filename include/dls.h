@@ -265,6 +265,14 @@ int dls_repeat_rank_row(const uint16_t* row, int32_t n, int32_t T, uint16_t* out
  * default. Returns the previous setting (0 or 1). */
 int dls_set_stream_path(int enabled);
 
+/* Test/measurement switch (no reference counterpart). A batch with ONE topology, one node set (node_off == NULL) and
+ * per-instance durations only (flags == DLS_F_DUR_PER_INSTANCE) normally has DFS, Greedy and MRU scheduled once, on
+ * instance 0 — their decisions never read a duration (schedulers.py:154-208,244-296,444-525) — and every instance's
+ * node finish times and makespan replayed along that one assignment sequence (simulation.py:261-271); Critical still
+ * runs per instance. 0 schedules every instance with every algorithm instead; any other value restores the default.
+ * Returns the previous setting. */
+int dls_set_replay_path(int enabled);
+
 /* Number of kernel launches the library has enqueued since load (for bench accounting). */
 int64_t dls_launch_count(void);
 
@@ -285,7 +293,8 @@ int64_t dls_launch_count(void);
 #define DLS_KERNEL_STREAM_CRITICAL 10
 #define DLS_KERNEL_STREAM_MRU 11
 #define DLS_KERNEL_UNPERMUTE 12
-#define DLS_NUM_KERNELS 13
+#define DLS_KERNEL_REPLAY 13
+#define DLS_NUM_KERNELS 14
 int dls_profile_enable(int on);
 int dls_profile_read(double* ms_per_kernel, int64_t* launches_per_kernel);
 const char* dls_kernel_name(int kernel_id);

@@ -116,6 +116,67 @@ def test_shared_topology_perturbed_durations(oracle_mod):
         assert (got.node_of[slot].reshape(B, n) == got.node_of[slot, :n][None, :]).all()
 
 
+def test_one_schedule_for_duration_only_batches(oracle_mod):
+    """One topology, one node set, durations per instance: DFS / Greedy / MRU are scheduled once and replayed
+    (dls_replay.cu) — bit for bit what scheduling every instance gives and what the oracle gives, under memory
+    pressure too (failed and pending tasks, rounds, cache statistics are the template's), for any algorithm mask,
+    with the extension outputs; and the short cut steps aside when instances differ in more than their durations."""
+    import ctypes as C
+    lib = N.load()
+    base = [c for c in golden_io.load("cfg3_gpt2.npz") if c.label == "gpt2|8laptops"][0]
+    pipe = [c for c in golden_io.load("cfg2_sweep_seed0.npz") if c.label.startswith("Pipeline")][4]
+    rnd = random_dag_batch(1, 300, 8, 0.8, seed=12)
+    from dls_b200.lowering import LoweredDag
+    rdag = LoweredDag(names=[f"task_{i}" for i in range(300)], param_names=[f"p{i}" for i in range(rnd.P_max)],
+                      pred_ptr=rnd.pred_ptr, pred_idx=rnd.pred_idx, par_ptr=rnd.par_ptr, par_idx=rnd.par_idx, rank=rnd.rank,
+                      mem=rnd.mem, dur=rnd.dur)
+    cases = [(base.dag, base.cap, base.spd), (base.dag, base.cap * 0.5, base.spd), (pipe.dag, pipe.cap * 0.8, pipe.spd),
+             (rdag, rnd.cap, rnd.spd)]
+    ms = (C.c_double * N.NUM_KERNELS)()
+    cnt = (C.c_int64 * N.NUM_KERNELS)()
+    for dag, cap, spd in cases:
+        B = 96
+        batch = DagBatch.shared_topology(dag, cap, spd, B, dur=perturbed_durations(dag, B, 0.1, seed=3))
+        want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+        lib.dls_profile_enable(1)
+        lib.dls_profile_read(ms, cnt)
+        for i in range(N.NUM_KERNELS):
+            cnt[i] = 0
+        got = schedule_batch(batch, N.MASK_ALL, peak=True, cached=True).host()
+        lib.dls_profile_read(ms, cnt)
+        lib.dls_profile_enable(0)
+        names = {lib.dls_kernel_name(k).decode(): int(cnt[k]) for k in range(N.NUM_KERNELS)}
+        assert names["replay_kernel"] == 1, names
+        assert_results_equal(got, want, "replayed, all algorithms")
+        for mask in (1, 2, 8, 3, 11, 5, 4):
+            got = schedule_batch(batch, mask).host()
+            for slot, a in enumerate(got.algos):
+                np.testing.assert_array_equal(got.node_of[slot], want.node_of[a])
+                np.testing.assert_array_equal(got.seq_pos[slot], want.seq_pos[a])
+                np.testing.assert_array_equal(got.fin[slot].view(np.uint64), want.fin[a].view(np.uint64))
+                _summary_equal(got.summary[slot], want.summary[a], False)
+        old = lib.dls_set_replay_path(0)
+        try:
+            plain = schedule_batch(batch, N.MASK_ALL, peak=True, cached=True).host()
+        finally:
+            lib.dls_set_replay_path(old)
+        assert_results_equal(got := schedule_batch(batch, N.MASK_ALL, peak=True, cached=True).host(), plain, "replay vs every instance")
+    # memory per instance as well: decisions differ between instances, nothing is replayed
+    dag, cap, spd = cases[1]
+    rng = np.random.default_rng(1)
+    batch = DagBatch.shared_topology(dag, cap, spd, 64, dur=perturbed_durations(dag, 64, 0.1, seed=3),
+                                     mem=dag.mem[None, :] * rng.uniform(0.7, 1.3, (64, dag.n)))
+    lib.dls_profile_enable(1)
+    lib.dls_profile_read(ms, cnt)
+    for i in range(N.NUM_KERNELS):
+        cnt[i] = 0
+    got = schedule_batch(batch, N.MASK_ALL).host()
+    lib.dls_profile_read(ms, cnt)
+    lib.dls_profile_enable(0)
+    assert cnt[N.NUM_KERNELS - 1] == 0
+    assert_results_equal(got, oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8), "per-instance memory: no replay")
+
+
 def test_size_independent_properties_full_size():
     """At BASELINE.json's 1k-task size without an oracle run: structural invariants of any valid outcome."""
     batch = random_dag_batch(2048, 1000, 8, 0.9, seed=11)
