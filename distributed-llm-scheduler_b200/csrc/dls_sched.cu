@@ -141,7 +141,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_simple_kernel(dls_bat
   Inst v;
   bind_instance(b, inst, v);
   const OutPtrs o = bind_out(b, r, slot, inst, v);
-  const int tstat = w.topo_status[v.topo];
+  int tstat = w.topo_status[v.topo];
+  if (v.K < 0 || v.K > b.K_max) {  // node_off inconsistent with K_max, which is what the per-DAG state was sized for
+    tstat = DLS_ST_BAD_TOPOLOGY;
+    v.K = max(0, min(v.K, b.K_max));
+  }
   if (tstat != DLS_ST_OK || v.n == 0) {
     write_unscheduled(o, v, lane, tstat);
     return;
@@ -354,7 +358,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) sched_mru_kernel(dls_batch_
   Inst v;
   bind_instance(b, inst, v);
   const OutPtrs o = bind_out(b, r, slot, inst, v);
-  const int tstat = w.topo_status[v.topo];
+  int tstat = w.topo_status[v.topo];
+  if (v.K < 0 || v.K > b.K_max) {  // node_off inconsistent with K_max, which is what the per-DAG state was sized for
+    tstat = DLS_ST_BAD_TOPOLOGY;
+    v.K = max(0, min(v.K, b.K_max));
+  }
   if (tstat != DLS_ST_OK || v.n == 0) {
     write_unscheduled(o, v, lane, tstat);
     return;

@@ -19,14 +19,14 @@ def bits(a):
     return np.ascontiguousarray(a, np.float64).view(np.uint64)
 
 
-def assert_matches_expected(exp: dict, batch: DagBatch, res: ResultArrays, slot: int, b: int, what: str = ""):
+def assert_matches_expected(exp: dict, batch: DagBatch, res: ResultArrays, slot: int, b: int, what: str = "", status: int = 0):
     """Compare one (algo slot, instance) of a ResultArrays with a reference outcome from
     refharness.expected_arrays / a golden fixture. Integer/index data and fp64 state: bit-exact."""
     ts, ks, ps = batch.task_slice(b), batch.node_slice(b), batch.param_slice(b)
     K = ks.stop - ks.start
     tag = f"[{what} slot={slot} inst={b}] "
     summ = res.summary[slot, b]
-    assert summ["status"] == 0, tag + f"status {summ['status']}"
+    assert summ["status"] == status, tag + f"status {summ['status']}"
     np.testing.assert_array_equal(res.node_of[slot, ts], exp["node_of"], err_msg=tag + "node_of")
     order, nodes = sequence_of(batch, res, slot, b)
     assert order.tolist() == list(exp["order"]), tag + "global assignment order"

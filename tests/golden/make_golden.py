@@ -78,6 +78,7 @@ class Writer:
             self.arrays[f"c{c}_a{algo}_scalars"] = np.array([float(exp[f]) for f in EXP_SCALAR], np.float64)
             self.arrays[f"c{c}_a{algo}_pernode_len"] = np.array([len(x) for x in exp["per_node_seq"]], np.int32)
             self.arrays[f"c{c}_a{algo}_pernode"] = np.array([i for x in exp["per_node_seq"] for i in x], np.int32)
+            self.arrays[f"c{c}_a{algo}_refused"] = np.array(exp["refused"], np.int64)
             algmask |= 1 << algo
             dt = time.time() - t0
             if dt > 5:
@@ -103,10 +104,29 @@ class Writer:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true", help="also regenerate the slow 1k/10k-task fixtures")
+    ap.add_argument("--only-refused", action="store_true", help="write cfg1b_mru_refused.npz only")
     args = ap.parse_args()
     sch, sim = rh.ref_modules()
     ev = sim.ImprovedSchedulerEvaluator({})
     G = sim.DAGGenerator
+
+    # ---- MRU's refused assignment (ref schedulers.py:82-83 reached from :509) -----------------------------------------
+    # assign_task_to_node re-checks the fit after MRU has chosen a node. It can only say no when the eviction that made
+    # the node a candidate freed "enough" by its own arithmetic (freed >= need - avail, ref :425) while avail + 0.5 * j
+    # still rounds below need, and nothing is left to evict for a second try (:506-507). With 0.5-steps that takes an
+    # available memory in (-0.25, 0): the numbers below were found by search (negative task memory is outside the
+    # generators' domain but is data like any other to the scheduler). Task "late" is refused in round 2, stays pending,
+    # is looked at again in round 3 and fails there.
+    w = Writer()
+    for C, m0, m1 in ((0.3909436547441535, -0.3765207077218265, -0.10905634525584645),
+                      (0.3238587717729853, -0.4348473194366214, -0.17614122822701467),
+                      (0.36289824318069075, -0.5366170053406539, -0.1371017568193092)):
+        tasks = [sch.Task("first", m0, 0.1, [], {"a"}), sch.Task("late", m1, 0.2, ["first"], {"b"}),
+                 sch.Task("side", 0.0, 0.05, ["first"], set()), sch.Task("tail", 0.0, 0.05, ["late", "side"], set())]
+        w.add(f"mru_refused|C{C:.3f}", tasks, [sch.Node("only", C, 1.0)], names=True)
+    w.save(os.path.join(HERE, "cfg1b_mru_refused.npz"))
+    if args.only_refused:
+        return
 
     # ---- config 1: the built-in 4-task example (ref schedulers.py:534-548) + hand-made edge cases -----------------
     w = Writer()

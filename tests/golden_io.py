@@ -39,6 +39,7 @@ class Case:
             offs = np.concatenate([[0], np.cumsum(lens)])
             e["per_node_seq"] = [flat[offs[k]:offs[k + 1]].tolist() for k in range(K)]
             e["order"] = e["order"].tolist()
+            e["refused"] = int(z[f"c{c}_a{a}_refused"]) if f"c{c}_a{a}_refused" in z else 0
             self.exp[a] = e
 
 

@@ -96,6 +96,14 @@ class PeakMixin:
             self.__dict__.setdefault("_order_log", []).append(task_id)
         return super().complete_task(task_id)
 
+    def assign_task_to_node(self, task_id, node_id):
+        """Counts the assignments the reference refuses AFTER a node was chosen (ref schedulers.py:82-83; reached from
+        MRU's :509 when an eviction's rounding leaves the node a hair short and nothing is left to evict)."""
+        ok = super().assign_task_to_node(task_id, node_id)
+        if not ok:
+            self.__dict__["_refused"] = self.__dict__.get("_refused", 0) + 1
+        return ok
+
 
 def run_reference(algo: int, tasks, nodes):
     """Run one reference scheduler on copies of (tasks, nodes) exactly as run_single_test does
@@ -163,6 +171,6 @@ def expected_arrays(run, dag):
             "per_node_seq": per_node_seq, "completed": len(s.completed_tasks), "failed": len(s.failed_tasks),
             "pending": len(s.pending_tasks), "makespan": run["makespan"],
             "hits": run["stats"]["param_cache_hits"], "misses": run["stats"]["param_cache_misses"],
-            "key_order": [kidx[k] for k in run["schedule"].keys()],
+            "key_order": [kidx[k] for k in run["schedule"].keys()], "refused": int(getattr(s, "_refused", 0)),
             "avg_node_utilization": run["avg_node_utilization"], "load_balance_score": run["load_balance_score"],
             "completion_rate": run["completion_rate"]}

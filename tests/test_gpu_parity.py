@@ -411,6 +411,40 @@ def test_garbage_inputs_are_contained(oracle_mod):
             assert sorted(o.tolist()) == list(range(200)), (name, b)
 
 
+def test_refused_assignment_is_flagged(oracle_mod):
+    """The one corner the device does not replay: MRU's assign_task_to_node refusing after the node was chosen
+    (ref schedulers.py:82-83,509). On the three reference-generated instances where that happens
+    (cfg1b_mru_refused.npz; the oracle replays them literally, tests/test_oracle_golden.py) every device path sets
+    DLS_ST_CARRY for MRU — exactly there: the other algorithms of those instances and every algorithm of the ordinary
+    instances batched next to them come out as the reference's, and the Python class raises instead of returning a
+    schedule the reference would not have produced."""
+    from dls_b200.schedulers import MRUScheduler, Node, Task
+    odd = golden_io.load("cfg1b_mru_refused.npz")
+    plain = [c for c in golden_io.load("cfg1_example_and_edges.npz") if c.mask == N.MASK_ALL][:5]
+    cases = [plain[0], odd[0], plain[1], odd[1], odd[2]] + plain[2:]
+    batch = golden_io.batch_of(cases)
+    for path, res in run_both_paths(batch, N.MASK_ALL):
+        for b, c in enumerate(cases):
+            refused = c in odd
+            for slot, a in enumerate(res.algos):
+                if refused and a == N.ALGO_MRU:
+                    assert res.summary[slot, b]["status"] == N.ST_CARRY, f"{path} {c.label}: refusal not flagged"
+                else:
+                    assert_matches_expected(c.exp[a], batch, res, slot, b, f"{path} {c.label} algo={a}")
+    c = odd[0]
+    d = c.dag
+    s = MRUScheduler([Node("only", float(c.cap[0]), float(c.spd[0]))])
+    for i in range(d.n):
+        s.add_task(Task(d.names[i], float(d.mem[i]), float(d.dur[i]), [d.names[j] for j in d.pred_idx[d.pred_ptr[i]:d.pred_ptr[i + 1]]],
+                        {d.param_names[p] for p in d.par_idx[d.par_ptr[i]:d.par_ptr[i + 1]]}))
+    # (with "side" ahead of "late" in the set order the eviction happens for "side" and nothing is refused: impose the
+    # fixture's order, as tests/test_gpu_host_api.py does)
+    from test_gpu_host_api import _OrderedPending
+    s.pending_tasks = _OrderedPending([d.names[i] for i in np.argsort(d.rank)])
+    with pytest.raises(RuntimeError, match="refused"):
+        s.schedule()
+
+
 def test_timeline_extension_matches_oracle(oracle_mod):
     """dls_result_t.tfin (extension: node finish times on a dependency-aware timeline) — no reference output exists
     for it, so parity is pinned by the oracle only: bit for bit, on random DAGs under memory pressure, on DAGs with

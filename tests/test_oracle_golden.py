@@ -23,6 +23,23 @@ def test_oracle_reproduces_reference_fixtures(oracle_mod, fname):
                 assert_matches_expected(c.exp[a], batch, res, slot, b, f"{fname}:{c.label} algo={a}")
 
 
+def test_oracle_replays_the_refused_assignment(oracle_mod):
+    """MRU's assign_task_to_node saying no after a node was chosen (ref schedulers.py:82-83 from :509): the reference
+    leaves the task pending and looks at it again next round. tests/golden/cfg1b_mru_refused.npz holds three instances
+    on which the unmodified reference does exactly that (the harness counted one refusal each). The oracle replays it
+    literally — same verdicts, order, node state — and reports the refusal in the status word, which is what the device
+    kernels set INSTEAD of replaying (tests/test_gpu_parity.py::test_refused_assignment_is_flagged)."""
+    from dls_b200 import _native as N
+    cases = golden_io.load("cfg1b_mru_refused.npz")
+    assert len(cases) == 3 and all(c.exp[3]["refused"] == 1 and c.exp[0]["refused"] == 0 for c in cases)
+    batch = golden_io.batch_of(cases)
+    res = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=2)
+    for b, c in enumerate(cases):
+        for slot, a in enumerate(res.algos):
+            assert_matches_expected(c.exp[a], batch, res, slot, b, f"{c.label} algo={a}",
+                                    status=N.ST_CARRY if a == N.ALGO_MRU else 0)
+
+
 def test_gpt2_paper_numbers():
     """ref PDF section 6.1/6.2.2 and SURVEY.md 8(c): 99 tasks; MRU on the 4 laptops completes 99/99 with
     24/28/22/25 tasks per node; DFS/Greedy 66 done, Critical 66 done."""
