@@ -16,6 +16,7 @@
 // value buckets and pair counting inside a bucket.
 #include "dls_common.cuh"
 #include "dls_sort.cuh"
+#include "dls_tma.cuh"
 
 namespace dls {
 
@@ -302,36 +303,44 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
   const int n = v.n;
   if (n == 0) return;
   const int n_al = (n + 3) & ~3;
-  double* s_up = reinterpret_cast<double*>(smem_raw);             // [n]
-  // sort scratch (use_key): s_key[n], the keys in bucket order; without it (very large DAGs) keys are read in place
-  double* s_key = s_up + ((n + 1) & ~1);  // 16-byte aligned
-  const int nkey = use_key ? ((n + 1) & ~1) : 0;
-  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(s_key + nkey);     // [n+2] first position of each level
-  uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_lvl + (n + 2)); // [n_al] order_dg
-  uint16_t* s_depth = s_ord + n_al;                               // [n_al]
-  uint16_t* s_pq = s_depth + n_al;                                // [n_al] (use_key) pi position of each bucketed key
+  // shared memory, every region 16-byte aligned; the staged arrays sit at their global offset modulo 16 (dls_tma.cuh)
+  const size_t nkey = use_key ? ((n + 1) & ~1) : 0;
+  unsigned char* r_up = smem_raw;                                        // durations, then upward ranks [n]
+  unsigned char* r_key = r_up + staged_bytes((size_t)n * 8);             // (use_key) keys in bucket order [n]; before: reverse CSR
+  unsigned char* r_lvl = r_key + nkey * 8;                               // [n+2] first position of each level
+  unsigned char* r_ord = r_lvl + (((size_t)(n + 2) * 4 + 15) & ~(size_t)15);  // order_dg [n]
+  unsigned char* r_depth = r_ord + staged_bytes((size_t)n * 2);          // [n]
+  unsigned char* r_pq = r_depth + staged_bytes((size_t)n * 2);           // (use_key) pi position of each bucketed key [n_al]
+  double* s_key = reinterpret_cast<double*>(r_key);
+  uint32_t* s_lvl = reinterpret_cast<uint32_t*>(r_lvl);
+  uint16_t* s_pq = reinterpret_cast<uint16_t*>(r_pq);
   const uint16_t* g_depth = w.depth + v.t_topo;
   const uint32_t* succ_ptr = w.succ_ptr + v.t_topo + v.topo;
   const uint16_t* succ_idx = w.succ_idx + b.pred_off[v.topo];
   const int64_t cp_off = w.cp_per_instance ? v.t_inst : v.t_topo;
 
-  // One coalesced pass brings in everything the level loop touches: durations land in s_up (a task's slot holds its
-  // own duration until its level is processed), and the reverse adjacency is copied over the key array, which is not
-  // needed before the sort (if it fits: 4(n+1) + 2E bytes in 8n). From global memory the dependent loads of the level
-  // loop were 53 % of this kernel (clock64 per phase, round 1e).
+  // Everything the level loop touches comes in by bulk copies (one instruction of one thread per array, arrival counted
+  // on an mbarrier): durations land in s_up (a task's slot holds its own duration until its level is processed), and
+  // the reverse adjacency is copied over the key array, which is not needed before the sort (if it fits). From global
+  // memory the dependent loads of the level loop were 53 % of this kernel (clock64 per phase, round 1e); as LDG -> STS
+  // the staging was 8 % of its instructions and a fifth of its stall samples (round 2b).
   const uint32_t E = (uint32_t)(b.pred_off[v.topo + 1] - b.pred_off[v.topo]);
-  const bool staged = use_key && (size_t)4 * (n + 1) + (size_t)2 * E <= (size_t)8 * ((n + 1) & ~1);
-  uint32_t* s_sptr = reinterpret_cast<uint32_t*>(s_key);
-  uint16_t* s_sidx = reinterpret_cast<uint16_t*>(s_sptr + (n + 1));
-  strided_for<8>(n, [&](int q) {
-    s_ord[q] = __ldg(w.order_dg + v.t_topo + q);
-    s_depth[q] = __ldg(g_depth + q);
-    s_up[q] = __ldg(v.dur + q);
-  });
+  const bool staged = use_key && staged_bytes((size_t)4 * (n + 1)) + staged_bytes((size_t)2 * E) <= nkey * 8;
+  __shared__ __align__(8) uint64_t s_bar;
+  if (tid == 0) mbar_init(&s_bar, 1);
+  __syncthreads();
+  uint32_t tx = 0;
+  uint16_t* s_ord = stage_array(r_ord, w.order_dg + v.t_topo, n, &s_bar, tx);
+  uint16_t* s_depth = stage_array(r_depth, g_depth, n, &s_bar, tx);
+  double* s_up = stage_array(r_up, v.dur, n, &s_bar, tx);
+  uint32_t* s_sptr = nullptr;
+  uint16_t* s_sidx = nullptr;
   if (staged) {
-    strided_for<8>(n + 1, [&](int i) { s_sptr[i] = __ldg(succ_ptr + i); });
-    strided_for<8>((int)E, [&](int e) { s_sidx[e] = __ldg(succ_idx + e); });
+    s_sptr = stage_array(r_key, succ_ptr, n + 1, &s_bar, tx);
+    s_sidx = stage_array(r_key + staged_bytes((size_t)4 * (n + 1)), succ_idx, (int)E, &s_bar, tx);
   }
+  if (tid == 0) mbar_expect_tx(&s_bar, tx);  // (this thread's one arrival, with the byte count the copies will report)
+  mbar_wait(&s_bar, 0);
   const uint32_t* sptr = staged ? s_sptr : succ_ptr;
   const uint16_t* sidx = staged ? s_sidx : succ_idx;
   __syncthreads();
@@ -469,10 +478,11 @@ size_t priority_smem_param(int /*n_max*/, int P_max) {
   return ((size_t)P_max + 2) * sizeof(uint32_t);
 }
 
-size_t priority_smem_inst(int n_max, bool with_key) {
+size_t priority_smem_inst(int n_max, bool with_key) {  // (the carve-up at the top of priority_critical_kernel)
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
   const size_t nkey = with_key ? ((n + 1) & ~(size_t)1) : 0;
-  return (((n + 1) & ~(size_t)1) + nkey) * sizeof(double) + (n + 2) * sizeof(uint32_t) + (with_key ? 3 : 2) * n_al * sizeof(uint16_t);
+  return staged_bytes(n * 8) + nkey * 8 + (((n + 2) * 4 + 15) & ~(size_t)15) + 2 * staged_bytes(n * 2) +
+         (with_key ? n_al * sizeof(uint16_t) : 0);
 }
 
 // Small DAGs (GPT-2: 99 tasks) leave most of a 128-thread CTA idle at every barrier: one or two warps then.

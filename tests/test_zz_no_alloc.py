@@ -20,12 +20,12 @@ from dls_b200.gen import random_dag_batch
 pytestmark = pytest.mark.gpu
 
 
-def _static_call(host_batch, mask):
+def _static_call(host_batch, mask, peak=True, cached=True):
     """Call the new entry point directly through the C ABI: device inputs, device outputs, no workspace argument."""
     lib = N.load()
     dev = torch.device("cuda", torch.cuda.current_device())
     d = DeviceBatch(host_batch, dev)
-    out = BatchResult(host_batch, mask, dev, peak=True, cached=True)
+    out = BatchResult(host_batch, mask, dev, peak=peak, cached=cached)
     stream = torch.cuda.current_stream(dev).cuda_stream
     rc = lib.dls_schedule_batch_static(C.byref(d.struct), C.byref(out.struct), mask, C.c_void_p(stream))
     N.check(rc)
@@ -46,6 +46,31 @@ def test_static_scratch_matches_workspace_entry_point_twice_in_a_row():
     got = _static_call(first, 1 << N.ALGO_MRU)
     want = schedule_batch(first, 1 << N.ALGO_MRU).host()
     assert_results_equal(got, want, "static scratch, third call (MRU only)")
+
+
+def test_static_scratch_thread_per_dag_kernels_on_stale_contents(oracle_mod):
+    """Without the `cached` output a batch that fits takes the thread-per-DAG kernels on the built-in array as well
+    (record streams, verdict bytes, routing bytes, param classes all live in it). They run here right after a call of
+    another shape has left its data everywhere in the array, are checked against the CPU oracle bit for bit, and the
+    launch counters show that it really was those kernels."""
+    lib = N.load()
+    before = random_dag_batch(160, 150, 4, 0.6, seed=31)          # leaves other offsets and sizes behind
+    _static_call(before, N.MASK_ALL)
+    batch = random_dag_batch(40, 600, 8, 0.85, seed=32)
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    ms = (C.c_double * N.NUM_KERNELS)()
+    cnt = (C.c_int64 * N.NUM_KERNELS)()
+    lib.dls_profile_enable(1)
+    lib.dls_profile_read(ms, cnt)
+    for i in range(N.NUM_KERNELS):
+        cnt[i] = 0
+    for _ in range(2):   # twice: the second call reads an array full of the first one's own leftovers
+        got = _static_call(batch, N.MASK_ALL, peak=True, cached=False)
+        assert_results_equal(got, want, "static scratch, thread-per-DAG kernels")
+    lib.dls_profile_read(ms, cnt)
+    lib.dls_profile_enable(0)
+    names = {lib.dls_kernel_name(k).decode(): int(cnt[k]) for k in range(N.NUM_KERNELS)}
+    assert names["stream_build_kernel"] == 2 and names["sched_stream_mru_kernel"] == 2 and names["unpermute_kernel"] == 2, names
 
 
 def test_static_scratch_refuses_batches_beyond_its_size():
