@@ -42,20 +42,25 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   bind_topology(b, t, v);
   const int n = v.n;
   const int n_al = (n + 3) & ~3;
-  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw);              // [n+2]
-  uint16_t* s_depth = reinterpret_cast<uint16_t*>(s_cnt + (n + 2));     // [n_al]
-  uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_depth + n_al);       // [n+2]
-  uint16_t* s_ord = reinterpret_cast<uint16_t*>(s_hist + (n + 2));      // [n_al]
+  auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+  unsigned char* r_cnt = smem_raw;                                      // every region 16-byte aligned
+  unsigned char* r_depth = r_cnt + up16((size_t)(n + 2) * 4);
+  unsigned char* r_hist = r_depth + up16((size_t)n_al * 2);
+  unsigned char* r_ord = r_hist + staged_bytes((size_t)(n + 2) * 4);
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(r_cnt);                 // [n+2]
+  uint16_t* s_depth = reinterpret_cast<uint16_t*>(r_depth);             // [n_al]
+  uint32_t* s_hist = reinterpret_cast<uint32_t*>(r_hist);               // [n+2]
+  uint16_t* s_ord = reinterpret_cast<uint16_t*>(r_ord);                 // [n_al]
   uint16_t* s_tmp = s_ord + n_al;                                       // [n_al]
   // Until the orders are built (which is when s_hist / s_ord / s_tmp are first needed) the same bytes hold a copy of
   // the dependency CSR: row pointers over s_hist, indices over s_ord + s_tmp (if they fit: E <= 2 n). The depth pass
   // walks the CSR with dependent loads, one 32-task chunk after the other; from global memory that chain cost 48 %
-  // of this kernel (measured with clock64 per phase, round 1e).
-  uint32_t* s_pptr = s_hist;                                            // [n+1]
-  uint16_t* s_pidx = s_ord;                                             // [E]
-  stage = stage && v.E <= (uint32_t)(2 * n_al);
-  const uint32_t* pptr = stage ? s_pptr : v.pred_ptr;
-  const uint16_t* pidx = stage ? s_pidx : v.pred_idx;
+  // of this kernel (measured with clock64 per phase, round 1e). The copy is made by the bulk-copy engine
+  // (dls_tma.cuh) while the threads check the param row pointers and the ranks, which stay in global memory.
+  stage = stage && staged_bytes((size_t)v.E * 2) <= (size_t)n_al * 4;
+  __shared__ __align__(8) uint64_t s_bar;
+  const uint32_t* pptr = v.pred_ptr;
+  const uint16_t* pidx = v.pred_idx;
 
   uint16_t* g_depth = w.depth + v.t_topo;
   uint16_t* g_outdeg = w.outdeg + v.t_topo;
@@ -75,20 +80,30 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
       return;
     }
     if (n > 0 && (v.pred_ptr[0] != 0 || v.par_ptr[0] != 0 || v.pred_ptr[n] != v.E || v.par_ptr[n] != v.R)) bad = 1;
+    if (stage) {
+      if (tid == 0) mbar_init(&s_bar, 1);
+      __syncthreads();
+      uint32_t tx = 0;
+      pptr = stage_array(r_hist, v.pred_ptr, n + 1, &s_bar, tx);
+      pidx = stage_array(r_ord, v.pred_idx, (int)v.E, &s_bar, tx);
+      if (tid == 0) mbar_expect_tx(&s_bar, tx);
+    }
     // every load below is independent of the others: a thread keeps 8 iterations' worth in flight at once
     strided_for<8>(n, [&](int i) {
-      const uint32_t p0 = __ldg(v.pred_ptr + i), p1 = __ldg(v.pred_ptr + i + 1);
       const uint32_t q0 = __ldg(v.par_ptr + i), q1 = __ldg(v.par_ptr + i + 1);
-      if (p0 > p1 || q0 > q1 || p1 > v.E) bad = 1;
+      if (q0 > q1) bad = 1;
       if (__ldg(v.rank + i) >= n) bad = 1;
-      if (stage) s_pptr[i] = p0;
     });
-    if (stage && tid == 0) s_pptr[n] = v.E;
-    strided_for<8>((int)v.E, [&](int e) {
-      const uint16_t p = __ldg(v.pred_idx + e);
-      if (p >= n) bad = 1;
-      if (stage) s_pidx[e] = p;
-    });
+    if (stage) {
+      mbar_wait(&s_bar, 0);
+      __syncthreads();  // (the few edge elements were copied by threads)
+    }
+    for (int i = tid; i < n; i += blockDim.x) {
+      const uint32_t p0 = pptr[i], p1 = pptr[i + 1];
+      if (p0 > p1 || p1 > v.E) bad = 1;
+    }
+    for (int e = tid; e < (int)v.E; e += blockDim.x)
+      if (pidx[e] >= n) bad = 1;
     if (check_params) {  // (with the streamed path on, param_class_kernel checks them as it reads them anyway)
       strided_for<8>((int)v.R, [&](int e) {
         if (__ldg(v.par_idx + e) >= v.P) bad = 1;
@@ -471,7 +486,8 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
 
 size_t priority_smem_topo(int n_max, int /*E_max*/) {  // the staged dependency CSR aliases the sort scratch
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
-  return 2 * (n + 2) * sizeof(uint32_t) + 3 * n_al * sizeof(uint16_t);
+  auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+  return up16((n + 2) * 4) + up16(n_al * 2) + staged_bytes((n + 2) * 4) + up16(n_al * 4);
 }
 
 size_t priority_smem_param(int /*n_max*/, int P_max) {
