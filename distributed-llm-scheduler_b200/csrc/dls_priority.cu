@@ -95,8 +95,8 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
       if (__ldg(v.rank + i) >= n) bad = 1;
     });
     if (stage) {
-      mbar_wait(&s_bar, 0);
-      __syncthreads();  // (the few edge elements were copied by threads)
+      if (tid < 32) mbar_wait(&s_bar, 0);  // one warp polls; the others sleep at the barrier (polling took 6 % of the issue slots)
+      __syncthreads();  // (also: the few edge elements were copied by threads)
     }
     for (int i = tid; i < n; i += blockDim.x) {
       const uint32_t p0 = pptr[i], p1 = pptr[i + 1];
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
     s_sidx = stage_array(r_key + staged_bytes((size_t)4 * (n + 1)), succ_idx, (int)E, &s_bar, tx);
   }
   if (tid == 0) mbar_expect_tx(&s_bar, tx);  // (this thread's one arrival, with the byte count the copies will report)
-  mbar_wait(&s_bar, 0);
+  if (tid < 32) mbar_wait(&s_bar, 0);        // one warp polls; the others sleep at the barrier below
   const uint32_t* sptr = staged ? s_sptr : succ_ptr;
   const uint16_t* sidx = staged ? s_sidx : succ_idx;
   __syncthreads();

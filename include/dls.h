@@ -279,7 +279,10 @@ int64_t dls_launch_count(void);
 /* Measurement support (no reference counterpart): when enabled, every kernel the library enqueues is bracketed by
  * CUDA events on the caller's stream. dls_profile_read waits for the recorded events, ADDS the elapsed
  * milliseconds / launch counts per kernel id into the caller's arrays (DLS_NUM_KERNELS entries each) and clears
- * the record list. At most 4096 launches are kept between reads. */
+ * the record list. At most 4096 launches are kept between reads. The switch and the record list are process-wide and
+ * not synchronised: measurement code for one host thread. While it is on, events are created on demand
+ * (cudaEventCreate), also under dls_schedule_batch_static — leave it off where that entry point's "allocates nothing"
+ * matters. */
 #define DLS_KERNEL_PRIO_TOPOLOGY 0
 #define DLS_KERNEL_PRIO_CRITICAL 1
 #define DLS_KERNEL_SCHED_DFS 2
