@@ -114,91 +114,128 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
       return;
     }
   }
-  // ---- out-degree and reverse CSR (task_dependencies, ref schedulers.py:47-48) ----
-  for (int i = tid; i < n + 2; i += blockDim.x) s_cnt[i] = 0;
+  // ---- two things at once: warp 0 computes the depths, the other warps build out-degrees and the reverse CSR ----
+  // (with one warp per CTA, small DAGs, the same warp does one after the other)
+  __shared__ int s_unsorted;
+  const int nthr = blockDim.x;
+  const bool split = nthr >= 64;                 // warp 0 | warps 1..: each side syncs by itself
+  const int gtid = split ? tid - 32 : tid;       // thread index inside the CSR group (negative: warp 0 of a split CTA)
+  const int gthr = split ? nthr - 32 : nthr;
+  auto group_sync = [&]() {  // the CSR group's own barrier
+    if (split) asm volatile("bar.sync 1, %0;" ::"r"(gthr) : "memory");
+    else __syncthreads();
+  };
+  for (int i = tid; i < n + 2; i += nthr) s_cnt[i] = 0;
+  for (int i = tid; i < n; i += nthr) s_depth[i] = 0;
+  if (tid == 0) s_unsorted = 0;
   __syncthreads();
-  for (uint32_t e = tid; e < v.E; e += blockDim.x) atomicAdd(&s_cnt[pidx[e]], 1u);
-  __syncthreads();
-  {
-    int mdg = 0;
-    for (int i = tid; i < n; i += blockDim.x) {
-      g_outdeg[i] = (uint16_t)min(s_cnt[i], 65535u);
-      mdg = max(mdg, (int)min(s_cnt[i], 65535u));
+  if (gtid >= 0) {
+    // out-degree and reverse CSR (task_dependencies, ref schedulers.py:47-48)
+    for (uint32_t e = gtid; e < v.E; e += gthr) atomicAdd(&s_cnt[pidx[e]], 1u);
+    group_sync();
+    {
+      int mdg = 0;
+      for (int i = gtid; i < n; i += gthr) {
+        g_outdeg[i] = (uint16_t)min(s_cnt[i], 65535u);
+        mdg = max(mdg, (int)min(s_cnt[i], 65535u));
+      }
+      atomicMax(&s_maxdeg, mdg);
     }
-    atomicMax(&s_maxdeg, mdg);
-  }
-  __syncthreads();
-  block_exclusive_scan(s_cnt, n + 1, s_part, false);  // s_cnt[i] = start of i's dependents, s_cnt[n] = E
-  for (int i = tid; i <= n; i += blockDim.x) g_succ_ptr[i] = s_cnt[i];
-  __syncthreads();
-  // (the same walk over (task, dependency) pairs tells whether the tasks are listed in a topological order)
-  int unsorted = 0;
-  for (int i = tid; i < n; i += blockDim.x)
-    for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) {
-      const uint32_t p = pidx[e];
-      unsorted |= (int)p >= i;
-      uint32_t pos = atomicAdd(&s_cnt[p], 1u);  // order inside a list is irrelevant to max() and counts
-      g_succ_idx[pos] = (uint16_t)i;
-    }
-  unsorted = __syncthreads_or(unsorted);
-  // ---- depth: relax until a fixed point (<= levels+1 sweeps; more than n+1 sweeps means a cycle) ----
-  // The dependency CSR is staged in shared memory once: every sweep walks it again.
-  for (int i = tid; i < n; i += blockDim.x) s_depth[i] = 0;
-  __syncthreads();
-  // Tasks are usually listed in a topological order already (every dependency has a smaller index: all of the
-  // reference's generators emit them that way). Then one in-order pass by a single warp is exact: a chunk of 32
-  // tasks is repeated only while some task of the chunk still depends on another task of the same chunk.
-  int sweeps = 0, changed = 0;
-  if (!unsorted) {
-    // One in-order pass by ONE warp, 32 tasks at a time: dependencies below the chunk are final and are folded in
-    // once; a chunk is repeated only while one of its tasks depends on another task of the same chunk whose depth
-    // moved (with 32-task chunks few do: ~2 rounds per chunk instead of ~4 with CTA-wide chunks of 128, no CTA
-    // barrier, a quarter of the lanes: 5.3 k -> 2 k warp-instructions per 1k-task DAG; the other warps sleep at the
-    // barrier below and the SM's other CTAs take the issue slots).
-    if (tid < 32) {
-      const int lane = tid;
-      for (int base = 0; base < n; base += 32) {
-        const int i = base + lane;
-        const bool valid = i < n;
-        const uint32_t eb = valid ? pptr[i] : 0, ee = valid ? pptr[i + 1] : 0, np = ee - eb;
-        const uint32_t p0 = np > 0 ? pidx[eb] : 0, p1 = np > 1 ? pidx[eb + 1] : 0, p2 = np > 2 ? pidx[eb + 2] : 0;
-        const bool in0 = np > 0 && (int)p0 >= base, in1 = np > 1 && (int)p1 >= base, in2 = np > 2 && (int)p2 >= base;
-        int d_out = 0;  // what the dependencies below the chunk ask for
-        if (np > 0 && !in0) d_out = (int)s_depth[p0] + 1;
-        if (np > 1 && !in1) d_out = max(d_out, (int)s_depth[p1] + 1);
-        if (np > 2 && !in2) d_out = max(d_out, (int)s_depth[p2] + 1);
-        bool in_more = false;
-        for (uint32_t e = eb + 3; e < ee; ++e) {
-          const int p = pidx[e];
-          if (p < base) d_out = max(d_out, (int)s_depth[p] + 1);
-          else in_more = true;
-        }
-        int cur = min(d_out, 65535);
-        if (valid) s_depth[i] = (uint16_t)cur;
-        if (__any_sync(DLS_FULL_MASK, in0 || in1 || in2 || in_more)) {
-          bool moved;
-          do {
-            __syncwarp();
-            int d = d_out;
-            if (in0) d = max(d, (int)s_depth[p0] + 1);
-            if (in1) d = max(d, (int)s_depth[p1] + 1);
-            if (in2) d = max(d, (int)s_depth[p2] + 1);
-            if (in_more)
-              for (uint32_t e = eb + 3; e < ee; ++e) {
-                const int p = pidx[e];
-                if (p >= base) d = max(d, (int)s_depth[p] + 1);
-              }
-            d = min(d, 65535);
-            moved = valid && d != cur;
-            cur = d;
-            __syncwarp();  // everybody has read this round's depths
-            if (moved) s_depth[i] = (uint16_t)d;
-          } while (__any_sync(DLS_FULL_MASK, moved));
-        }
+    group_sync();
+    {  // exclusive scan of s_cnt[0..n] by the group: s_cnt[i] = start of i's dependents, s_cnt[n] = E
+      const int m = n + 1, chunk = (m + gthr - 1) / gthr;
+      const int lo = min(gtid * chunk, m), hi = min(lo + chunk, m);
+      uint32_t sum = 0;
+      for (int i = lo; i < hi; ++i) sum += s_cnt[i];
+      uint32_t incl = sum;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t x = __shfl_up_sync(DLS_FULL_MASK, incl, off);
+        if ((gtid & 31) >= off) incl += x;
+      }
+      const int gw = gtid >> 5, ngw = gthr >> 5;
+      if ((gtid & 31) == 31) s_part[gw] = incl;
+      group_sync();
+      uint32_t before = 0;
+      for (int k = 0; k < gw && k < ngw; ++k) before += s_part[k];
+      uint32_t run = before + (incl - sum);
+      for (int i = lo; i < hi; ++i) {
+        const uint32_t x = s_cnt[i];
+        s_cnt[i] = run;
+        run += x;
       }
     }
+    group_sync();
+    for (int i = gtid; i <= n; i += gthr) g_succ_ptr[i] = s_cnt[i];
+    group_sync();
+    for (int i = gtid; i < n; i += gthr)
+      for (uint32_t e = pptr[i]; e < pptr[i + 1]; ++e) {
+        const uint32_t p = pidx[e];
+        uint32_t pos = atomicAdd(&s_cnt[p], 1u);  // order inside a list is irrelevant to max() and counts
+        g_succ_idx[pos] = (uint16_t)i;
+      }
+  }
+  if (!split) __syncthreads();
+  // Tasks are usually listed in a topological order already (every dependency has a smaller index: all of the
+  // reference's generators emit them that way). Then one in-order pass by ONE warp, 32 tasks at a time, is exact:
+  // dependencies below the chunk are final and are folded in once; a chunk is repeated only while one of its tasks
+  // depends on another task of the same chunk whose depth moved (~2 rounds per chunk; CTA-wide chunks of 128 took ~4
+  // rounds, two CTA barriers each, and four times the lanes: 5.3 k -> 2 k warp-instructions per 1k-task DAG). A
+  // dependency that does not point backwards ends the pass: the relaxation below takes over.
+  if (tid < 32) {
+    const int lane = tid;
+    bool out_of_order = false;
+    for (int base = 0; base < n && !out_of_order; base += 32) {
+      const int i = base + lane;
+      const bool valid = i < n;
+      const uint32_t eb = valid ? pptr[i] : 0, ee = valid ? pptr[i + 1] : 0, np = ee - eb;
+      const uint32_t p0 = np > 0 ? pidx[eb] : 0, p1 = np > 1 ? pidx[eb + 1] : 0, p2 = np > 2 ? pidx[eb + 2] : 0;
+      bool fwd = (np > 0 && (int)p0 >= i) || (np > 1 && (int)p1 >= i) || (np > 2 && (int)p2 >= i);
+      const bool in0 = np > 0 && (int)p0 >= base, in1 = np > 1 && (int)p1 >= base, in2 = np > 2 && (int)p2 >= base;
+      int d_out = 0;  // what the dependencies below the chunk ask for
+      if (np > 0 && !in0) d_out = (int)s_depth[p0] + 1;
+      if (np > 1 && !in1) d_out = max(d_out, (int)s_depth[p1] + 1);
+      if (np > 2 && !in2) d_out = max(d_out, (int)s_depth[p2] + 1);
+      bool in_more = false;
+      for (uint32_t e = eb + 3; e < ee; ++e) {
+        const int p = pidx[e];
+        fwd |= p >= i;
+        if (p < base) d_out = max(d_out, (int)s_depth[p] + 1);
+        else in_more = true;
+      }
+      if (__any_sync(DLS_FULL_MASK, fwd)) { out_of_order = true; break; }
+      int cur = min(d_out, 65535);
+      if (valid) s_depth[i] = (uint16_t)cur;
+      if (__any_sync(DLS_FULL_MASK, in0 || in1 || in2 || in_more)) {
+        bool moved;
+        do {
+          __syncwarp();
+          int d = d_out;
+          if (in0) d = max(d, (int)s_depth[p0] + 1);
+          if (in1) d = max(d, (int)s_depth[p1] + 1);
+          if (in2) d = max(d, (int)s_depth[p2] + 1);
+          if (in_more)
+            for (uint32_t e = eb + 3; e < ee; ++e) {
+              const int p = pidx[e];
+              if (p >= base) d = max(d, (int)s_depth[p] + 1);
+            }
+          d = min(d, 65535);
+          moved = valid && d != cur;
+          cur = d;
+          __syncwarp();  // everybody has read this round's depths
+          if (moved) s_depth[i] = (uint16_t)d;
+        } while (__any_sync(DLS_FULL_MASK, moved));
+      }
+    }
+    if (lane == 0 && out_of_order) s_unsorted = 1;
+  }
+  __syncthreads();
+  // ---- depth of DAGs listed in any other order: relax until a fixed point (<= levels+1 sweeps; more than n+1 sweeps
+  // means a cycle). The dependency CSR is staged in shared memory once: every sweep walks it again.
+  int sweeps = 0, changed = 0;
+  if (s_unsorted) {
+    for (int i = tid; i < n; i += nthr) s_depth[i] = 0;
     __syncthreads();
-  } else {
     do {
       changed = 0;
       for (int i = tid; i < n; i += blockDim.x) {
