@@ -368,7 +368,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   if (tid == 0) w.nshared[t] = (int)nsh;
 }
 
-__global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key) {
+__global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_kernel(dls_batch_t b, Workspace w, int use_key, int have_mru) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int s_maxd;
   __shared__ uint32_t s_part[33];
@@ -387,7 +387,8 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
   unsigned char* r_lvl = r_key + nkey * 8;                               // [n+2] first position of each level
   unsigned char* r_ord = r_lvl + (((size_t)(n + 2) * 4 + 15) & ~(size_t)15);  // order_dg [n]
   unsigned char* r_depth = r_ord + staged_bytes((size_t)n * 2);          // [n]
-  unsigned char* r_pq = r_depth + staged_bytes((size_t)n * 2);           // (use_key) pi position of each bucketed key [n_al]
+  unsigned char* r_pq = r_depth + staged_bytes((size_t)n * 2);           // (use_key) pi position of each bucketed key [n_al];
+                                                                         // before the sort: the MRU order (see the level loop)
   double* s_key = reinterpret_cast<double*>(r_key);
   uint32_t* s_lvl = reinterpret_cast<uint32_t*>(r_lvl);
   uint16_t* s_pq = reinterpret_cast<uint16_t*>(r_pq);
@@ -408,6 +409,10 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
   __syncthreads();
   uint32_t tx = 0;
   uint16_t* s_ord = stage_array(r_ord, w.order_dg + v.t_topo, n, &s_bar, tx);
+  // The level loop may visit a level's tasks in any order. In the MRU order (same levels, out-degree descending) the 32
+  // tasks of a warp have about the same number of dependents, which is what its inner loop runs over.
+  const uint16_t* s_walk = s_ord;
+  if (use_key && have_mru) s_walk = stage_array(r_pq, w.order_mru + v.t_topo, n, &s_bar, tx);
   uint16_t* s_depth = stage_array(r_depth, g_depth, n, &s_bar, tx);
   double* s_up = stage_array(r_up, v.dur, n, &s_bar, tx);
   uint32_t* s_sptr = nullptr;
@@ -433,7 +438,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
   // upward rank, sinks first: every dependent lies on a deeper level, so it is final when read
   for (int d = maxd; d >= 0; --d) {
     for (int q = s_lvl[d] + tid; q < (int)s_lvl[d + 1]; q += blockDim.x) {
-      const int i = s_ord[q];
+      const int i = s_walk[q];
       const uint32_t sb = sptr[i], se = sptr[i + 1];
       double path = s_up[i];  // == dur[i]
       if (se > sb) {
@@ -560,7 +565,7 @@ size_t priority_smem_inst(int n_max, bool with_key) {  // (the carve-up at the t
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
   const size_t nkey = with_key ? ((n + 1) & ~(size_t)1) : 0;
   return staged_bytes(n * 8) + nkey * 8 + (((n + 2) * 4 + 15) & ~(size_t)15) + 2 * staged_bytes(n * 2) +
-         (with_key ? n_al * sizeof(uint16_t) : 0);
+         (with_key ? staged_bytes(n_al * sizeof(uint16_t)) : 0);
 }
 
 // Small DAGs (GPT-2: 99 tasks) leave most of a 128-thread CTA idle at every barrier: one or two warps then.
@@ -605,7 +610,7 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     if (e != cudaSuccess) return e;
     int grid = w.cp_per_instance ? b.B : 1;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;
-    priority_critical_kernel<<<grid, threads, sm2, ctx.st>>>(b, w, use_key);
+    priority_critical_kernel<<<grid, threads, sm2, ctx.st>>>(b, w, use_key, (algo_mask >> DLS_ALGO_MRU) & 1);
     if (ctx.prof) ctx.prof->end(rec, ctx.st);
     ++ctx.launches;
     ctx.why = "priority_critical_kernel launch";
