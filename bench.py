@@ -434,6 +434,35 @@ def main():
     clk = clocks.stop() if clocks else None
     h2d, d2h = e2e_bytes()
 
+    # ---- the sweep as run_experiments consumes it (ref simulation.py:365-416,518-524): build the instances, schedule them,
+    # average per (algorithm, group) — all on the device; only the group table crosses the bus ---------------------------
+    sweep = None
+    if wl.name == "random1k":
+        from dls_b200.batch import aggregate
+        from dls_b200.gen import random_dag_batch_device
+        groups = torch.arange(B, dtype=torch.int32, device=device) % 3   # three "regime" groups, like the reference's tables
+        res_sweep = BatchResult(host, wl.mask, device, peak=False, cached=False)   # (`res` keeps the resident run's results)
+
+        def step_sweep(k):
+            d = random_dag_batch_device(B, N_TASKS, K_NODES, REGIME, seed=SEED + 7919 * (k + 1) + rank, device=device,
+                                        rank=tie_break_rank(N_TASKS))
+            r = schedule_batch(d, wl.mask, workspace=ws, result=res_sweep)
+            return aggregate(r, groups, 3)   # returns host arrays: the D2H of the [4, 3, 8] table is the synchronisation
+
+        step_sweep(-1)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            table = step_sweep(k)
+        barrier()
+        sweep_ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(sweep_ms, op=dist.ReduceOp.MAX)
+        sweep = {"value": 4 * B * world * args.steps / (float(sweep_ms.item()) * 1e-3), "unit": UNIT,
+                 "ms_per_step": float(sweep_ms.item()) / args.steps, "d2h_bytes_per_step": int(4 * 3 * 8 * 8), "h2d_bytes_per_step": 0,
+                 "what": "dls_generate_* -> dls_schedule_batch -> dls_aggregate -> group table to the host, every step a fresh batch",
+                 "completion_rate_mean_last_step": [float(x) for x in table["completion_rate"].mean(1)]}
+
     # sanity: every instance scheduled, statuses clean (not part of any timed region)
     summ = res.summary_host()
     assert (summ["status"] == 0).all() and (summ["completed"] + summ["failed"] + summ["pending"] == n).all()
@@ -492,6 +521,8 @@ def main():
         "gpu_launches": launches,
         "clocks": clk,
     }
+    if sweep is not None:
+        line["sweep"] = sweep
     if world == 1:
         from oracle import oracle
         oracle.build()

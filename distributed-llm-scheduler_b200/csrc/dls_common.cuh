@@ -269,6 +269,11 @@ struct ReplayArgs {
   int8_t* seq_node;            // [nslots][n] scratch: its node
 };
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize for `kernel`, set only when a call needs more than was granted to that
+// kernel on the current device so far (the attribute is sticky; a scheduling call launches 13 kernels, and setting it
+// on every launch was 13 runtime calls per call). dls_abi.cu.
+cudaError_t ensure_dynamic_smem(const void* kernel, size_t bytes);
+
 // Host-side launchers (one translation unit each).
 cudaError_t launch_replay(const dls_batch_t& b, const dls_result_t& r, const ReplayArgs& a, LaunchCtx& ctx);
 cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_mask, LaunchCtx& ctx);

@@ -170,7 +170,7 @@ cudaError_t launch_gen_count(const dls_gen_t& g, int32_t* e_count, int32_t* r_co
 cudaError_t launch_gen_fill(const dls_gen_t& g, const dls_batch_t& out, LaunchCtx& ctx) {
   const size_t smem = ((size_t)2 * (g.n + 1) + 2 * (size_t)g.n + 1) * sizeof(uint32_t);
   ctx.why = "cudaFuncSetAttribute(gen_fill_kernel)";
-  cudaError_t e = cudaFuncSetAttribute(gen_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(gen_fill_kernel), (size_t)smem);
   if (e != cudaSuccess) return e;
   gen_fill_kernel<<<g.B, kGenThreads, smem, ctx.st>>>(g, out);
   ++ctx.launches;

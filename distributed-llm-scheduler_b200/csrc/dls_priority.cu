@@ -578,7 +578,7 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
   if (w.par_sid) {
     size_t smp = priority_smem_param(b.n_max, b.P_max);
     ctx.why = "cudaFuncSetAttribute(param_class_kernel)";
-    e = cudaFuncSetAttribute(param_class_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp);
+    e = ensure_dynamic_smem(reinterpret_cast<const void*>(param_class_kernel), (size_t)smp);
     if (e != cudaSuccess) return e;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PARAM_CLASS, ctx.st) : -1;
     param_class_kernel<<<b.T, threads_for(b.P_max), smp, ctx.st>>>(b, w);
@@ -591,7 +591,7 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
   size_t sm1 = priority_smem_topo(b.n_max, b.E_max);
   const int stage = 1;
   ctx.why = "cudaFuncSetAttribute(priority_topology_kernel)";
-  e = cudaFuncSetAttribute(priority_topology_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+  e = ensure_dynamic_smem(reinterpret_cast<const void*>(priority_topology_kernel), (size_t)sm1);
   if (e != cudaSuccess) return e;
   rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_TOPOLOGY, ctx.st) : -1;
   priority_topology_kernel<<<b.T, threads, sm1, ctx.st>>>(b, w, (algo_mask >> DLS_ALGO_MRU) & 1, stage,
@@ -606,7 +606,7 @@ cudaError_t launch_priority(const dls_batch_t& b, const Workspace& w, int algo_m
     const int use_key = sm2 <= 96 * 1024;
     if (!use_key) sm2 = priority_smem_inst(b.n_max, false);
     ctx.why = "cudaFuncSetAttribute(priority_critical_kernel)";
-    e = cudaFuncSetAttribute(priority_critical_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    e = ensure_dynamic_smem(reinterpret_cast<const void*>(priority_critical_kernel), (size_t)sm2);
     if (e != cudaSuccess) return e;
     int grid = w.cp_per_instance ? b.B : 1;
     rec = ctx.prof ? ctx.prof->begin(DLS_KERNEL_PRIO_CRITICAL, ctx.st) : -1;

@@ -577,7 +577,7 @@ static cudaError_t launch_one(Kern kern, int kernel_id, size_t smem, const dls_b
   const size_t slice = base + (r.tfin ? (((size_t)b.n_max * sizeof(double) + 15) & ~(size_t)15) : 0);
   const int wpc = slice * kWarpsPerCta <= 100 * 1024 ? kWarpsPerCta : 1;
   ctx.why = "cudaFuncSetAttribute(sched kernel)";
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * wpc));
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), (size_t)(slice * wpc));
   if (e != cudaSuccess) return e;
   int rec = ctx.prof ? ctx.prof->begin(kernel_id, ctx.st) : -1;
   kern<<<(b.B + wpc - 1) / wpc, 32 * wpc, slice * wpc, ctx.st>>>(b, r, w, slot, (int)(slice / 4), r.tfin ? (int)(base / 4) : -1);

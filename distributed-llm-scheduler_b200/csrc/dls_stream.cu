@@ -848,7 +848,7 @@ bool stream_path_possible(const dls_batch_t& b, const dls_result_t* r, int smem_
 template <class Kern, class... Args>
 static cudaError_t launch_fast(Kern kern, int kernel_id, dim3 grid, int threads, size_t smem, LaunchCtx& ctx, Args... args) {
   ctx.why = "cudaFuncSetAttribute(stream kernel)";
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(kern), (size_t)smem);
   if (e != cudaSuccess) return e;
   int rec = ctx.prof ? ctx.prof->begin(kernel_id, ctx.st) : -1;
   kern<<<grid, threads, smem, ctx.st>>>(args...);
