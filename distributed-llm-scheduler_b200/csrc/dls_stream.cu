@@ -784,6 +784,58 @@ __global__ void __launch_bounds__(128) unpermute_kernel(dls_batch_t b, dls_resul
   int8_t* s_node = reinterpret_cast<int8_t*>(smem_raw) + (size_t)(threadIdx.x >> 5) * 3 * n_al;
   uint16_t* s_seq = reinterpret_cast<uint16_t*>(s_node + n_al);
   int base = 0;
+  // Fast path (everything 4-aligned: any batch of DAGs whose sizes are multiples of four): a lane takes four
+  // consecutive positions — one 32-bit load of verdicts, one 64-bit load of task ids — and the prefix count of
+  // assignments over the warp comes from three ballots (a lane's count is 0..4: three bits). A third of the
+  // instructions per position of the one-position-per-lane loop below (0.85 -> see DESIGN.md).
+  const bool quad = staged && (v.n & 3) == 0 && ((reinterpret_cast<uintptr_t>(npos) & 3) == 0) &&
+                    ((reinterpret_cast<uintptr_t>(order) & 7) == 0) && ((reinterpret_cast<uintptr_t>(node_of) & 3) == 0) &&
+                    ((reinterpret_cast<uintptr_t>(seq_pos) & 7) == 0) && ((reinterpret_cast<uintptr_t>(node_of2) & 3) == 0) &&
+                    ((reinterpret_cast<uintptr_t>(seq_pos2) & 7) == 0);
+  if (quad) {
+    const unsigned lt = (1u << lane) - 1u;
+    for (int t0 = 0; t0 < v.n; t0 += 128) {
+      const int t = t0 + 4 * lane;
+      uint32_t vw = 0xfefefefeu;  // four DLS_TASK_PENDING
+      uint2 ow = make_uint2(0, 0);
+      if (t < v.n) {
+        vw = *reinterpret_cast<const uint32_t*>(npos + t);
+        ow = *reinterpret_cast<const uint2*>(order + t);
+      }
+      int vd[4], tk[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) vd[j] = (int)(int8_t)(vw >> (8 * j));
+      tk[0] = ow.x & 0xffff; tk[1] = ow.x >> 16; tk[2] = ow.y & 0xffff; tk[3] = ow.y >> 16;
+      const int c = (vd[0] >= 0) + (vd[1] >= 0) + (vd[2] >= 0) + (vd[3] >= 0);
+      const unsigned b0 = __ballot_sync(DLS_FULL_MASK, c & 1), b1 = __ballot_sync(DLS_FULL_MASK, c & 2),
+                     b2 = __ballot_sync(DLS_FULL_MASK, c & 4);
+      int sq = base + __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt);
+      base += __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+      if (t < v.n) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          int verdict = vd[j];
+          const bool asg = verdict >= 0;
+          if ((route & kRouteFailRest) && verdict == DLS_TASK_PENDING) verdict = DLS_TASK_FAILED;  // "fail all pending" (ref :202-206)
+          s_node[tk[j]] = (int8_t)verdict;
+          s_seq[tk[j]] = asg ? (uint16_t)sq : (uint16_t)DLS_SEQ_NONE;
+          sq += asg;
+        }
+      }
+    }
+    __syncwarp();
+    for (int i = 4 * lane; i < v.n; i += 128) {
+      const uint32_t nd = *reinterpret_cast<const uint32_t*>(s_node + i);
+      const uint2 sq = *reinterpret_cast<const uint2*>(s_seq + i);
+      *reinterpret_cast<uint32_t*>(node_of + i) = nd;
+      *reinterpret_cast<uint2*>(seq_pos + i) = sq;
+      if (dup) {
+        *reinterpret_cast<uint32_t*>(node_of2 + i) = nd;
+        *reinterpret_cast<uint2*>(seq_pos2 + i) = sq;
+      }
+    }
+    return;
+  }
   constexpr int kU = 4;  // chunks of 32 positions whose (independent) loads are issued together
   for (int t0 = 0; t0 < v.n; t0 += 32 * kU) {
     int verdicts[kU], tasks[kU];
@@ -904,7 +956,7 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
     sk.kind[slot++] = kOrderMRU;
   }
   // verdicts of all slots back to task ids in one launch
-  const int n_al = (b.n_max + 3) & ~3;
+  const int n_al = (b.n_max + 7) & ~7;  // (8: the staged seq_pos rows are read back eight bytes at a time)
   const size_t usm = (size_t)4 * 3 * n_al;
   const int staged = usm <= 160 * 1024;
   return launch_fast(unpermute_kernel, DLS_KERNEL_UNPERMUTE, dim3((b.B + 3) / 4, slot), 128, staged ? usm : 0, ctx, b, r, w, sk,
