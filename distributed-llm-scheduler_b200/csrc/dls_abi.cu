@@ -33,7 +33,7 @@ constexpr size_t kAlign = 256;
 size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 struct Layout {
-  size_t off_depth, off_outdeg, off_order_dg, off_order_mru, off_order_cp, off_up, off_succ_ptr, off_succ_idx,
+  size_t off_depth, off_outdeg, off_order_dg, off_order_mru, off_order_cp, off_lvl_end, off_up, off_succ_ptr, off_succ_idx,
       off_status, total;
   // streamed path (present when `stream` is set)
   size_t off_sid, off_nshared, off_stream[3], off_node_pos, off_route;
@@ -54,6 +54,7 @@ Layout layout_of(const dls_batch_t& b, int algo_mask = DLS_MASK_ALL, bool stream
   L.off_order_dg = o;  o = align_up(o + nt * sizeof(uint16_t));
   L.off_order_mru = o; o = align_up(o + nt * sizeof(uint16_t));
   L.off_order_cp = o;  o = align_up(o + ncp * sizeof(uint16_t));
+  L.off_lvl_end = o;   o = align_up(o + nt * sizeof(uint16_t));
   L.off_up = o;        o = align_up(o + ncp * sizeof(double));
   L.off_succ_ptr = o;  o = align_up(o + (nt + (size_t)b.T) * sizeof(uint32_t));
   L.off_succ_idx = o;  o = align_up(o + (size_t)b.e_total * sizeof(uint16_t));
@@ -87,6 +88,7 @@ dls::Workspace carve(void* base, const Layout& L) {
   w.order_dg = reinterpret_cast<uint16_t*>(p + L.off_order_dg);
   w.order_mru = reinterpret_cast<uint16_t*>(p + L.off_order_mru);
   w.order_cp = reinterpret_cast<uint16_t*>(p + L.off_order_cp);
+  w.lvl_end = reinterpret_cast<uint16_t*>(p + L.off_lvl_end);
   w.up = reinterpret_cast<double*>(p + L.off_up);
   w.succ_ptr = reinterpret_cast<uint32_t*>(p + L.off_succ_ptr);
   w.succ_idx = reinterpret_cast<uint16_t*>(p + L.off_succ_idx);

@@ -22,6 +22,7 @@ struct Workspace {
   uint16_t* order_dg;   // [nt_topo]   (depth asc, rank asc)
   uint16_t* order_mru;  // [nt_topo]   (depth asc, outdeg desc, rank asc)
   uint16_t* order_cp;   // [nt_cp]     (depth asc, up desc, rank asc)
+  uint16_t* lvl_end;    // [nt_topo]   lvl_end[d] = end of depth d in the orders (all three list depth 0, 1, 2, ...)
   double* up;           // [nt_cp]     upward rank                                        ref schedulers.py:301-321
   uint32_t* succ_ptr;   // [nt_topo+T] reverse adjacency (task_dependencies)              ref schedulers.py:39,47-48
   uint16_t* succ_idx;   // [e_total]

@@ -280,13 +280,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   const int maxd = s_maxd, maxdeg = s_maxdeg;
   // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
   auto by_depth = [&](int i) { return (uint32_t)s_depth[i]; };
-#ifdef DLS_SORT_CHUNKED
-  const bool chunked_d = chunk_sort_fits(n, maxd + 1, n + 2);
-#else
-  const bool chunked_d = false;
-#endif
-  if (chunked_d) chunk_counting_sort(s_ord, s_tmp, n, maxd + 1, by_depth, s_hist, s_part);
-  else stable_counting_sort(s_ord, s_tmp, n, maxd + 1, by_depth, s_hist, n + 2, s_part);
+  stable_counting_sort(s_ord, s_tmp, n, maxd + 1, by_depth, s_hist, n + 2, s_part, w.lvl_end + v.t_topo);
   for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = s_tmp[q];
   __syncthreads();
   if (want_mru) {
@@ -296,9 +290,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
     __syncthreads();
     // (one pass on the combined key (depth, degree) needs ~200 x 4 counters and was measured slower than these two)
     auto by_degree = [&](int i) { return (uint32_t)maxdeg - s_deg[i]; };
-    if (chunked_d && chunk_sort_fits(n, maxdeg + 1, n + 2)) {
-      chunk_counting_sort(s_ord, s_tmp, n, maxdeg + 1, by_degree, s_hist, s_part);
-    } else if (maxdeg + 2 <= n + 2) {
+    if (maxdeg + 2 <= n + 2) {
       stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, by_degree, s_hist, n + 2, s_part);
     } else {
       // duplicate dependency entries can push an out-degree beyond n: more keys than the histogram holds.
@@ -314,8 +306,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
       }
       __syncthreads();
     }
-    if (chunked_d) chunk_counting_sort(s_tmp, s_ord, n, maxd + 1, by_depth, s_hist, s_part);
-    else stable_counting_sort(s_tmp, s_ord, n, maxd + 1, by_depth, s_hist, n + 2, s_part);
+    stable_counting_sort(s_tmp, s_ord, n, maxd + 1, by_depth, s_hist, n + 2, s_part);
     for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_ord[q];
   }
 }
@@ -426,14 +417,15 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
   const uint32_t* sptr = staged ? s_sptr : succ_ptr;
   const uint16_t* sidx = staged ? s_sidx : succ_idx;
   __syncthreads();
+  // where each level starts in the orders: the topology kernel's depth sort left the ends (a few dozen values)
   if (tid == 0) s_maxd = s_depth[s_ord[n - 1]];
-  for (int q = tid; q < n; q += blockDim.x) {
-    int d = s_depth[s_ord[q]];
-    if (q == 0 || s_depth[s_ord[q - 1]] != d) s_lvl[d] = q;
-  }
   __syncthreads();
   const int maxd = s_maxd;
-  if (tid == 0) s_lvl[maxd + 1] = n;
+  {
+    const uint16_t* lvl_end = w.lvl_end + v.t_topo;
+    for (int d = tid; d <= maxd; d += blockDim.x) s_lvl[d + 1] = __ldg(lvl_end + d);
+    if (tid == 0) s_lvl[0] = 0;
+  }
   __syncthreads();
   // upward rank, sinks first: every dependent lies on a deeper level, so it is final when read
   for (int d = maxd; d >= 0; --d) {

@@ -16,9 +16,10 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
 // block-wide scan over the [key][warp] table turns the counts into start offsets, and each warp then places its own
 // chunk, 32 elements at a time, with __match_any giving each lane its rank among equal keys (stable). Otherwise the
 // histogram is shared and warp 0 places everything.
+// `ends_out` (optional, global memory): ends_out[k] = position after the last element with key k.
 template <class KeyF>
 __device__ inline void stable_counting_sort(const uint16_t* src, uint16_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
-                                     int hist_cap, uint32_t* s_part) {
+                                     int hist_cap, uint32_t* s_part, uint16_t* ends_out = nullptr) {
   const int nwarp = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool split = nkeys * nwarp + 1 <= hist_cap;
   const int stride = split ? nwarp : 1, col = split ? wid : 0;
@@ -51,57 +52,13 @@ __device__ inline void stable_counting_sort(const uint16_t* src, uint16_t* dst, 
     }
   }
   __syncthreads();
+  // (after placement every counter has advanced to the end of its segment: the last column of a key is the key's end)
+  if (ends_out)
+    for (int k = threadIdx.x; k < nkeys; k += blockDim.x) ends_out[k] = (uint16_t)s_hist[k * stride + stride - 1];
 }
 
-// The same sort without atomics, for up to kChunkSortMax * 32 * (warps per CTA) elements: one counter per (key,
-// 32-element chunk of src). A warp takes every (warps per CTA)-th chunk; __match_any gives each lane the lanes of its
-// chunk that hold the same key, the lowest of them stores their number (no atomic, no read-modify-write), and after
-// one scan of the [key][chunk] table a lane's destination is its counter plus its rank among those lanes, both still
-// in registers from the first pass. Measured round 2c on the topology kernel's three sorts: see DESIGN.md.
-constexpr int kChunkSortMax = 8;   // chunks per thread kept in registers
-
-__device__ __forceinline__ bool chunk_sort_fits(int n, int nkeys, int hist_cap) {
-  const int nchunks = (n + 31) >> 5, nwarp = blockDim.x >> 5;
-  return nchunks <= kChunkSortMax * nwarp && nkeys < 2048 && nkeys * (nchunks | 1) + 1 <= hist_cap;
-}
-
-template <class KeyF>
-__device__ inline void chunk_counting_sort(const uint16_t* src, uint16_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
-                                           uint32_t* s_part) {
-  const int nwarp = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nchunks = (n + 31) >> 5;
-  const int row = nchunks | 1;  // odd row length: the lanes of a warp (same chunk, different keys) fall into different banks
-  for (int k = threadIdx.x; k <= nkeys * row; k += blockDim.x) s_hist[k] = 0;
-  __syncthreads();
-  uint32_t keep[kChunkSortMax];  // element (16 bits) | key (11 bits) << 16 | rank among equal keys of the chunk << 27
-#pragma unroll
-  for (int u = 0; u < kChunkSortMax; ++u) {
-    const int c = wid + u * nwarp, q = c * 32 + lane;
-    keep[u] = 0xffffffffu;
-    if (c < nchunks) {  // (uniform per warp)
-      const bool valid = q < n;
-      const unsigned vm = __ballot_sync(DLS_FULL_MASK, valid);
-      if (valid) {
-        const uint32_t i = src[q];
-        const uint32_t k = key((int)i);
-        const unsigned peers = __match_any_sync(vm, k);
-        const uint32_t rank = __popc(peers & lanemask_lt());
-        if (rank == 0) s_hist[k * row + c] = __popc(peers);
-        keep[u] = i | (k << 16) | (rank << 27);
-      }
-    }
-  }
-  __syncthreads();
-  block_exclusive_scan(s_hist, nkeys * row, s_part);
-#pragma unroll
-  for (int u = 0; u < kChunkSortMax; ++u) {
-    const int c = wid + u * nwarp;
-    if (keep[u] != 0xffffffffu) {
-      const uint32_t k = (keep[u] >> 16) & 0x7ffu;
-      dst[s_hist[k * row + c] + (keep[u] >> 27)] = (uint16_t)(keep[u] & 0xffffu);
-    }
-  }
-  __syncthreads();
-}
+// (Measured and rejected, round 2c: the same sort with one counter per (key, 32-element chunk) — no atomics, ranks kept
+// in registers between the two passes. The scan over keys x chunks counters costs more than the atomics it replaces:
+// 4.04 -> 4.30 ms for the topology kernel.)
 
 }  // namespace dls
