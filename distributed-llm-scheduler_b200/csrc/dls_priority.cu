@@ -136,8 +136,9 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
     {
       int mdg = 0;
       for (int i = gtid; i < n; i += gthr) {
-        g_outdeg[i] = (uint16_t)min(s_cnt[i], 65535u);
-        mdg = max(mdg, (int)min(s_cnt[i], 65535u));
+        const uint32_t c = min(s_cnt[i], 65535u);
+        if (w.keep_up) g_outdeg[i] = (uint16_t)c;  // (an output of dls_priorities only; the MRU order below reads shared memory)
+        mdg = max(mdg, (int)c);
       }
       atomicMax(&s_maxdeg, mdg);
     }
@@ -285,21 +286,20 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   __syncthreads();
   if (want_mru) {
     // MRU: (depth asc, urgency desc, ready-index asc) — ref schedulers.py:462-475. LSD: urgency first, then depth.
-    uint32_t* s_deg = s_cnt;  // reuse: out-degree per task
-    strided_for<8>(n, [&](int i) { s_deg[i] = g_outdeg[i]; });
-    __syncthreads();
+    // out-degree of task i: after the fill above s_cnt[i] is the END of i's dependents in the reverse CSR
+    auto deg_of = [&](int i) { return min(s_cnt[i] - (i ? s_cnt[i - 1] : 0u), 65535u); };
     // (one pass on the combined key (depth, degree) needs ~200 x 4 counters and was measured slower than these two)
-    auto by_degree = [&](int i) { return (uint32_t)maxdeg - s_deg[i]; };
+    auto by_degree = [&](int i) { return (uint32_t)maxdeg - deg_of(i); };
     if (maxdeg + 2 <= n + 2) {
       stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, by_degree, s_hist, n + 2, s_part);
     } else {
       // duplicate dependency entries can push an out-degree beyond n: more keys than the histogram holds.
       // Rare, so place by counting: position = #(larger degree) + #(equal degree earlier in pi order).
       for (int q = tid; q < n; q += blockDim.x) {
-        const uint32_t dq = s_deg[s_ord[q]];
+        const uint32_t dq = deg_of(s_ord[q]);
         int ahead = 0;
         for (int q2 = 0; q2 < n; ++q2) {
-          const uint32_t d2 = s_deg[s_ord[q2]];
+          const uint32_t d2 = deg_of(s_ord[q2]);
           ahead += (d2 > dq) || (d2 == dq && q2 < q);
         }
         s_tmp[ahead] = s_ord[q];
