@@ -71,7 +71,8 @@ Layout layout_of(const dls_batch_t& b, int algo_mask = DLS_MASK_ALL, bool stream
                           (algo_mask & (1 << DLS_ALGO_MRU)) != 0};
     for (int k = 0; k < 3; ++k) {
       if (!need[k]) continue;
-      L.off_stream[k] = o; o = align_up(o + (size_t)b.nt_inst * 32 + 256);  // (+ room for the last prefetch)
+      // blocks of eight tasks; an instance starts at block (its first task >> 3) + (its index): see stream_block()
+      L.off_stream[k] = o; o = align_up(o + ((size_t)b.nt_inst / dls::kBlkTasks + (size_t)b.B + 4) * dls::kBlkBytes);
     }
     L.off_node_pos = o; o = align_up(o + (size_t)A * (size_t)b.nt_inst);
     L.off_route = o;    o = align_up(o + (size_t)A * (size_t)b.B);
@@ -101,7 +102,7 @@ dls::Workspace carve(void* base, const Layout& L) {
     w.par_sid = reinterpret_cast<uint16_t*>(p + L.off_sid);
     w.nshared = reinterpret_cast<int32_t*>(p + L.off_nshared);
     for (int k = 0; k < 3; ++k)
-      if (L.off_stream[k]) w.stream[k] = reinterpret_cast<dls::Rec*>(p + L.off_stream[k]);
+      if (L.off_stream[k]) w.stream[k] = reinterpret_cast<unsigned char*>(p + L.off_stream[k]);
     w.node_pos = reinterpret_cast<int8_t*>(p + L.off_node_pos);
     w.route = reinterpret_cast<uint8_t*>(p + L.off_route);
   }

@@ -32,29 +32,25 @@ struct Workspace {
   // ---- streamed (thread-per-DAG) path; all null when that path is not used ----
   uint16_t* par_sid;    // [np_topo]   dense id of a param shared by >= 2 tasks, 0xFFFF if private to one task
   int32_t* nshared;     // [T]         shared params of the topology; kUnstreamable = leave the DAG to the general kernels
-  struct Rec* stream[3];   // [nt_inst] task records in processing order: kOrderDG (DFS/Greedy), kOrderCP, kOrderMRU
+  unsigned char* stream[3];  // task blocks in processing order (see kBlkBytes): kOrderDG (DFS/Greedy), kOrderCP, kOrderMRU
   int8_t* node_pos;     // [A][nt_inst] verdict per order position (node, -1 failed, -2 pending)
   uint8_t* route;       // [A][B]      1 = instance left to the warp-per-DAG kernel
 };
 
-// One task, everything kernel S needs for a step in 32 bytes (one DRAM sector, read by one 256-bit load). The record
-// does not depend on the processing order: dependencies are task ids, and "a new round starts here" is the parity of
-// the task's depth changing (the orders list depth 0, 1, 2, ... without gaps). A stream is therefore nothing but the
-// records permuted: stream_build_kernel makes each record once and copies it to its place in every order.
-// (Reading ONE array of records through the order arrays instead was measured in round 2a: each 32-byte read costs
-// a 128-byte DRAM line, 133 KB per instance and kernel, and the scheduling kernels ran 2.4x slower.)
-struct __align__(16) Rec {
-  double m;          // Task.memory_required
-  double c;          // Task.compute_time
-  uint16_t pred[3];  // task ids of the first three dependencies (the rest: pred_idx of the input, from pred_ptr[id] + 3)
-  uint16_t id;       // the task itself (what a thread that reads records sequentially needs for its done-bitmap)
-  uint16_t a0, a1;   // first two shared-param ids (with more than two: all of them are looked up through par_idx / par_sid)
-  uint16_t npriv;    // params private to this task
-  uint8_t npred;     // number of dependencies (255 and more: DAG left to the general kernels)
-  uint8_t nsh_par;   // bits 0-6: shared params of the task (127 and more: general kernels); bit 7: depth & 1
-};
-static_assert(sizeof(Rec) == 32, "Rec must be one 32-byte sector");
-constexpr int kRecParity = 0x80;
+// What kernel S needs of a task for one step: its memory and duration (16 bytes, "hot") and one 32-bit word
+// ("meta": task id, number of private params, depth parity, has-shared-params flag). A stream holds the tasks of one
+// instance in one processing order, eight to a 160-byte block: 8 x 16 hot bytes, then 8 meta words. A scheduling
+// thread reads a block with five 32-byte loads (one per two steps for the hot pairs, one per eight for the meta words):
+// 0.625 requests and 20 bytes per step. Nothing in a block depends on the order it sits in: "a new round starts here"
+// is the parity of the task's depth flipping (the orders list depths 0, 1, 2, ... without gaps), and dependencies are
+// not in the stream at all — a task that fails or stays pending marks its dependents through the reverse CSR
+// (dls_stream.cu). (Round 2b-2e: one 32-byte record per task with the first three dependencies inline, 12.6 GB
+// written and read per 131k-instance sweep instead of 7.9; round 1: the same with dependencies translated to order
+// positions per stream. Reading ONE array of records through the order arrays instead was measured in round 2a: each
+// 32-byte read costs a 128-byte DRAM line and the scheduling kernels ran 2.4x slower.)
+constexpr int kBlkTasks = 8;
+constexpr int kBlkBytes = 160;
+constexpr uint32_t kMetaParity = 1u << 24, kMetaShared = 1u << 25;   // meta = id | npriv << 16 | flags
 constexpr int kOrderDG = 0, kOrderCP = 1, kOrderMRU = 2;  // which of kernel P's orders an algorithm slot walks
 constexpr int kSharedCap = 32;   // shared params per DAG the streamed DFS/Greedy/Critical kernel keeps masks for
 constexpr int kUnstreamable = 0x7fffffff;  // value of nshared[t] for DAGs a record cannot describe

@@ -36,7 +36,12 @@ constexpr int kRouteGeneral = 1, kRouteFailRest = 2, kRouteTwin = 4, kRouteOpen 
 constexpr int kTPB = 64;        // threads per CTA of the thread-per-DAG DFS/Greedy/Critical kernels
 constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp CTAs, 7 instead of 6 warps/SM, are slower)
 #ifndef DLS_S_MINB
-#define DLS_S_MINB 1
+#define DLS_S_MINB 8
+#endif
+#ifdef DLS_S_MAXREG
+#define DLS_S_BOUNDS(tpb) __maxnreg__(DLS_S_MAXREG)
+#else
+#define DLS_S_BOUNDS(tpb) __launch_bounds__(tpb, DLS_S_MINB)
 #endif
 constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
 constexpr int kBitmapWordsMax = 64;  // done-bits in shared memory up to 2048 tasks per DAG; beyond, done-bytes in HBM
@@ -49,58 +54,46 @@ struct RecRegs {
   uint4 lo, hi;
 };
 
-// The record of task i (dls::Rec) from the instance's arrays. Sets `unstreamable` when a count does not fit its field.
-__device__ __forceinline__ RecRegs make_record(const Inst& v, int i, const uint16_t* depth, int nsh_topo, const uint16_t* sid,
-                                               int& unstreamable) {
+// First block of an instance's stream: blocks hold eight tasks, instances have any number of them, so an instance
+// starts at (its first task >> 3) + (its index) — never inside the previous instance's last block.
+__device__ __forceinline__ size_t stream_block(int inst, const Inst& v) { return (size_t)(v.t_inst >> 3) + (size_t)inst; }
+
+struct TaskBits {
+  uint4 hot;      // m, c
+  uint32_t meta;  // id | npriv << 16 | parity | has-shared
+};
+
+// What the stream holds of task i, from the instance's arrays. Sets `unstreamable` when a count does not fit its field.
+__device__ __forceinline__ TaskBits make_task(const Inst& v, int i, const uint16_t* depth, int nsh_topo, const uint16_t* sid,
+                                              int& unstreamable) {
   const double m = __ldg(v.mem + i), c = __ldg(v.dur + i);
-  const uint32_t pb = __ldg(v.pred_ptr + i), pe = __ldg(v.pred_ptr + i + 1);
   const uint32_t qb = __ldg(v.par_ptr + i), qe = __ldg(v.par_ptr + i + 1);
-  uint32_t np = pe - pb;
-  const uint32_t p0 = np > 0 ? __ldg(v.pred_idx + pb) : 0u;
-  const uint32_t p1 = np > 1 ? __ldg(v.pred_idx + pb + 1) : 0u;
-  const uint32_t p2 = np > 2 ? __ldg(v.pred_idx + pb + 2) : 0u;
   const uint32_t d = __ldg(depth + i);
-  uint32_t nsh = 0, a0 = 0, a1 = 0, npriv = qe - qb;
+  uint32_t nsh = 0, npriv = qe - qb;
   if (nsh_topo > 0) {  // (no shared param in the DAG: nothing to look up, par_sid not even written)
     npriv = 0;
     for (uint32_t e = qb; e < qe; ++e) {
-      const uint32_t sd = sid[__ldg(v.par_idx + e)];
-      if (sd == 0xFFFF) { ++npriv; continue; }
-      if (nsh == 0) a0 = sd;
-      else if (nsh == 1) a1 = sd;
-      ++nsh;
+      if (sid[__ldg(v.par_idx + e)] == 0xFFFF) ++npriv;
+      else ++nsh;
     }
   }
-  if (np >= 255u || nsh >= 127u || npriv > 65535u) {
-    unstreamable = 1;
-    np = min(np, 255u); nsh = min(nsh, 127u); npriv = min(npriv, 65535u);
-  }
-  RecRegs r;
-  r.lo.x = (uint32_t)__double2loint(m); r.lo.y = (uint32_t)__double2hiint(m);
-  r.lo.z = (uint32_t)__double2loint(c); r.lo.w = (uint32_t)__double2hiint(c);
-  r.hi.x = p0 | (p1 << 16);
-  r.hi.y = p2 | ((uint32_t)i << 16);
-  r.hi.z = a0 | (a1 << 16);
-  r.hi.w = npriv | (np << 16) | (nsh << 24) | ((d & 1u) << 31);
-  return r;
+  if (npriv > 255u) { unstreamable = 1; npriv = 255u; }
+  TaskBits tb;
+  tb.hot.x = (uint32_t)__double2loint(m); tb.hot.y = (uint32_t)__double2hiint(m);
+  tb.hot.z = (uint32_t)__double2loint(c); tb.hot.w = (uint32_t)__double2hiint(c);
+  tb.meta = (uint32_t)i | (npriv << 16) | ((d & 1u) ? kMetaParity : 0u) | (nsh ? kMetaShared : 0u);
+  return tb;
 }
 
-__device__ __forceinline__ void store_rec(Rec* p, const RecRegs& r) {
-#if defined(DLS_ST_V4)
-  uint4* q = reinterpret_cast<uint4*>(p);
-  q[0] = r.lo;
-  q[1] = r.hi;
-#else
-  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(r.lo.x), "r"(r.lo.y), "r"(r.lo.z),
-               "r"(r.lo.w), "r"(r.hi.x), "r"(r.hi.y), "r"(r.hi.z), "r"(r.hi.w)
-               : "memory");
-#endif
+__device__ __forceinline__ void store_task(unsigned char* stream, size_t blk0, int t, const uint4& hot, uint32_t meta) {
+  unsigned char* blk = stream + (blk0 + (size_t)(t >> 3)) * kBlkBytes;
+  reinterpret_cast<uint4*>(blk)[t & 7] = hot;
+  reinterpret_cast<uint32_t*>(blk + kBlkTasks * 16)[t & 7] = meta;
 }
 
-// `staged`: the records are made in task order (coalesced reads) into shared memory, two 16-byte halves in two arrays
-// (with whole 32-byte records every first half starts on one of only four bank groups: 3.5 wavefronts per ideal one on
-// the gather, ncu source view round 1i), and each order then gathers them. Without (DAGs beyond ~7k tasks): every
-// thread makes the record of the task at its position, once per order.
+// `staged`: the tasks' stream bits are made in task order (coalesced reads) into shared memory (20 bytes per task) and
+// each order then gathers them. Without (DAGs beyond ~10k tasks): every thread makes the bits of the task at its
+// position, once per order.
 __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t b, Workspace w, int kind_mask, int staged) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int inst = blockIdx.x;
@@ -120,14 +113,15 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
   for (int kind = 0; kind < 3; ++kind)  // DAGs the thread-per-DAG kernels leave to the general ones get no stream
     use[kind] = ((kind_mask >> kind) & 1) && (kind == kOrderMRU ? nsh_topo == 0 : nsh_topo <= kSharedCap);
   if (!use[0] && !use[1] && !use[2]) return;
+  const size_t blk0 = stream_block(inst, v);
   int unstreamable = 0;
   if (staged) {
-    uint4* s_lo = reinterpret_cast<uint4*>(smem_raw);  // [n]
-    uint4* s_hi = s_lo + n;                            // [n]
+    uint4* s_hot = reinterpret_cast<uint4*>(smem_raw);            // [n]
+    uint32_t* s_meta = reinterpret_cast<uint32_t*>(s_hot + n);    // [n]
     strided_for<4>(n, [&](int i) {
-      const RecRegs r = make_record(v, i, depth, nsh_topo, sid, unstreamable);
-      s_lo[i] = r.lo;
-      s_hi[i] = r.hi;
+      const TaskBits tb = make_task(v, i, depth, nsh_topo, sid, unstreamable);
+      s_hot[i] = tb.hot;
+      s_meta[i] = tb.meta;
     });
     __syncthreads();
     // position t of all the orders in one iteration: three independent gathers per thread
@@ -136,57 +130,84 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
       for (int kind = 0; kind < 3; ++kind) {
         if (!use[kind]) continue;
         const int i = __ldg(g_order[kind] + t);
-        RecRegs r;
-        r.lo = s_lo[i];
-        r.hi = s_hi[i];
-        store_rec(w.stream[kind] + v.t_inst + t, r);
+        store_task(w.stream[kind], blk0, t, s_hot[i], s_meta[i]);
       }
     });
   } else {
     for (int kind = 0; kind < 3; ++kind) {
       if (!use[kind]) continue;
       strided_for<2>(n, [&](int t) {
-        const int i = __ldg(g_order[kind] + t);
-        store_rec(w.stream[kind] + v.t_inst + t, make_record(v, i, depth, nsh_topo, sid, unstreamable));
+        const TaskBits tb = make_task(v, __ldg(g_order[kind] + t), depth, nsh_topo, sid, unstreamable);
+        store_task(w.stream[kind], blk0, t, tb.hot, tb.meta);
       });
     }
   }
-  // a count no record can hold: the general kernels take this DAG (nshared is what routes it there)
+  // a count no field can hold: the general kernels take this DAG (nshared is what routes it there)
   if (unstreamable) w.nshared[v.topo] = kUnstreamable;
 }
 
 // -------------------------------------------------------------------------------------------------------------------
 // Shared pieces of the thread-per-DAG kernels
 // -------------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ RecRegs load_rec(const Rec* p) {
+__device__ __forceinline__ RecRegs load32(const void* p) {
   RecRegs r;
-  const uint4* q = reinterpret_cast<const uint4*>(p);
-  // L2::128B: a miss in L2 brings in the whole 128-byte line, i.e. this DAG's next three records as well
-  // and one 256-bit load instead of two 128-bit ones halves the requests of the 32 lanes, each on its own line.
-  // L1::no_allocate: a record is read once; kept out of L1 the MRU kernel runs 2.19 instead of 2.87 ms (round 2b)
-#if !defined(DLS_REC_L1ALLOC)
+  // One 256-bit load: two hot pairs or eight meta words. L2::128B: a miss in L2 brings in the whole 128-byte line, i.e.
+  // most of this DAG's block. L1::no_allocate: the stream is read once; kept out of L1 the MRU kernel ran 2.19 instead
+  // of 2.87 ms (round 2b).
   asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-#else
-  asm volatile("ld.global.nc.L2::128B.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-#endif
                : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
-               : "l"(q));
+               : "l"(p));
   return r;
 }
+#ifdef DLS_NO_PREFETCH
+__device__ __forceinline__ void prefetch_l2(const void*) {}
+#else
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-// Field accessors of a record held in registers (layout of dls::Rec).
-__device__ __forceinline__ double rec_m(const RecRegs& r) { return __hiloint2double((int)r.lo.y, (int)r.lo.x); }
-__device__ __forceinline__ double rec_c(const RecRegs& r) { return __hiloint2double((int)r.lo.w, (int)r.lo.z); }
-__device__ __forceinline__ uint32_t rec_p0(const RecRegs& r) { return r.hi.x & 0xffff; }
-__device__ __forceinline__ uint32_t rec_p1(const RecRegs& r) { return r.hi.x >> 16; }
-__device__ __forceinline__ uint32_t rec_p2(const RecRegs& r) { return r.hi.y & 0xffff; }
-__device__ __forceinline__ int rec_id(const RecRegs& r) { return (int)(r.hi.y >> 16); }
-__device__ __forceinline__ int rec_a0(const RecRegs& r) { return (int)(r.hi.z & 0xffff); }
-__device__ __forceinline__ int rec_a1(const RecRegs& r) { return (int)(r.hi.z >> 16); }
-__device__ __forceinline__ int rec_npriv(const RecRegs& r) { return (int)(r.hi.w & 0xffff); }
-__device__ __forceinline__ int rec_npred(const RecRegs& r) { return (int)((r.hi.w >> 16) & 0xff); }
-__device__ __forceinline__ int rec_nsh(const RecRegs& r) { return (int)((r.hi.w >> 24) & 0x7f); }
-__device__ __forceinline__ int rec_parity(const RecRegs& r) { return (int)(r.hi.w >> 31); }
+#endif
+
+// A thread's walk over its stream (blocks of eight tasks: 8 x 16 hot bytes, then 8 meta words). Sixteen registers
+// hold the current pair of tasks and the current block's meta words; each is reloaded the moment its last value has
+// been handed out, one step before the next one is needed (the L2 prefetch keeps that a hit). (With the next pair and
+// the next block's words in registers of their own the kernels needed ~30 registers more and lost two CTAs per SM:
+// DFS 1.38 -> 2.31 ms, round 2f.)
+struct StreamReader {
+  const unsigned char* base;  // first block of the instance
+  RecRegs hot;                // the current pair of tasks (lo: even position, hi: odd)
+  RecRegs meta;               // the current block's eight meta words
+  int n;
+  __device__ __forceinline__ void init(const unsigned char* stream, size_t blk0, int n_) {
+    base = stream + blk0 * kBlkBytes;
+    n = n_;
+    hot.lo = hot.hi = make_uint4(0, 0, 0, 0);
+    meta = hot;
+    if (n > 0) { hot = load32(base); meta = load32(base + kBlkTasks * 16); }
+    if (n > 8) {
+      prefetch_l2(base + kBlkBytes);
+      if (((uintptr_t)(base + kBlkBytes) & 127u) == 96u) prefetch_l2(base + kBlkBytes + 32);
+    }
+  }
+  // The task at position t; to be called for t = 0, 1, 2, ... in order (t is the same for all lanes of a warp).
+  __device__ __forceinline__ void take(int t, double& m, double& c, uint32_t& mw) {
+    const uint4 h = (t & 1) ? hot.hi : hot.lo;
+    m = __hiloint2double((int)h.y, (int)h.x);
+    c = __hiloint2double((int)h.w, (int)h.z);
+    const uint4 q = (t & 4) ? meta.hi : meta.lo;
+    const uint32_t qa = (t & 2) ? q.z : q.x, qb = (t & 2) ? q.w : q.y;
+    mw = (t & 1) ? qb : qa;
+    const int tn = t + 1;
+    if ((t & 1) && tn < n) {
+      const unsigned char* nb = base + (size_t)(tn >> 3) * kBlkBytes;
+      hot = load32(nb + (tn & 7) * 16);
+      if ((tn & 7) == 0) {
+        meta = load32(nb + kBlkTasks * 16);
+        if (tn + 8 < n) {  // the block after this one on its way into L2: blocks are 160 bytes, so the lines holding
+          prefetch_l2(nb + kBlkBytes);  // block starts are four out of five; the fifth follows a start at byte 96
+          if (((uintptr_t)(nb + kBlkBytes) & 127u) == 96u) prefetch_l2(nb + kBlkBytes + 32);
+        }
+      }
+    }
+  }
+};
 
 // A thread's verdict bytes (node or DLS_TASK_*) by order position. They leave in aligned words: 32 lanes storing one
 // byte each to 32 different lines cost the L1-to-L2 request path — what bounds these kernels — as much as a record
@@ -225,25 +246,77 @@ struct Slab {
   __device__ __forceinline__ double& f(int k) const { return d[k * 32 + lane]; }
 };
 
-// Which tasks of this thread's DAG are completed (is_task_ready, ref schedulers.py:50-53). One bit per task id in the
-// thread's column of the slab; for DAGs too large for that (bm_words == 0) the verdict bytes the thread itself writes
-// in task space into the node_of output (unpermute_kernel rewrites that array afterwards with the same values).
-struct DoneSet {
+// is_task_ready (ref schedulers.py:50-53) without looking at dependencies: a task is NOT ready exactly when one of its
+// dependencies failed or was left pending, and that is known when the dependency is visited (it lies in an earlier
+// round). So a task that ends without a node marks its dependents (reverse CSR of kernel P), and every task tests
+// its own mark. While nothing has failed nothing is marked or tested. One bit per task in the thread's column of the
+// slab; for DAGs too large for that (bm_words == 0) one byte per task in the node_of output, which the launcher
+// cleared and unpermute_kernel rewrites afterwards.
+struct BlockedSet {
   Slab sl;
-  int bm;            // first bitmap word in the slab
+  int bm;            // first mark word in the slab
   bool in_smem;
-  int8_t* bytes;     // task-space verdict bytes (node_of of this slot and instance)
-  __device__ __forceinline__ bool test(uint32_t p) const {
-    if (in_smem) return (sl.w(bm + (int)(p >> 5)) >> (p & 31u)) & 1u;
-    return __ldcg(bytes + p) >= 0;
+  int8_t* bytes;     // task-space mark bytes (node_of of this slot and instance)
+  __device__ __forceinline__ bool test(int i) const {
+    if (in_smem) return (sl.w(bm + (i >> 5)) >> (i & 31)) & 1u;
+    return __ldcg(bytes + i) != 0;
   }
-  __device__ __forceinline__ void record(int i, int verdict) const {  // called for every task visited while running
-    if (in_smem) {
-      if (verdict >= 0) sl.w(bm + (i >> 5)) |= 1u << (i & 31);
-    } else {
-      bytes[i] = (int8_t)verdict;
+  __device__ __forceinline__ void mark(int s) const {
+    if (in_smem) sl.w(bm + (s >> 5)) |= 1u << (s & 31);
+    else bytes[s] = 1;
+  }
+  // (the reverse CSR's addresses are worked out here, on the rare path, instead of living in registers)
+  __device__ __noinline__ void mark_dependents(const dls_batch_t& b, const Workspace& w, const Inst& v, int i) const {
+    const uint32_t* succ_ptr = w.succ_ptr + v.t_topo + v.topo;
+    const uint16_t* succ_idx = w.succ_idx + b.pred_off[v.topo];
+    const uint32_t sb = succ_ptr[i], se = succ_ptr[i + 1];
+    for (uint32_t e = sb; e < se; ++e) mark(succ_idx[e]);
+  }
+};
+
+// mark_dependents spread over three steps of the walk, for the kernels whose tasks fail often (in the 1k-task sweep a
+// tenth of the tasks of DFS / Greedy / Critical end without a node): the reverse CSR is per instance, so its two
+// dependent loads (range, then successors) are two trips to DRAM, and done on the spot they stall the warp for the one
+// lane that failed. Here the step that fails a task issues the range loads, the next step issues the loads of the first
+// four successors, the one after sets the marks; each load has a step's worth of the other warps' work to land in.
+// A dependent lies in a later round than the task (greater depth), so the marks are in time if everything in flight
+// is drained when a round starts.
+#ifndef DLS_PIPE_FAN
+#define DLS_PIPE_FAN 4
+#endif
+constexpr int kPipeFan = DLS_PIPE_FAN;  // successors fetched ahead per failed task; the rest on the spot
+struct MarkPipe {
+  const uint32_t* succ_ptr;
+  const uint16_t* succ_idx;
+  uint32_t sb, se;      // stage 1: successor range of the task that just ended without a node (loads in flight)
+  uint32_t rb, re;      // stage 2: range whose first successors are in q (loads in flight)
+  uint32_t q[kPipeFan];
+  __device__ __forceinline__ void init(const dls_batch_t& b, const Workspace& w, const Inst& v, bool have) {
+    succ_ptr = w.succ_ptr + v.t_topo + v.topo;
+    succ_idx = w.succ_idx + (have ? b.pred_off[v.topo] : 0);
+    sb = se = rb = re = 0;
+  }
+  __device__ __forceinline__ void issue(int i) { sb = succ_ptr[i]; se = succ_ptr[i + 1]; }
+  __device__ __forceinline__ void land(const BlockedSet& bs) {  // stage 2 -> marks
+    if (re > rb) {
+#pragma unroll
+      for (int j = 0; j < kPipeFan; ++j)
+        if (rb + j < re) bs.mark((int)q[j]);
+      for (uint32_t e = rb + kPipeFan; e < re; ++e) bs.mark(succ_idx[e]);
+      rb = re = 0;
     }
   }
+  __device__ __forceinline__ void fetch() {  // stage 1 -> stage 2
+    if (se > sb) {
+#pragma unroll
+      for (int j = 0; j < kPipeFan; ++j)
+        if (sb + j < se) q[j] = succ_idx[sb + j];
+      rb = sb; re = se;
+      sb = se = 0;
+    }
+  }
+  __device__ __forceinline__ void advance(const BlockedSet& bs) { land(bs); fetch(); }
+  __device__ __forceinline__ void drain(const BlockedSet& bs) { land(bs); fetch(); land(bs); }
 };
 
 template <int KMAX>
@@ -304,7 +377,7 @@ __device__ __forceinline__ void finish_thread(const dls_batch_t& b, const dls_re
 // DFS / Greedy / Critical, one thread per DAG
 // -------------------------------------------------------------------------------------------------------------------
 template <int ALGO, int KMAX, bool PEAK>
-__global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+__global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
                                                        int twin_mode, int twin_slot, int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -348,15 +421,15 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
     if (have && twin_mode == 1) w.route[(int64_t)twin_slot * b.B + inst] = kRouteOpen;
     return;
   }
-  const Rec* rec = w.stream[ALGO == DLS_ALGO_CRITICAL ? kOrderCP : kOrderDG] + v.t_inst;
+  const unsigned char* stream = w.stream[ALGO == DLS_ALGO_CRITICAL ? kOrderCP : kOrderDG];
   const uint16_t* sid = w.par_sid + (have ? b.pid_off[v.topo] : 0);
   VerdictOut vout;
   vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
-  DoneSet done;
-  done.sl = sl;
-  done.bm = BM;
-  done.in_smem = bm_words > 0;
-  done.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
+  BlockedSet blocked;
+  blocked.sl = sl;
+  blocked.bm = BM;
+  blocked.in_smem = bm_words > 0;
+  blocked.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
 
   // Node state. avail[k] of a node that does not exist is -inf: it never fits and never wins a max.
   double avail[KMAX];
@@ -396,18 +469,22 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
   bool running = elig, any_ready = false, any_assigned = false;
   bool clean = true;  // no task so far was failed or left pending: every dependency of the next task is done
   int prev_par = 0;
-  RecRegs cur;
-  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
-  if (n > 0) cur = load_rec(rec);
+  StreamReader sr;
+  sr.init(stream, stream_block(inst, v), n);
+  MarkPipe mp;
+  mp.init(b, w, v, have);
   for (int t = 0; t < n_warp; ++t) {
-    RecRegs nxt = cur;
-    if (t + 1 < n) nxt = load_rec(rec + t + 1);
-    if ((t & 3) == 0 && t + 8 < n) prefetch_l2(rec + t + 8);  // once per 128-byte line; (measured: of no use to MRU)
     if (t < n) {
-      const int i = rec_id(cur);
-      const double m = rec_m(cur), c = rec_c(cur);
-      const int npred = rec_npred(cur), npriv = rec_npriv(cur), nsh = rec_nsh(cur);
-      const int par = rec_parity(cur);
+      double m, c;
+      uint32_t mw;
+      sr.take(t, m, c, mw);
+      const int i = (int)(mw & 0xffffu), npriv = (int)((mw >> 16) & 0xffu);
+      const bool has_shared = (mw & kMetaShared) != 0;
+      const int par = (mw & kMetaParity) ? 1 : 0;
+      if (!clean) {
+        if (par != prev_par) mp.drain(blocked);
+        else mp.advance(blocked);
+      }
       if (t == 0 || par != prev_par) {  // first task of a round
         if (t > 0 && running) {
           if (!any_ready) running = false;                       // ready list empty (ref schedulers.py:172-174)
@@ -417,34 +494,21 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
       }
       prev_par = par;
       int verdict = DLS_TASK_PENDING;
-      // the shared params of the task: the first two ride in the record, with more all are read from the input
+      int nsh = 0;  // shared params of the task (counted where they are walked)
+      // the shared params of the task, through the input CSR and the param classes (LLM DAGs: a few tasks have any)
       auto for_each_shared = [&](auto f) {
-        if (nsh <= 2) {
-          if (nsh > 0) f(rec_a0(cur));
-          if (nsh > 1) f(rec_a1(cur));
-        } else {
-          for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) {
-            const int sd = sid[v.par_idx[e]];
-            if (sd != 0xFFFF) f(sd);
-          }
+        for (uint32_t e = v.par_ptr[i]; e < v.par_ptr[i + 1]; ++e) {
+          const int sd = sid[v.par_idx[e]];
+          if (sd != 0xFFFF) f(sd);
         }
       };
       if (running) {
-        // is_task_ready (ref :50-53): dependencies live in earlier rounds; while no task has failed or stayed pending
-        // they are all done and nothing is looked up
-        bool ready = true;
-        if (npred > 0 && !clean) {
-          ready = done.test(rec_p0(cur)) && (npred < 2 || done.test(rec_p1(cur))) && (npred < 3 || done.test(rec_p2(cur)));
-          if (npred > 3 && ready) {
-            const uint32_t pb = v.pred_ptr[i];
-            for (int j = 3; j < npred && ready; ++j) ready = done.test(v.pred_idx[pb + j]);
-          }
-        }
+        const bool ready = clean || !blocked.test(i);
         if (ready) {
           any_ready = true;
           int best = -1, lbest = npriv;
           double a = 0.0;  // available memory of the chosen node
-          if (nsh == 0) {
+          if (!has_shared) {
             // Every param of the task is private: params_to_load and hence the requirement are the same on every
             // node, so "fits" is avail >= need and the best fitting node is the first maximum, if that one fits.
             const double need = memory_requirement(m, npriv);
@@ -468,6 +532,7 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
             // shared params not yet cached, per node, packed one byte per node
             unsigned long long miss = 0;
             for_each_shared([&](int sd) {
+              ++nsh;
               const uint32_t mask = (sl.w(SMASK + (sd >> 2)) >> ((sd & 3) * 8)) & 0xffu;
               const unsigned long long spread = ((unsigned long long)(mask ^ 0xffu) * 0x0101010101010101ull) & 0x8040201008040201ull;
               miss += ((spread + 0x7f7f7f7f7f7f7f7full) >> 7) & 0x0101010101010101ull;
@@ -506,7 +571,7 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
             sl.w(CNT + best) += 1;
             to.misses += lbest;
             to.hits += npriv + nsh - lbest;
-            if (nsh > 0)
+            if (has_shared)
               for_each_shared([&](int sd) { sl.w(SMASK + (sd >> 2)) |= (1u << best) << ((sd & 3) * 8); });
             verdict = best;
             ++to.completed;
@@ -516,12 +581,13 @@ __global__ void __launch_bounds__(kTPB, DLS_S_MINB) sched_stream_kernel(dls_batc
             ++to.failed;
           }
         }
-        done.record(i, verdict);
+        if (verdict < 0) {  // failed, or not ready: its dependents will not be ready either
+          clean = false;
+          mp.issue(i);
+        }
       }
-      if (verdict < 0) clean = false;
       vout.put(t, verdict, t == n - 1);
     }
-    cur = nxt;
   }
   if (elig) {
     if (running) {
@@ -567,7 +633,7 @@ __device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_
 }
 
 template <int KMAX, bool PEAK>
-__global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
+__global__ void DLS_S_BOUNDS(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_result_t r, Workspace w, int slot,
                                                                  int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -596,14 +662,14 @@ __global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls
   const int n = elig ? v.n : 0, K = v.K;
   const int n_warp = __reduce_max_sync(DLS_FULL_MASK, n);
   if (n_warp == 0) return;
-  const Rec* rec = w.stream[kOrderMRU] + v.t_inst;
+  const unsigned char* stream = w.stream[kOrderMRU];
   VerdictOut vout;
   vout.init(w.node_pos + (int64_t)slot * b.nt_inst + v.t_inst);
-  DoneSet done;
-  done.sl = sl;
-  done.bm = BM;
-  done.in_smem = bm_words > 0;
-  done.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
+  BlockedSet blocked;
+  blocked.sl = sl;
+  blocked.bm = BM;
+  blocked.in_smem = bm_words > 0;
+  blocked.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
 
   double avail[KMAX];  // -inf for nodes that do not exist: they never fit
 #pragma unroll
@@ -626,17 +692,15 @@ __global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls
   int carried = 0;
   bool running = elig, any_ready = false, any_assigned = false, clean = true;
   int prev_par = 0;
-  RecRegs cur;
-  cur.lo = cur.hi = make_uint4(0, 0, 0, 0);
-  if (n > 0) cur = load_rec(rec);
+  StreamReader sr;
+  sr.init(stream, stream_block(inst, v), n);
   for (int t = 0; t < n_warp; ++t) {
-    RecRegs nxt = cur;
-    if (t + 1 < n) nxt = load_rec(rec + t + 1);
     if (t < n) {
-      const int i = rec_id(cur);
-      const double m = rec_m(cur), c = rec_c(cur);
-      const int npred = rec_npred(cur), npar = rec_npriv(cur);
-      const int par = rec_parity(cur);
+      double m, c;
+      uint32_t mw;
+      sr.take(t, m, c, mw);
+      const int i = (int)(mw & 0xffffu), npar = (int)((mw >> 16) & 0xffu);
+      const int par = (mw & kMetaParity) ? 1 : 0;
       if (t == 0 || par != prev_par) {
         if (t > 0 && running) {
           if (!any_ready) running = false;
@@ -647,14 +711,7 @@ __global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls
       prev_par = par;
       int verdict = DLS_TASK_PENDING;
       if (running) {
-        bool ready = true;  // is_task_ready (ref :50-53), as in sched_stream_kernel
-        if (npred > 0 && !clean) {
-          ready = done.test(rec_p0(cur)) && (npred < 2 || done.test(rec_p1(cur))) && (npred < 3 || done.test(rec_p2(cur)));
-          if (npred > 3 && ready) {
-            const uint32_t pb = v.pred_ptr[i];
-            for (int j = 3; j < npred && ready; ++j) ready = done.test(v.pred_idx[pb + j]);
-          }
-        }
+        const bool ready = clean || !blocked.test(i);  // is_task_ready (ref :50-53), as in sched_stream_kernel
         if (ready) {
           any_ready = true;
           // none of the task's (private) params is cached anywhere: params_to_load = npar on every node
@@ -734,12 +791,13 @@ __global__ void __launch_bounds__(kTPBM, DLS_S_MINB) sched_stream_mru_kernel(dls
             ++to.failed;
           }
         }
-        done.record(i, verdict);
+        if (verdict < 0) {  // failed, or not ready: its dependents will not be ready either
+          clean = false;
+          blocked.mark_dependents(b, w, v, i);
+        }
       }
-      if (verdict < 0) clean = false;
       vout.put(t, verdict, t == n - 1);
     }
-    cur = nxt;
   }
   if (elig) {
     if (running) {
@@ -915,7 +973,7 @@ cudaError_t launch_stream_build(const dls_batch_t& b, const Workspace& w, int al
   if (algo_mask & 3) kinds |= 1 << kOrderDG;
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) kinds |= 1 << kOrderCP;
   if (algo_mask & (1 << DLS_ALGO_MRU)) kinds |= 1 << kOrderMRU;
-  const size_t smem = (size_t)b.n_max * 32;
+  const size_t smem = (size_t)b.n_max * 20;
   const int staged = smem <= 200 * 1024;
   return launch_fast(stream_build_kernel, DLS_KERNEL_STREAM_BUILD, dim3(b.B), kBuildThreads, staged ? smem : 0, ctx, b, w, kinds,
                      staged);
@@ -926,6 +984,13 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
                                          LaunchCtx& ctx) {
   const dim3 grid((b.B + kTPB - 1) / kTPB);
   const int bmw = bitmap_words(b.n_max);
+  if (bmw == 0) {  // DAGs too large for mark bits in shared memory keep mark bytes in the node_of output: start from zero
+    int A = 0;
+    for (int a = 0; a < DLS_NUM_ALGOS; ++a) A += (algo_mask >> a) & 1;
+    ctx.why = "cudaMemsetAsync(node_of)";
+    cudaError_t e0 = cudaMemsetAsync(r.node_of, 0, (size_t)A * (size_t)b.nt_inst, ctx.st);
+    if (e0 != cudaSuccess) return e0;
+  }
   int slot = 0;
   SlotKinds sk = {{0, 0, 0, 0}, {-1, -1, -1, -1}};
   cudaError_t e = cudaSuccess;
