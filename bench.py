@@ -119,11 +119,21 @@ class ClockSampler:
     def __init__(self, gpu_index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.gpu = gpu_index
+        self.skip = 0
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
                                        "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
+
+    def mark(self):
+        """The timed region starts here: samples written before are dropped. (The sampler is started BEFORE the region:
+        nvidia-smi attaching to the driver stalled rank 0's first launches by 35-80 ms on an 8-GPU box, which the other
+        ranks then waited for in the sweep's collective — r2f, 22.6 instead of 15.0 ms per step.)"""
+        try:
+            self.skip = os.path.getsize(self.f.name)
+        except OSError:
+            self.skip = 0
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
@@ -135,7 +145,7 @@ class ClockSampler:
         except Exception:
             self.p.kill()
         self.f.flush()
-        self.f.seek(0)
+        self.f.seek(self.skip)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f.read().splitlines():
@@ -363,12 +373,14 @@ def main():
         torch.cuda.synchronize(device)
 
     # ---- resident-input timing -----------------------------------------------------------------------------------
+    clocks = ClockSampler(local) if rank == 0 else None  # (running before the region starts: see ClockSampler.mark)
     for _ in range(args.warmup):
         step_resident()
     if world > 1:
         gathered = gather_summaries(res.summary, world)  # (warm-up of the collective as well)
     barrier()
-    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.mark()
     lib.dls_profile_enable(1)
     ms_k = (C.c_double * N.NUM_KERNELS)()
     cnt_k = (C.c_int64 * N.NUM_KERNELS)()
@@ -377,10 +389,12 @@ def main():
         ms_k[i] = 0.0
         cnt_k[i] = 0
     launches0 = lib.dls_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    gathered = None  # (the warm-up gather's 200 MB go back to torch's allocator: the timed one reuses them)
+    ev0, ev1, evm = (torch.cuda.Event(enable_timing=True) for _ in range(3))
     ev0.record()
     for _ in range(args.steps):
         step_resident()
+    evm.record()
     if world > 1:  # the sweep's one collective: every rank's per-instance records (makespan, peak memory, counters)
         gathered = gather_summaries(res.summary, world)
     ev1.record()
@@ -388,10 +402,15 @@ def main():
     launches = int(lib.dls_launch_count() - launches0)
     N.check(lib.dls_profile_read(ms_k, cnt_k))
     lib.dls_profile_enable(0)
-    elapsed = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=device)
+    # max over ranks of the whole region; beside it, where a multi-rank region's time went: this rank's steps (max and
+    # min over ranks) and the collective including the wait for the slowest rank
+    elapsed = torch.tensor([ev0.elapsed_time(ev1), ev0.elapsed_time(evm), -ev0.elapsed_time(evm), evm.elapsed_time(ev1)],
+                           dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
-    ms_total = float(elapsed.item())
+    ms_total = float(elapsed[0].item())
+    region = {"steps_ms_max_over_ranks": float(elapsed[1].item()), "steps_ms_min_over_ranks": -float(elapsed[2].item()),
+              "collective_and_wait_ms_max_over_ranks": float(elapsed[3].item())}
 
     # ---- end-to-end timing: host inputs in, host results out, every step -------------------------------------------
     if wl.name == "random1k":
@@ -519,7 +538,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": float(e2e_ms.item()) / args.steps, "api": e2e_api},
         "gpu_launches": launches,
-        "clocks": clk,
+        "clocks": clk, "timed_region": region,
     }
     if sweep is not None:
         line["sweep"] = sweep

@@ -169,7 +169,8 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // hold the current pair of tasks and the current block's meta words; each is reloaded the moment its last value has
 // been handed out, one step before the next one is needed (the L2 prefetch keeps that a hit). (With the next pair and
 // the next block's words in registers of their own the kernels needed ~30 registers more and lost two CTAs per SM:
-// DFS 1.38 -> 2.31 ms, round 2f.)
+// DFS 1.38 -> 2.31 ms, round 2f. Issuing each load TWO steps ahead, with the odd task of the pair and the block's last
+// meta word parked in five more registers, was slower too: DFS 1.64 -> 1.91 ms, MRU 2.29 -> 2.53 ms.)
 struct StreamReader {
   const unsigned char* base;  // first block of the instance
   RecRegs hot;                // the current pair of tasks (lo: even position, hi: odd)

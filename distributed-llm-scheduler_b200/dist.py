@@ -35,7 +35,7 @@ def gather_summaries(summary, world: int):
     # (8 bytes per rank, every call: a cached "shards are equal" would let ranks disagree on which collective comes next
     # as soon as one call has even shards and the next has not)
     dist.all_gather(all_sizes, sizes)
-    b_max = int(max(int(s.item()) for s in all_sizes))
+    b_max = int(torch.cat(all_sizes).max().item())  # (one device-to-host read, not one per rank)
     if b_max != b_local:
         pad = torch.zeros((A, b_max - b_local, summary.shape[2]), dtype=summary.dtype, device=summary.device)
         summary = torch.cat([summary, pad], 1)
