@@ -502,3 +502,55 @@ def test_tasks_listed_in_any_order(oracle_mod):
     assert (want.summary["status"] == 0).all() and want.summary["completed"].sum() > 0
     for path, got in run_both_paths(batch, N.MASK_ALL):
         assert_results_equal(got, want, f"{path} relabelled tasks")
+
+
+def _hub_dag(rng, n, fan, K):
+    """A DAG in which one early task (the hub) cannot fit anywhere: it fails, and everything that depends on it,
+    directly (`fan` tasks) or through other tasks, must stay pending. Other dependencies are random."""
+    from dls_b200.lowering import LoweredDag
+    hub = int(rng.integers(0, max(1, n // 4)))
+    later = np.arange(hub + 1, n)
+    direct = set(rng.choice(later, size=min(fan, len(later)), replace=False).tolist()) if len(later) else set()
+    preds = []
+    for i in range(n):
+        p = set()
+        if i in direct:
+            p.add(hub)
+        for _ in range(int(rng.integers(0, 3))):
+            if i > 0:
+                p.add(int(rng.integers(0, i)))
+        preds.append(sorted(p))
+    npar = rng.integers(1, 3, size=n)
+    mem = rng.uniform(0.1, 0.5, size=n)
+    cap = np.full(K, float((mem + 0.5 * npar).max() + 0.5 * npar.sum() * rng.uniform(0.3, 1.1) / K))
+    mem[hub] = 10.0 * cap[0] + 5.0
+    dag = LoweredDag(names=[f"t{j}" for j in range(n)], param_names=[f"p{j}" for j in range(int(npar.sum()))],
+                     pred_ptr=np.concatenate([[0], np.cumsum([len(p) for p in preds])]).astype(np.uint32),
+                     pred_idx=np.asarray([q for p in preds for q in p], np.uint16),
+                     par_ptr=np.concatenate([[0], np.cumsum(npar)]).astype(np.uint32),
+                     par_idx=np.arange(int(npar.sum()), dtype=np.uint16), rank=rng.permutation(n).astype(np.uint16),
+                     mem=mem, dur=rng.uniform(0.05, 0.15, size=n))
+    return dag, (cap, rng.uniform(0.5, 2.0, size=K))
+
+
+@pytest.mark.parametrize("sizes,fans", [((5, 8, 9, 17, 40, 100, 300), (1, 3, 4, 5, 17, 10 ** 6)), ((2100, 2500), (4, 5, 600, 10 ** 6))])
+def test_failed_tasks_block_their_dependents_at_any_fan_out(oracle_mod, sizes, fans):
+    """is_task_ready on the thread-per-DAG path is a mark set by the dependency that ended without a node (reverse
+    CSR, the first four dependents fetched ahead, the rest on the spot; marks drained when a round starts): hubs with
+    fewer, exactly, and many more dependents than the pipeline's width, cascades over several rounds, instance lengths
+    around the 8-task blocks of the streams, and DAGs beyond 2,048 tasks (mark bytes in HBM instead of bits in shared
+    memory) — every device path against the oracle, bit for bit."""
+    rng = np.random.default_rng(len(sizes) * 1000 + 7)
+    dags, nodes = [], []
+    for n in sizes:
+        for fan in fans:
+            for _ in range(2):
+                d, nd = _hub_dag(rng, n, fan, 4)
+                dags.append(d)
+                nodes.append(nd)
+    batch = DagBatch.from_instances(dags, nodes)
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    assert (want.summary["status"] == 0).all()
+    assert (want.summary["failed"] >= 1).all() and want.summary["pending"].sum() > 0 and want.summary["completed"].sum() > 0
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} hub DAGs n={sizes}")
