@@ -618,18 +618,38 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
 // frees exactly 0.5 and the reference walks them until `freed >= shortage`: it needs j = ceil(shortage / 0.5) of
 // them and succeeds iff j <= ncached. On success the node's available memory goes up by 0.5, j times (ref :429); on
 // failure all ncached are evicted and rolled back, which leaves only the +0.5 / -0.5 rounding trace (ref :438-441).
+//
+// x + 0.5 + 0.5 + ... (j additions, one rounding each, as the reference does them) equals fl(x + 0.5 j) whenever that
+// one sum is exact (TwoSum's error term is zero): every partial sum v = x + 0.5 i lies between x and the result s, is a
+// multiple of ulp(x) counted from x and of ulp(s) counted back from s (0.5 is a multiple of both below 2^51), hence
+// of ulp(v) <= max(ulp(x), ulp(s)): representable, so no addition of the chain rounds. Anything else (a sum that
+// crosses into a binade where x's last bits do not fit, NaN, infinities) takes the chain itself. The chain was 10 % of
+// this kernel's stall samples (ncu r2f): lanes evict different numbers of params and the warp waits for the longest.
+__device__ __forceinline__ bool add_halves_exactly(double x, uint32_t j, double& s) {
+  const double h = __dmul_rn(0.5, (double)j);  // exact
+  s = __dadd_rn(x, h);
+  const double bb = __dsub_rn(s, x);
+  const double err = __dadd_rn(__dsub_rn(x, __dsub_rn(s, bb)), __dsub_rn(h, bb));
+  return err == 0.0 && fabs(x) < 0x1p51 && fabs(s) < 0x1p51;
+}
+
 __device__ __forceinline__ bool plan_evict(double need, double& avail_k, uint32_t& ncached) {
   const double shortage = __dsub_rn(need, avail_k);
   if (shortage <= 0.0) return true;
   const double want = ceil(__dmul_rn(shortage, 2.0));  // exact: power-of-two scaling, then ceil
+  double s;
   if (want <= (double)ncached) {
     const uint32_t j = (uint32_t)want;
-    for (uint32_t q = 0; q < j; ++q) avail_k = __dadd_rn(avail_k, 0.5);
+    if (add_halves_exactly(avail_k, j, s)) avail_k = s;
+    else
+      for (uint32_t q = 0; q < j; ++q) avail_k = __dadd_rn(avail_k, 0.5);
     ncached -= j;
     return true;
   }
-  for (uint32_t q = 0; q < ncached; ++q) avail_k = __dadd_rn(avail_k, 0.5);
-  for (uint32_t q = 0; q < ncached; ++q) avail_k = __dsub_rn(avail_k, 0.5);
+  if (!add_halves_exactly(avail_k, ncached, s)) {  // (exact on the way up: the way down retraces the same values)
+    for (uint32_t q = 0; q < ncached; ++q) avail_k = __dadd_rn(avail_k, 0.5);
+    for (uint32_t q = 0; q < ncached; ++q) avail_k = __dsub_rn(avail_k, 0.5);
+  }
   return false;
 }
 

@@ -117,3 +117,31 @@ def check_random_dag_structure(b, n):
 
 def test_generator_matches_reference_distribution():
     check_random_dag_structure(random_dag_batch(32, 300, 8, 0.9, seed=3), 300)
+
+
+def test_chain_of_half_additions_has_a_closed_form_when_exact():
+    """dls_stream.cu::add_halves_exactly replaces MRU's eviction chain x + 0.5 + 0.5 + ... (ref schedulers.py:429, one
+    rounding per param) by ONE addition whenever TwoSum says that addition is exact; the claim is that the chain then
+    never rounds either, and that the rollback chain (ref :438-441) returns to x. Checked here in numpy on magnitudes,
+    binade edges and signs the kernels see, including many cases where the one-shot sum is NOT exact (those keep the
+    chain on the device)."""
+    rng = np.random.default_rng(1)
+    n = 300_000
+    exp = rng.integers(-8, 12, n)
+    x = np.ldexp(1 + rng.random(n), exp) * rng.choice([1, -1], n)
+    edge = rng.random(n) < 0.3
+    x[edge] = np.ldexp(1.0, exp[edge]) - np.ldexp(rng.integers(0, 8, edge.sum()).astype(float), exp[edge] - 53) * rng.choice([1, -1], edge.sum())
+    j = rng.integers(0, 70, n)
+    h = 0.5 * j
+    s = x + h
+    bb = s - x
+    err = (x - (s - bb)) + (h - bb)
+    exact = (err == 0) & (np.abs(x) < 2.0 ** 51) & (np.abs(s) < 2.0 ** 51)
+    up = x.copy()
+    for q in range(70):
+        up[q < j] += 0.5
+    down = up.copy()
+    for q in range(70):
+        down[q < j] -= 0.5
+    assert 0.2 < exact.mean() < 0.9 and (up != s).sum() > 1000          # both kinds of case are in the sample
+    assert (up[exact] == s[exact]).all() and (down[exact] == x[exact]).all()

@@ -9,6 +9,7 @@ from dls_b200 import _native as N
 from dls_b200.batch import schedule_batch
 from dls_b200.gen import random_dag_batch_device
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 131072
+STAGGER = os.environ.get("DLS_STAGGER")  # stream s starts s/S of a step late, so that different kernels overlap
 for S in (1, 2, 4):
     devs = [random_dag_batch_device(B // S, 1000, 8, 0.9, seed=1000 + s) for s in range(S)]
     streams = [torch.cuda.Stream() for _ in range(S)]
@@ -26,10 +27,13 @@ for S in (1, 2, 4):
         step()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    K = 5
+    K = 10
     e0.record()
-    for st in streams:
+    for s, st in enumerate(streams):
         st.wait_event(e0)
+        if STAGGER and s:
+            with torch.cuda.stream(st):
+                torch.cuda._sleep(int(float(STAGGER) * 1.9e6 * s / S))  # DLS_STAGGER = ms of a step, in cycles at 1.9 GHz
     for _ in range(K):
         step()
     for st in streams:
