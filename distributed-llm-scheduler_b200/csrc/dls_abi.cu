@@ -66,7 +66,7 @@ Layout layout_of(const dls_batch_t& b, int algo_mask = DLS_MASK_ALL, bool stream
     const int A = count_bits(algo_mask & DLS_MASK_ALL);
     L.off_sid = o;     o = align_up(o + np * sizeof(uint16_t));
     L.off_nshared = o; o = align_up(o + (size_t)b.T * sizeof(int32_t));
-    // per processing order in use, one 32-byte record per instance-task
+    // per processing order in use, one stream of 160-byte blocks (eight tasks each)
     const bool need[3] = {(algo_mask & 3) != 0, (algo_mask & (1 << DLS_ALGO_CRITICAL)) != 0,
                           (algo_mask & (1 << DLS_ALGO_MRU)) != 0};
     for (int k = 0; k < 3; ++k) {

@@ -1,23 +1,25 @@
-// dls_stream.cu — the throughput path: one THREAD per DAG instance over an order-permuted record stream.
+// dls_stream.cu — the throughput path: one THREAD per DAG instance over order-permuted task streams.
 //
 // Why: the list-scheduling loop is a serial chain of n dependent steps per DAG, but a sweep has ~10^5..10^6
 // independent DAGs. With one warp per DAG every instruction of the chain serves one DAG (≈340 warp-instructions per
 // task-step, profiles/r1a_*); with one thread per DAG the same instruction serves 32. To make that work the
-// per-thread memory accesses must not scatter: stream_build_kernel writes each DAG, once per processing order, as a
-// contiguous array of 32-byte records (dls::Rec, one DRAM sector per step), so every step of every thread reads
-// exactly one fully used sector, and per-thread mutable state lives in shared memory laid out [word][lane] (each lane
-// owns a bank: no conflicts whatever the index), including one done-bit per task.
+// per-thread memory accesses must not scatter: stream_build_kernel writes each DAG, once per processing order, as
+// contiguous 160-byte blocks of eight tasks (dls_common.cuh: 8 x {memory, duration}, then 8 meta words), so every
+// thread reads fully used 32-byte sectors and nothing else, and per-thread mutable state lives in shared memory laid
+// out [word][lane] (each lane owns a bank: no conflicts whatever the index), including one mark bit per task.
 //
-// A record does not depend on the order it is placed in (dependencies are task ids, a new round is the depth parity
-// flipping): the build kernel makes every record once, in task order with coalesced reads, and then only permutes.
-// (Round 1 translated dependencies to order positions per stream: an inverted order per stream, three look-ups per
-// record and a 4.3 ms kernel. Round 2a tried no streams at all — one record array read through the order arrays — and
-// found every 32-byte read costing a 128-byte DRAM line: the scheduling kernels ran 2.4x slower.)
+// A task's stream bits do not depend on the order they are placed in (a new round is the depth parity flipping;
+// dependencies are not in the stream: a task that ends without a node marks its dependents through the reverse CSR,
+// see BlockedSet / MarkPipe): the build kernel makes them once, in task order with coalesced reads, and then only
+// permutes. (Round 1 translated dependencies to order positions per stream: an inverted order per stream, three
+// look-ups per record and a 4.3 ms kernel. Round 2a tried no streams at all — one record array read through the
+// order arrays — and found every 32-byte read costing a 128-byte DRAM line: the scheduling kernels ran 2.4x slower.
+// Rounds 2b-2e: 32-byte records with the first three dependencies inline, build kernel 3.26 ms against 2.18.)
 //
 // Verdicts are written in order-position space (sequential bytes per thread, stored a word at a time);
 // unpermute_kernel maps them back to task ids and derives seq_pos by a prefix count. Instances the fast kernels
-// cannot take (more than 8 nodes, more than 32 shared params, MRU with any shared param, a task with 255+
-// dependencies, bad topology) are flagged in `route` and picked up by the warp-per-DAG kernels of dls_sched.cu, which
+// cannot take (more than 8 nodes, more than 32 shared params, MRU with any shared param, a task with 256+
+// private params, bad topology) are flagged in `route` and picked up by the warp-per-DAG kernels of dls_sched.cu, which
 // remain the general implementation.
 //
 // All fp64 arithmetic is the same op-by-op replay as in dls_sched.cu (see the header comment there).
@@ -44,7 +46,7 @@ constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp
 #define DLS_S_BOUNDS(tpb) __launch_bounds__(tpb, DLS_S_MINB)
 #endif
 constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
-constexpr int kBitmapWordsMax = 64;  // done-bits in shared memory up to 2048 tasks per DAG; beyond, done-bytes in HBM
+constexpr int kBitmapWordsMax = 64;  // mark bits in shared memory up to 2048 tasks per DAG; beyond, mark bytes in HBM
 
 // -------------------------------------------------------------------------------------------------------------------
 // stream_build_kernel: grid B. One CTA per instance makes the instance's records and writes them in every requested
@@ -383,7 +385,7 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   // slab layout per warp: doubles fin[KMAX], spd[KMAX] (+ amin[KMAX]); words smask[kSharedCap/4], cnt[KMAX],
-  // done-bits[bm_words]
+  // mark-bits[bm_words]
   constexpr int kD = (PEAK ? 3 : 2) * KMAX;
   const int kW = kSharedCap / 4 + KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
@@ -659,7 +661,7 @@ __global__ void DLS_S_BOUNDS(kTPBM) sched_stream_mru_kernel(dls_batch_t b, dls_r
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   // slab per warp: doubles fin[KMAX], spd[KMAX], hcnt[KMAX] (+ amin[KMAX]); words cnt[KMAX], ncached[KMAX],
-  // done-bits[bm_words]
+  // mark-bits[bm_words]
   constexpr int kD = (PEAK ? 4 : 3) * KMAX;
   const int kW = 2 * KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
