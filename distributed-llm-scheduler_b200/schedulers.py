@@ -104,6 +104,14 @@ class BaseScheduler:
         node_list = list(self.nodes.values())
         if not tasks:
             return {}
+        if self.completed_tasks or self.failed_tasks:
+            # A second call after a run: whatever is still pending waits for a task that failed, so the reference's
+            # loop finds nothing ready and returns an empty schedule (schedulers.py:167-174); same here, without a launch.
+            return {}
+        if any(nd.cached_params or nd.completed_tasks for nd in node_list):
+            # (the device starts every node with an empty cache and no completed tasks; available_memory is taken as is)
+            raise ValueError("nodes that already hold cached params or completed tasks are not supported: "
+                             "pass fresh Node objects (their available_memory is honoured)")
         if not node_list:
             # ref: every ready task fails, then nothing was scheduled -> all pending fail (schedulers.py:198-206)
             for tid in list(self.pending_tasks):

@@ -145,3 +145,22 @@ def test_chain_of_half_additions_has_a_closed_form_when_exact():
         down[q < j] -= 0.5
     assert 0.2 < exact.mean() < 0.9 and (up != s).sum() > 1000          # both kinds of case are in the sample
     assert (up[exact] == s[exact]).all() and (down[exact] == x[exact]).all()
+
+
+def test_mirror_scheduler_rejects_state_it_would_ignore():
+    """The device starts every node with an empty cache: nodes that already carry cached params or completed tasks
+    are refused instead of being scheduled as if they were fresh. A scheduler that has run returns the
+    empty schedule on a second call, like the reference's loop that finds nothing ready (ref schedulers.py:167-174)."""
+    from dls_b200.schedulers import GreedyScheduler
+    nd = Node("n1", 4.0)
+    nd.cached_params.add("p1")
+    s = GreedyScheduler([nd])
+    s.add_task(Task("t1", 1.0, 0.1, [], {"p1"}))
+    with pytest.raises(ValueError, match="cached params"):
+        s.schedule()
+    s2 = GreedyScheduler([Node("n1", 4.0)])
+    s2.add_task(Task("t1", 1.0, 0.1, [], {"p1"}))
+    s2.add_task(Task("t2", 1.0, 0.1, ["t1"], {"p2"}))
+    s2.failed_tasks.add("t1")          # as after a run in which t1 failed and t2 stayed pending
+    s2.pending_tasks.discard("t1")
+    assert s2.schedule() == {}
