@@ -554,3 +554,42 @@ def test_failed_tasks_block_their_dependents_at_any_fan_out(oracle_mod, sizes, f
     assert (want.summary["failed"] >= 1).all() and want.summary["pending"].sum() > 0 and want.summary["completed"].sum() > 0
     for path, got in run_both_paths(batch, N.MASK_ALL):
         assert_results_equal(got, want, f"{path} hub DAGs n={sizes}")
+
+
+def test_dense_dags_take_the_unstaged_paths(oracle_mod):
+    """Many dependencies per task (E up to ~8n, in-degrees up to 12, out-degrees in the dozens): the dependency CSR no
+    longer fits the shared-memory bytes the priority kernels stage it in (they then read it from global memory), the
+    depth pass meets tasks with more than three dependencies, failed tasks have more dependents than the marks
+    pipeline fetches ahead — under memory pressure, with private and shared params, against the oracle."""
+    from dls_b200.lowering import LoweredDag
+    rng = np.random.default_rng(77)
+    dags, nodes = [], []
+    for b in range(40):
+        n = int(rng.choice([24, 90, 200, 640]))
+        K = int(rng.choice([2, 5, 8]))
+        preds = [sorted(set(rng.integers(0, i, size=int(rng.integers(0, 13))).tolist())) if i else [] for i in range(n)]
+        pool = 0 if b % 2 == 0 else 6                      # every other instance shares a few params
+        pars, P = [], pool
+        for i in range(n):
+            own = list(range(P, P + int(rng.integers(0, 3))))
+            P += len(own)
+            shared = sorted(set(rng.integers(0, pool, size=int(rng.integers(0, 3))).tolist())) if pool else []
+            pars.append(shared + own)
+        mem = rng.uniform(0.1, 0.5, size=n)
+        npar = np.array([len(p) for p in pars])
+        cap = np.full(K, float((mem + 0.5 * npar).max() + 0.5 * npar.sum() * rng.uniform(0.25, 0.9) / K))
+        dags.append(LoweredDag(
+            names=[f"t{j}" for j in range(n)], param_names=[f"p{j:05d}" for j in range(max(P, 1))],
+            pred_ptr=np.concatenate([[0], np.cumsum([len(p) for p in preds])]).astype(np.uint32),
+            pred_idx=np.asarray([q for p in preds for q in p], np.uint16),
+            par_ptr=np.concatenate([[0], np.cumsum(npar)]).astype(np.uint32),
+            par_idx=np.asarray([q for p in pars for q in p], np.uint16), rank=rng.permutation(n).astype(np.uint16),
+            mem=mem, dur=rng.uniform(0.05, 0.15, size=n)))
+        nodes.append((cap, rng.uniform(0.5, 2.0, size=K)))
+    batch = DagBatch.from_instances(dags, nodes)
+    assert batch.e_total > 4 * batch.nt_inst
+    want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+    assert (want.summary["status"] == 0).all()
+    assert want.summary["failed"].sum() > 0 and want.summary["pending"].sum() > 0 and want.summary["completed"].sum() > 0
+    for path, got in run_both_paths(batch, N.MASK_ALL):
+        assert_results_equal(got, want, f"{path} dense DAGs")
