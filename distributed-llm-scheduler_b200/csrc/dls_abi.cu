@@ -1,7 +1,8 @@
 // dls_abi.cu — the extern "C" entry points declared in include/dls.h.
 //
 // The library never allocates device memory and never synchronises the stream: scratch comes from the
-// caller (dls_workspace_bytes), results go to caller buffers, kernels are enqueued on the caller's stream.
+// caller (dls_workspace_bytes), results go to caller buffers, kernels are enqueued on the caller's stream (one part
+// of the replay path on an auxiliary stream forked from it and joined back into it: see ForkJoin).
 #include <atomic>
 #include <cstdio>
 #include <cstring>
@@ -150,7 +151,7 @@ int validate(const dls_batch_t* b, int algo_mask, bool need_device) {
 }
 
 std::atomic<bool> g_stream_enabled{true};
-std::atomic<bool> g_replay_enabled{true};
+std::atomic<int> g_replay_mode{1};  // 0 off, 1 on (template run beside the Critical run), 2 on, one stream
 
 int cuda_fail(cudaError_t e, const char* why) {
   return fail(DLS_ERR_CUDA, std::string(why ? why : "cuda") + ": " + cudaGetErrorString(e));
@@ -226,7 +227,7 @@ int enqueue_schedule(const dls_batch_t* batch, const dls_result_t* result, int a
 constexpr int kDurationFree = (1 << DLS_ALGO_DFS) | (1 << DLS_ALGO_GREEDY) | (1 << DLS_ALGO_MRU);
 
 bool replay_applies(const dls_batch_t& b, const dls_result_t* r, int algo_mask) {
-  return g_replay_enabled.load() && b.T == 1 && b.B > 1 && b.flags == DLS_F_DUR_PER_INSTANCE && !b.node_off &&
+  return g_replay_mode.load() != 0 && b.T == 1 && b.B > 1 && b.flags == DLS_F_DUR_PER_INSTANCE && !b.node_off &&
          (algo_mask & kDurationFree) && !(r && r->tfin);  // (the timeline extension is made of durations)
 }
 
@@ -267,6 +268,36 @@ TemplateLayout template_layout(const dls_batch_t& b, int tmask, size_t base) {
   return T;
 }
 
+// The replay path's two halves — the one-instance template run of DFS / Greedy / MRU and the per-instance Critical
+// run — touch disjoint scratch and disjoint outputs, and the first is a handful of single-warp kernels whose time is
+// pure latency (GPT-2: 0.36 ms of a 2.2 ms step; the 9,986-task DAG: 10.6 of 22 ms). They are therefore enqueued side
+// by side: the template run on an auxiliary stream forked from the caller's stream by an event and joined back by
+// another before the replay kernel, so that everything is still ordered on the caller's stream (and capturable).
+// One auxiliary stream and two events per device, created on first use and kept; calls that use them are serialised
+// while they ENQUEUE (the events are re-recorded per call). dls_schedule_batch_static never comes here.
+struct ForkJoin {
+  std::mutex mu;
+  cudaStream_t aux = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool tried = false, ok = false;
+};
+
+ForkJoin* fork_join_for_current_device() {
+  static ForkJoin table[kMaxDevices];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+  ForkJoin& f = table[dev];
+  std::lock_guard<std::mutex> lock(f.mu);
+  if (!f.tried) {
+    f.tried = true;
+    f.ok = cudaStreamCreateWithFlags(&f.aux, cudaStreamNonBlocking) == cudaSuccess &&
+           cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming) == cudaSuccess;
+    if (!f.ok) (void)cudaGetLastError();  // (the calls then stay on one stream)
+  }
+  return f.ok ? &f : nullptr;
+}
+
 int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, void* workspace, size_t ws_bytes,
                  void* cuda_stream, bool clear_status, bool allow_replay) {
   dls::LaunchCtx ctx;
@@ -290,7 +321,22 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
       tr.peak = result->peak ? reinterpret_cast<double*>(p + T.off_peak) : nullptr;
       tr.cached = result->cached ? reinterpret_cast<uint32_t*>(p + T.off_cached) : nullptr;
       tr.tfin = nullptr;
-      rc = enqueue_schedule(&tb, &tr, tmask, p + T.off_ws, T.ws_bytes, ctx, true);
+      ForkJoin* fj = (cmask && g_replay_mode.load() == 1) ? fork_join_for_current_device() : nullptr;
+      std::unique_lock<std::mutex> fj_lock;
+      dls::LaunchCtx tctx = ctx;  // the template run's launches
+      if (fj) {
+        fj_lock = std::unique_lock<std::mutex>(fj->mu);
+        if (cudaEventRecord(fj->fork, ctx.st) == cudaSuccess && cudaStreamWaitEvent(fj->aux, fj->fork, 0) == cudaSuccess) {
+          tctx.st = fj->aux;
+        } else {
+          (void)cudaGetLastError();
+          fj = nullptr;
+          fj_lock.unlock();
+        }
+      }
+      rc = enqueue_schedule(&tb, &tr, tmask, p + T.off_ws, T.ws_bytes, tctx, true);
+      ctx.launches = tctx.launches;
+      if (rc != DLS_OK) ctx.why = tctx.why;
       if (rc == DLS_OK && cmask) {
         // Critical for every instance, written to its own slot of the caller's arrays
         int cslot = 0;
@@ -305,6 +351,12 @@ int run_schedule(const dls_batch_t* batch, dls_result_t* result, int algo_mask, 
         if (cr.peak) cr.peak += (int64_t)cslot * batch->nk_inst;
         if (cr.cached) cr.cached += (int64_t)cslot * batch->np_inst;
         rc = enqueue_schedule(batch, &cr, cmask, workspace, main_bytes, ctx, true);
+      }
+      if (fj) {  // join, whatever happened above: the caller's stream must not run ahead of the auxiliary one
+        cudaError_t e = cudaEventRecord(fj->join, fj->aux);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx.st, fj->join, 0);
+        if (e != cudaSuccess && rc == DLS_OK) rc = cuda_fail(e, "joining the template run's stream");
+        fj_lock.unlock();
       }
       if (rc == DLS_OK) {
         dls::ReplayArgs a;
@@ -483,7 +535,7 @@ int dls_repeat_rank_row(const uint16_t* row, int32_t n, int32_t T, uint16_t* out
  * instance, 1 (default) lets qualifying batches take the thread-per-DAG streamed path. Returns the old value. */
 int dls_set_stream_path(int enabled) { return g_stream_enabled.exchange(enabled != 0) ? 1 : 0; }
 
-int dls_set_replay_path(int enabled) { return g_replay_enabled.exchange(enabled != 0) ? 1 : 0; }
+int dls_set_replay_path(int mode) { return g_replay_mode.exchange(mode == 0 ? 0 : mode == 2 ? 2 : 1); }
 
 int dls_priorities(const dls_batch_t* batch, dls_prio_t* prio, void* workspace, size_t workspace_bytes, void* cuda_stream) {
   int rc = validate(batch, DLS_MASK_ALL, true);

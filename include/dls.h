@@ -269,9 +269,13 @@ int dls_set_stream_path(int enabled);
  * per-instance durations only (flags == DLS_F_DUR_PER_INSTANCE) normally has DFS, Greedy and MRU scheduled once, on
  * instance 0 — their decisions never read a duration (schedulers.py:154-208,244-296,444-525) — and every instance's
  * node finish times and makespan replayed along that one assignment sequence (simulation.py:261-271); Critical still
- * runs per instance. 0 schedules every instance with every algorithm instead; any other value restores the default.
- * Returns the previous setting. */
-int dls_set_replay_path(int enabled);
+ * runs per instance. The one-instance run is enqueued on an auxiliary stream of the library (one per device, created
+ * on first use), forked from the caller's stream by an event and joined back into it before the replay, so that it
+ * runs beside the Critical kernels; all of the call's work is still ordered on the caller's stream, and the call can
+ * be captured into a graph. mode 0 schedules every instance with every algorithm instead; mode 2 keeps the replay
+ * but enqueues everything on the caller's stream alone; any other value restores the default (1).
+ * Returns the previous mode. dls_schedule_batch_static does not use this path. */
+int dls_set_replay_path(int mode);
 
 /* Number of kernel launches the library has enqueued since load (for bench accounting). */
 int64_t dls_launch_count(void);

@@ -4,6 +4,7 @@ seeded inputs. Bar: bit-exact task order, node assignment, verdicts, fp64 node s
 (north star asks 1e-6 relative on makespan; assert_* checks both)."""
 import numpy as np
 import pytest
+import torch
 
 import golden_io
 from common import assert_matches_expected, assert_results_equal, run_both_paths
@@ -161,6 +162,21 @@ def test_one_schedule_for_duration_only_batches(oracle_mod):
         finally:
             lib.dls_set_replay_path(old)
         assert_results_equal(got := schedule_batch(batch, N.MASK_ALL, peak=True, cached=True).host(), plain, "replay vs every instance")
+        # the template run beside the Critical run (auxiliary stream, the default) and behind it (one stream)
+        assert lib.dls_set_replay_path(2) == 1
+        try:
+            one_stream = schedule_batch(batch, N.MASK_ALL, peak=True, cached=True).host()
+        finally:
+            assert lib.dls_set_replay_path(1) == 2
+        assert_results_equal(one_stream, want, "replayed on one stream")
+        # ... and on a stream of the caller's, again and again into the same buffers (fork / join per call)
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            res = schedule_batch(batch, N.MASK_ALL, peak=True, cached=True)
+            for _ in range(4):
+                res = schedule_batch(batch, N.MASK_ALL, workspace=res.workspace, result=res)
+        st.synchronize()
+        assert_results_equal(res.host(), want, "replayed repeatedly on a side stream")
     # memory per instance as well: decisions differ between instances, nothing is replayed
     dag, cap, spd = cases[1]
     rng = np.random.default_rng(1)
