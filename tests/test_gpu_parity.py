@@ -609,3 +609,27 @@ def test_dense_dags_take_the_unstaged_paths(oracle_mod):
     assert want.summary["failed"].sum() > 0 and want.summary["pending"].sum() > 0 and want.summary["completed"].sum() > 0
     for path, got in run_both_paths(batch, N.MASK_ALL):
         assert_results_equal(got, want, f"{path} dense DAGs")
+
+
+def test_scheduling_call_can_be_captured_into_a_cuda_graph(oracle_mod):
+    """dls_schedule_batch only enqueues work on the caller's stream (the replay path forks an auxiliary stream from it
+    by an event and joins it back): after one ordinary call it can be captured into a CUDA graph and replayed, for an
+    instance-per-topology batch (thread-per-DAG kernels) and for a duration-only batch (template run + replay). The
+    result buffers are cleared between replays; what the graph writes must be the oracle's result every time."""
+    from dls_b200.batch import DeviceBatch
+    base = [c for c in golden_io.load("cfg3_gpt2.npz") if c.label == "gpt2|8laptops"][0]
+    shared = DagBatch.shared_topology(base.dag, base.cap * 0.5, base.spd, 64, dur=perturbed_durations(base.dag, 64, 0.1, seed=9))
+    for batch in (random_dag_batch(96, 200, 8, 0.8, seed=5), shared):
+        want = oracle_mod.schedule_batch(batch, N.MASK_ALL, nthreads=8)
+        dev = DeviceBatch(batch, torch.device("cuda", 0))
+        res = schedule_batch(dev, N.MASK_ALL)           # ordinary call first: function attributes, auxiliary stream
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            schedule_batch(dev, N.MASK_ALL, workspace=res.workspace, result=res)
+        for _ in range(3):
+            for t in (res.node_of, res.seq_pos, res.summary, res.fin, res.cnt, res.avail):
+                t.zero_()
+            g.replay()
+            torch.cuda.synchronize()
+            assert_results_equal(res.host(), want, "graph replay")
