@@ -23,18 +23,23 @@ __device__ __forceinline__ uint64_t mix64(uint64_t x) {  // splitmix64 finaliser
   return x ^ (x >> 31);
 }
 
-// uniform double in [0, 1) for (instance, task, draw)
+// uniform double in [0, 1) for (instance, task, draw): the draws of one task share the hash of (seed, instance, task)
+__device__ __forceinline__ uint64_t task_key(uint64_t seed, uint32_t inst, uint32_t task) {
+  return mix64(seed ^ ((uint64_t)inst << 32 | task));
+}
+__device__ __forceinline__ double u01(uint64_t key, uint32_t draw) {
+  return (double)(mix64(key + draw) >> 11) * (1.0 / 9007199254740992.0);
+}
 __device__ __forceinline__ double u01(uint64_t seed, uint32_t inst, uint32_t task, uint32_t draw) {
-  const uint64_t h = mix64(mix64(seed ^ ((uint64_t)inst << 32 | task)) + draw);
-  return (double)(h >> 11) * (1.0 / 9007199254740992.0);
+  return u01(task_key(seed, inst, task), draw);
 }
 
-__device__ __forceinline__ int draw_ndeps(const dls_gen_t& g, uint32_t inst, int i) {
+__device__ __forceinline__ int draw_ndeps(const dls_gen_t& g, uint64_t key, int i) {
   const int hi = min(g.max_deps, i);  // random.randint(0, min(max_deps, i))
-  return min((int)(u01(g.seed, inst, i, 0) * (double)(hi + 1)), hi);
+  return min((int)(u01(key, 0) * (double)(hi + 1)), hi);
 }
-__device__ __forceinline__ int draw_nparams(const dls_gen_t& g, uint32_t inst, int i) {
-  return u01(g.seed, inst, i, 1) < 0.5 ? 1 : 2;  // random.randint(1, 2)
+__device__ __forceinline__ int draw_nparams(uint64_t key) {
+  return u01(key, 1) < 0.5 ? 1 : 2;  // random.randint(1, 2)
 }
 
 __global__ void __launch_bounds__(kGenThreads) gen_count_kernel(dls_gen_t g, int32_t* e_count, int32_t* r_count) {
@@ -42,8 +47,9 @@ __global__ void __launch_bounds__(kGenThreads) gen_count_kernel(dls_gen_t g, int
   const uint32_t inst = blockIdx.x;
   int e = 0, r = 0;
   for (int i = threadIdx.x; i < g.n; i += blockDim.x) {
-    e += draw_ndeps(g, inst, i);
-    r += draw_nparams(g, inst, i);
+    const uint64_t key = task_key(g.seed, inst, i);
+    e += draw_ndeps(g, key, i);
+    r += draw_nparams(key);
   }
   for (int off = 16; off > 0; off >>= 1) {
     e += __shfl_xor_sync(DLS_FULL_MASK, e, off);
@@ -84,13 +90,14 @@ __global__ void __launch_bounds__(kGenThreads) gen_fill_kernel(dls_gen_t g, dls_
   __syncthreads();
   double need_max = 0.0;
   for (int i = tid; i < n; i += blockDim.x) {
-    const int nd = draw_ndeps(g, inst, i), np = draw_nparams(g, inst, i);
+    const uint64_t key = task_key(g.seed, inst, i);
+    const int nd = draw_ndeps(g, key, i), np = draw_nparams(key);
     s_e[i] = nd;
     s_r[i] = np;
     s_present[g.param_pos[2 * i]] = 1;
     if (np == 2) s_present[g.param_pos[2 * i + 1]] = 1;
-    const double m = 0.1 + (0.5 - 0.1) * u01(g.seed, inst, i, 2);    // random.uniform(0.1, 0.5)
-    const double c = 0.05 + (0.15 - 0.05) * u01(g.seed, inst, i, 3); // random.uniform(0.05, 0.15)
+    const double m = 0.1 + (0.5 - 0.1) * u01(key, 2);    // random.uniform(0.1, 0.5)
+    const double c = 0.05 + (0.15 - 0.05) * u01(key, 3); // random.uniform(0.05, 0.15)
     mem[i] = m;
     dur[i] = c;
     rank[i] = g.rank[i];
@@ -105,22 +112,23 @@ __global__ void __launch_bounds__(kGenThreads) gen_fill_kernel(dls_gen_t g, dls_
   for (int i = tid; i < n; i += blockDim.x) {
     // ordered sample without replacement of nd values from range(i): draw r_j in [0, i-j), skip earlier picks
     const int nd = (int)(s_e[i + 1] - s_e[i]);
-    int picks[8];
+    const uint64_t key = task_key(g.seed, inst, i);
+    int sorted[8];  // the picks so far in ascending order (registers: every index below is a compile-time constant)
+#pragma unroll
+    for (int a = 0; a < 8; ++a) sorted[a] = 0x7fffffff;
     for (int j = 0; j < nd; ++j) {
       const int span = i - j;
-      int rj = min((int)(u01(g.seed, inst, i, 8 + j) * (double)span), span - 1);
-      // earlier picks in ascending order
-      int sorted[8];
-      for (int a = 0; a < j; ++a) sorted[a] = picks[a];
-      for (int a = 1; a < j; ++a) {
-        const int key = sorted[a];
-        int bpos = a - 1;
-        while (bpos >= 0 && sorted[bpos] > key) { sorted[bpos + 1] = sorted[bpos]; --bpos; }
-        sorted[bpos + 1] = key;
-      }
-      for (int a = 0; a < j; ++a) rj += rj >= sorted[a];
-      picks[j] = rj;
+      int rj = min((int)(u01(key, 8 + j) * (double)span), span - 1);
+#pragma unroll
+      for (int a = 0; a < 8; ++a) rj += (a < j) && (rj >= sorted[a]);
       pred_idx[s_e[i] + j] = (uint16_t)rj;
+      int carry = rj;  // insert: every slot keeps the smaller of (its value, what is carried), the larger moves on
+#pragma unroll
+      for (int a = 0; a < 8; ++a) {
+        const int lo = min(sorted[a], carry), hi = max(sorted[a], carry);
+        sorted[a] = lo;
+        carry = hi;
+      }
     }
     const int np = (int)(s_r[i + 1] - s_r[i]);
     const uint32_t id0 = s_present[g.param_pos[2 * i]];
