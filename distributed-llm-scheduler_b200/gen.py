@@ -347,10 +347,14 @@ def random_dag_batch_device(B: int, n: int, K: int = 8, regime: float = 0.9, see
         zero = torch.zeros(1, dtype=torch.int64, device=dev)
         pred_off = torch.cat([zero, torch.cumsum(e_cnt.to(torch.int64), 0)])
         par_off = torch.cat([zero, torch.cumsum(r_cnt.to(torch.int64), 0)])
-        task_off = torch.arange(B + 1, dtype=torch.int64, device=dev) * n
-        node_off = torch.arange(B + 1, dtype=torch.int64, device=dev) * K
-        e_total, r_total = int(pred_off[-1].item()), int(par_off[-1].item())
-        e_max, r_max = int(e_cnt.max().item()), int(r_cnt.max().item())
+        task_off_h = np.arange(B + 1, dtype=np.int64) * n
+        node_off_h = np.arange(B + 1, dtype=np.int64) * K
+        task_off = torch.from_numpy(task_off_h).to(dev, non_blocking=True)
+        node_off = torch.from_numpy(node_off_h).to(dev, non_blocking=True)
+        # ONE device-to-host read for everything the host needs to size the arrays: both offset tables and the two maxima
+        head = torch.cat([pred_off, par_off, e_cnt.max().to(torch.int64).reshape(1), r_cnt.max().to(torch.int64).reshape(1)]).cpu().numpy()
+        pred_off_h, par_off_h = head[:B + 1].copy(), head[B + 1:2 * B + 2].copy()
+        e_total, r_total, e_max, r_max = int(pred_off_h[-1]), int(par_off_h[-1]), int(head[-2]), int(head[-1])
         t = {
             "task_off": task_off, "pred_off": pred_off, "par_off": par_off, "pid_off": par_off, "node_off": node_off,
             "pred_ptr": torch.empty(B * (n + 1), dtype=torch.int32, device=dev),
@@ -365,9 +369,9 @@ def random_dag_batch_device(B: int, n: int, K: int = 8, regime: float = 0.9, see
         }
         meta = DagBatch(
             B=B, T=B, n_max=n, K_max=K, P_max=r_max, E_max=e_max, R_max=r_max, flags=0,
-            task_off=task_off.cpu().numpy(), pred_off=pred_off.cpu().numpy(), par_off=par_off.cpu().numpy(),
-            pid_off=par_off.cpu().numpy(), pred_ptr=None, pred_idx=None, par_ptr=None, par_idx=None, rank=None,
-            mem=None, dur=None, node_off=node_off.cpu().numpy(), cap=None, spd=None, dags=None)
+            task_off=task_off_h, pred_off=pred_off_h, par_off=par_off_h,
+            pid_off=par_off_h.copy(), pred_ptr=None, pred_idx=None, par_ptr=None, par_idx=None, rank=None,
+            mem=None, dur=None, node_off=node_off_h, cap=None, spd=None, dags=None)
         db = DeviceBatch.from_tensors(meta, t, dev)
         N.check(lib.dls_generate_fill(C.byref(g), C.byref(db.struct), stream))
         db._keep = (rank_d, ppos_d)
