@@ -92,8 +92,8 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
     strided_for<8>(n, [&](int i) {
       const uint32_t q0 = __ldg(v.par_ptr + i), q1 = __ldg(v.par_ptr + i + 1);
       if (q0 > q1) bad = 1;
-      if (__ldg(v.rank + i) >= n) bad = 1;
     });
+    for_each_u16(v.rank, n, [&](int, int r) { bad |= r >= n; });
     if (stage) {
       if (tid < 32) mbar_wait(&s_bar, 0);  // one warp polls; the others sleep at the barrier (polling took 6 % of the issue slots)
       __syncthreads();  // (also: the few edge elements were copied by threads)
@@ -105,9 +105,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
     for (int e = tid; e < (int)v.E; e += blockDim.x)
       if (pidx[e] >= n) bad = 1;
     if (check_params) {  // (with the streamed path on, param_class_kernel checks them as it reads them anyway)
-      strided_for<8>((int)v.R, [&](int e) {
-        if (__ldg(v.par_idx + e) >= v.P) bad = 1;
-      });
+      for_each_u16(v.par_idx, (int)v.R, [&](int, int p) { bad |= p >= v.P; });
     }
     if (__syncthreads_or(bad)) {
       if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
@@ -267,12 +265,12 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   }
   // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
   __syncthreads();  // the staged CSR (aliased with s_hist / s_ord / s_tmp) is dead from here on
-  strided_for<8>(n, [&](int i) { s_ord[__ldg(v.rank + i)] = (uint16_t)i; });
+  for_each_u16(v.rank, n, [&](int i, int r) { s_ord[r] = (uint16_t)i; });
   __syncthreads();
   {  // rank[] must be a permutation: a repeated value would leave a position of every order unwritten
     // (a bitmap filled with atomicOr while the ranks are first read was measured slower than this second look)
     int dup = 0;
-    strided_for<8>(n, [&](int i) { dup |= s_ord[__ldg(v.rank + i)] != i; });
+    for_each_u16(v.rank, n, [&](int i, int r) { dup |= s_ord[r] != i; });
     if (__syncthreads_or(dup)) {
       if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
       return;
@@ -334,8 +332,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   uint32_t* s_rc = reinterpret_cast<uint32_t*>(smem_raw);             // [P+2]
   uint16_t* g_sid = w.par_sid + b.pid_off[t];
   int bad = 0;
-  strided_for<8>((int)v.R, [&](int e) {
-    const int p = __ldg(v.par_idx + e);
+  for_each_u16(v.par_idx, (int)v.R, [&](int e, int p) {
     if (p < P) s_rc[p] = (uint32_t)e;
     else bad = 1;  // never trust an index that addresses shared memory
   });
@@ -345,7 +342,7 @@ __global__ void __launch_bounds__(kThreadsP) param_class_kernel(dls_batch_t b, W
   }
   if (tid == 0) w.topo_status[t] = DLS_ST_OK;
   int twice = 0;
-  strided_for<8>((int)v.R, [&](int e) { twice |= s_rc[__ldg(v.par_idx + e)] != (uint32_t)e; });
+  for_each_u16(v.par_idx, (int)v.R, [&](int e, int p) { twice |= s_rc[p] != (uint32_t)e; });
   if (!__syncthreads_or(twice)) return;  // nshared[t] = 0 stands; par_sid is not read for such a DAG
   for (int p = tid; p < P + 2; p += blockDim.x) s_rc[p] = 0;
   __syncthreads();
