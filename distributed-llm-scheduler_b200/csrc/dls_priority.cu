@@ -44,16 +44,16 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   const int n_al = (n + 3) & ~3;
   auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
   unsigned char* r_cnt = smem_raw;                                      // every region 16-byte aligned
-  unsigned char* r_depth = r_cnt + up16((size_t)(n + 2) * 4);
-  unsigned char* r_hist = r_depth + up16((size_t)n_al * 2);
+  unsigned char* r_hist = r_cnt + up16((size_t)(n + 2) * 4);
   unsigned char* r_ord = r_hist + staged_bytes((size_t)(n + 2) * 4);
+  unsigned char* r_tmp = r_ord + up16((size_t)n_al * 4);
   uint32_t* s_cnt = reinterpret_cast<uint32_t*>(r_cnt);                 // [n+2]
-  uint16_t* s_depth = reinterpret_cast<uint16_t*>(r_depth);             // [n_al]
   uint32_t* s_hist = reinterpret_cast<uint32_t*>(r_hist);               // [n+2]
-  uint16_t* s_ord = reinterpret_cast<uint16_t*>(r_ord);                 // [n_al]
-  uint16_t* s_tmp = s_ord + n_al;                                       // [n_al]
+  uint32_t* s_ord = reinterpret_cast<uint32_t*>(r_ord);                 // [n_al] order elements: task | depth << 16
+  uint32_t* s_tmp = reinterpret_cast<uint32_t*>(r_tmp);                 // [n_al] the sorts' second buffer ...
+  uint16_t* s_depth = reinterpret_cast<uint16_t*>(r_tmp);               // [n_al] ... after the depths moved into the elements
   // Until the orders are built (which is when s_hist / s_ord / s_tmp are first needed) the same bytes hold a copy of
-  // the dependency CSR: row pointers over s_hist, indices over s_ord + s_tmp (if they fit: E <= 2 n). The depth pass
+  // the dependency CSR: row pointers over s_hist, indices over s_ord (if they fit: E <= 2 n). The depth pass
   // walks the CSR with dependent loads, one 32-task chunk after the other; from global memory that chain cost 48 %
   // of this kernel (measured with clock64 per phase, round 1e). The copy is made by the bulk-copy engine
   // (dls_tma.cuh) while the threads check the param row pointers and the ranks, which stay in global memory.
@@ -265,12 +265,14 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   }
   // ---- pi order: s_ord[r] = task at position r of list(pending_tasks) ----
   __syncthreads();  // the staged CSR (aliased with s_hist / s_ord / s_tmp) is dead from here on
-  for_each_u16(v.rank, n, [&](int i, int r) { s_ord[r] = (uint16_t)i; });
-  __syncthreads();
+  // Each element carries its task's depth along: the two sorts by depth then read their key out of the element instead
+  // of gathering it (those gathers were 9 % of this kernel's shared-memory wavefronts at 3x the conflict-free count).
+  for_each_u16(v.rank, n, [&](int i, int r) { s_ord[r] = (uint32_t)i | ((uint32_t)s_depth[i] << 16); });
+  __syncthreads();  // (from here on s_depth's bytes are s_tmp)
   {  // rank[] must be a permutation: a repeated value would leave a position of every order unwritten
     // (a bitmap filled with atomicOr while the ranks are first read was measured slower than this second look)
     int dup = 0;
-    for_each_u16(v.rank, n, [&](int i, int r) { dup |= s_ord[r] != i; });
+    for_each_u16(v.rank, n, [&](int i, int r) { dup |= (s_ord[r] & 0xffffu) != (uint32_t)i; });
     if (__syncthreads_or(dup)) {
       if (tid == 0) w.topo_status[t] = DLS_ST_BAD_TOPOLOGY;
       return;
@@ -278,16 +280,19 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
   }
   const int maxd = s_maxd, maxdeg = s_maxdeg;
   // DFS / Greedy: (depth asc, rank asc)  — ref schedulers.py:171-177 (the depth sort is a no-op inside a round)
-  auto by_depth = [&](int i) { return (uint32_t)s_depth[i]; };
+  auto by_depth = [](uint32_t e) { return e >> 16; };
   stable_counting_sort(s_ord, s_tmp, n, maxd + 1, by_depth, s_hist, n + 2, s_part, w.lvl_end + v.t_topo);
-  for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = s_tmp[q];
+  for (int q = tid; q < n; q += blockDim.x) w.order_dg[v.t_topo + q] = (uint16_t)s_tmp[q];
   __syncthreads();
   if (want_mru) {
     // MRU: (depth asc, urgency desc, ready-index asc) — ref schedulers.py:462-475. LSD: urgency first, then depth.
     // out-degree of task i: after the fill above s_cnt[i] is the END of i's dependents in the reverse CSR
-    auto deg_of = [&](int i) { return min(s_cnt[i] - (i ? s_cnt[i - 1] : 0u), 65535u); };
+    auto deg_of = [&](uint32_t e) {
+      const uint32_t i = e & 0xffffu;
+      return min(s_cnt[i] - (i ? s_cnt[i - 1] : 0u), 65535u);
+    };
     // (one pass on the combined key (depth, degree) needs ~200 x 4 counters and was measured slower than these two)
-    auto by_degree = [&](int i) { return (uint32_t)maxdeg - deg_of(i); };
+    auto by_degree = [&](uint32_t e) { return (uint32_t)maxdeg - deg_of(e); };
     if (maxdeg + 2 <= n + 2) {
       stable_counting_sort(s_ord, s_tmp, n, maxdeg + 1, by_degree, s_hist, n + 2, s_part);
     } else {
@@ -305,7 +310,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_TOPO_MINB) priority_topology_ke
       __syncthreads();
     }
     stable_counting_sort(s_tmp, s_ord, n, maxd + 1, by_depth, s_hist, n + 2, s_part);
-    for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = s_ord[q];
+    for (int q = tid; q < n; q += blockDim.x) w.order_mru[v.t_topo + q] = (uint16_t)s_ord[q];
   }
 }
 
@@ -543,7 +548,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
 size_t priority_smem_topo(int n_max, int /*E_max*/) {  // the staged dependency CSR aliases the sort scratch
   size_t n = (size_t)n_max, n_al = (n + 3) & ~(size_t)3;
   auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
-  return up16((n + 2) * 4) + up16(n_al * 2) + staged_bytes((n + 2) * 4) + up16(n_al * 4);
+  return up16((n + 2) * 4) + staged_bytes((n + 2) * 4) + 2 * up16(n_al * 4);
 }
 
 size_t priority_smem_param(int /*n_max*/, int P_max) {

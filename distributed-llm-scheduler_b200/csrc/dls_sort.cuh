@@ -11,14 +11,16 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
   return m;
 }
 
-// dst = src stably sorted by key(task) ascending, key in [0, nkeys). s_hist has hist_cap words.
+// dst = src stably sorted by key(element) ascending, key in [0, nkeys). s_hist has hist_cap words. Elements are
+// 32-bit words that carry whatever the later passes sort by (the topology kernel packs task | depth << 16, so that a
+// sort by depth looks nothing up).
 // When nkeys * (warps per CTA) counters fit, every warp owns a contiguous chunk of src: it counts its keys, one
 // block-wide scan over the [key][warp] table turns the counts into start offsets, and each warp then places its own
 // chunk, 32 elements at a time, with __match_any giving each lane its rank among equal keys (stable). Otherwise the
 // histogram is shared and warp 0 places everything.
 // `ends_out` (optional, global memory): ends_out[k] = position after the last element with key k.
 template <class KeyF>
-__device__ inline void stable_counting_sort(const uint16_t* src, uint16_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
+__device__ inline void stable_counting_sort(const uint32_t* src, uint32_t* dst, int n, int nkeys, KeyF key, uint32_t* s_hist,
                                      int hist_cap, uint32_t* s_part, uint16_t* ends_out = nullptr) {
   const int nwarp = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool split = nkeys * nwarp + 1 <= hist_cap;
@@ -40,11 +42,11 @@ __device__ inline void stable_counting_sort(const uint16_t* src, uint16_t* dst, 
       const bool valid = q < hi;
       const unsigned vm = __ballot_sync(DLS_FULL_MASK, valid);
       if (valid) {
-        const int i = src[q];
+        const uint32_t i = src[q];
         const uint32_t k = key(i) * stride + col;
         const unsigned peers = __match_any_sync(vm, k);
         const uint32_t pos = s_hist[k] + __popc(peers & lanemask_lt());
-        dst[pos] = (uint16_t)i;
+        dst[pos] = i;
         __syncwarp(vm);
         if (lane == __ffs(peers) - 1) s_hist[k] += __popc(peers);
         __syncwarp(vm);
