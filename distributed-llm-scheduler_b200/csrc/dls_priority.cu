@@ -492,8 +492,7 @@ __global__ void __launch_bounds__(kThreadsP, DLS_CRIT_MINB) priority_critical_ke
     __syncthreads();  // every warp has read the level starts (maxd) before the histogram reuses them
     for (int k = tid; k <= ngroups; k += blockDim.x) s_hist[k] = 0;
     __syncthreads();
-    for (int q = tid; q < n; q += blockDim.x) {
-      const int i = s_ord[q];
+    for (int i = tid; i < n; i += blockDim.x) {  // (in task order: the count does not care, and the reads do not scatter)
       const int g = group_of(s_depth[i], s_up[i]);
       s_depth[i] = (uint16_t)g;  // the depth is not needed again: from here on this array holds the task's group
       atomicAdd(&s_hist[g], 1u);
