@@ -45,6 +45,9 @@ constexpr int kTPBM = 64;       // ... of the MRU kernel (measured r1e: one-warp
 #else
 #define DLS_S_BOUNDS(tpb) __launch_bounds__(tpb, DLS_S_MINB)
 #endif
+#ifndef DLS_BUILD_U
+#define DLS_BUILD_U 4  // positions per thread whose order loads are in flight together (2: 2.17 ms, 4: 2.12 ms)
+#endif
 constexpr int kBuildThreads = 256;   // measured r1c: 128 -> 7.6 ms, 256 -> 5.7 ms per 131k instances
 constexpr int kBitmapWordsMax = 64;  // mark bits in shared memory up to 2048 tasks per DAG; beyond, mark bytes in HBM
 
@@ -127,7 +130,7 @@ __global__ void __launch_bounds__(kBuildThreads) stream_build_kernel(dls_batch_t
     });
     __syncthreads();
     // position t of all the orders in one iteration: three independent gathers per thread
-    strided_for<2>(n, [&](int t) {
+    strided_for<DLS_BUILD_U>(n, [&](int t) {
 #pragma unroll
       for (int kind = 0; kind < 3; ++kind) {
         if (!use[kind]) continue;
