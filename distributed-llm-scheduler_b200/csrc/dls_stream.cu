@@ -387,9 +387,10 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
                                                        int twin_mode, int twin_slot, int bm_words) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  // slab layout per warp: doubles fin[KMAX], spd[KMAX] (+ amin[KMAX]); words smask[kSharedCap/4], cnt[KMAX],
+  // slab layout per warp: doubles fin[KMAX], spd[KMAX] (+ amin[KMAX]) (+ avail[KMAX]); words smask[kSharedCap/4], cnt[KMAX],
   // mark-bits[bm_words]
-  constexpr int kD = (PEAK ? 3 : 2) * KMAX;
+  constexpr bool kAvSlab = ALGO == DLS_ALGO_CRITICAL;  // available memory in the slab (see `avail` below)
+  constexpr int kD = ((PEAK ? 3 : 2) + (kAvSlab ? 1 : 0)) * KMAX;
   const int kW = kSharedCap / 4 + KMAX + bm_words;
   const size_t warp_bytes = (size_t)kD * 32 * 8 + (size_t)kW * 32 * 4;
   Slab sl;
@@ -397,6 +398,7 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
   sl.u = reinterpret_cast<uint32_t*>(smem_raw + wib * warp_bytes + (size_t)kD * 32 * 8);
   sl.lane = lane;
   constexpr int FIN = 0, SPD = KMAX, AMIN = 2 * KMAX, SMASK = 0, CNT = kSharedCap / 4, BM = kSharedCap / 4 + KMAX;
+  constexpr int AV = (PEAK ? 3 : 2) * KMAX;  // available memory per node
 
   const int inst = blockIdx.x * kTPB + threadIdx.x;
   const bool have = inst < b.B;
@@ -437,7 +439,11 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
   blocked.in_smem = bm_words > 0;
   blocked.bytes = r.node_of + (int64_t)slot * b.nt_inst + v.t_inst;
 
-  // Node state. avail[k] of a node that does not exist is -inf: it never fits and never wins a max.
+  // Node state. avail[k] of a node that does not exist is -inf: it never fits and never wins a max. For Critical it
+  // lives in the slab and is copied into registers for the duration of a step: the chosen node — found by its speed
+  // rank, not by a scan over avail — is then ONE load and ONE store with a run-time index instead of two
+  // compare-and-select chains over the nodes (1.57 -> 1.49 ms). DFS / Greedy find the node BY that scan and keep avail
+  // in registers (in the slab: 1.64 -> 1.63 ms with peak tracking, 1.52 -> 1.63 ms without, where it costs a CTA).
   double avail[KMAX];
   // Critical: nodes ranked by (speed desc, index asc) once; key = rank*KMAX + k, nodes with speed <= 0 never chosen
   // ("node.compute_speed > best_speed" with best_speed = 0, ref schedulers.py:353-358).
@@ -446,6 +452,7 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
   for (int k = 0; k < KMAX; ++k) {
     const bool on = elig && k < K;
     avail[k] = on ? v.cap[k] : -INFINITY;
+    if constexpr (kAvSlab) sl.f(AV + k) = avail[k];
     const double sp = on ? v.spd[k] : 1.0;
     sl.f(FIN + k) = 0.0;
     sl.f(SPD + k) = sp;
@@ -514,6 +521,10 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
           any_ready = true;
           int best = -1, lbest = npriv;
           double a = 0.0;  // available memory of the chosen node
+          if constexpr (kAvSlab) {
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) avail[k] = sl.f(AV + k);
+          }
           if (!has_shared) {
             // Every param of the task is private: params_to_load and hence the requirement are the same on every
             // node, so "fits" is avail >= need and the best fitting node is the first maximum, if that one fits.
@@ -522,7 +533,7 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
               int bk = 0x7fffffff;
 #pragma unroll
               for (int k = 0; k < KMAX; ++k) bk = min(bk, need <= avail[k] ? ckey[k] : 0x7fffffff);
-              if (bk != 0x7fffffff) { best = bk & (KMAX - 1); a = pick<KMAX>(avail, best); }
+              if (bk != 0x7fffffff) { best = bk & (KMAX - 1); a = sl.f(AV + best); }
             } else {
               // DFS: strict '>' from max_memory = -1 (ref :186-192). Greedy: first fitting node, then strictly more
               // available memory among equal params_to_load (ref :267-281) == first maximum among fitting nodes.
@@ -562,7 +573,7 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
               }
             }
             a = bv;
-            if constexpr (ALGO == DLS_ALGO_CRITICAL) { if (best >= 0) a = pick<KMAX>(avail, best); }
+            if constexpr (ALGO == DLS_ALGO_CRITICAL) { if (best >= 0) a = sl.f(AV + best); }
           }
           if (best >= 0) {
             if (lbest > 0) a = __dsub_rn(a, 0.5);  // node.available_memory -= 0.5 per loaded param (ref :89)
@@ -571,8 +582,12 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
             a = __dsub_rn(a, m);                   // ref :95
             if constexpr (PEAK) sl.f(AMIN + best) = fmin(sl.f(AMIN + best), a);
             a = __dadd_rn(a, m);                   // complete_task frees it again (ref :126)
+            if constexpr (kAvSlab) {
+              sl.f(AV + best) = a;
+            } else {
 #pragma unroll
-            for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
+              for (int k = 0; k < KMAX; ++k) avail[k] = (k == best) ? a : avail[k];
+            }
             sl.f(FIN + best) = __dadd_rn(sl.f(FIN + best), __ddiv_rn(c, sl.f(SPD + best)));  // ref simulation.py:261-264
             sl.w(CNT + best) += 1;
             to.misses += lbest;
@@ -600,6 +615,10 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
       if (any_ready && !any_assigned) to.fail_rest = true;
       else if (any_ready && to.completed + to.failed < n) ++to.rounds;  // one more iteration finds nothing ready
     }
+    if constexpr (kAvSlab) {
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) avail[k] = sl.f(AV + k);
+    }
     finish_thread<KMAX>(b, r, w, slot, inst, v, avail, sl, FIN, CNT, PEAK ? AMIN : -1, to);
     if (twin_ok) finish_thread<KMAX>(b, r, w, twin_slot, inst, v, avail, sl, FIN, CNT, PEAK ? AMIN : -1, to, kRouteTwin);
   }
@@ -617,6 +636,8 @@ __global__ void DLS_S_BOUNDS(kTPB) sched_stream_kernel(dls_batch_t b, dls_result
 // The kernel therefore keeps one count per node and nothing per param. (The `cached` extension output needs the
 // identities; asking for it selects the warp-per-DAG kernel, which keeps them.) Rounds 1b-1f kept 4 bits per param in
 // shared memory to replay the eviction order: 24 KB per warp, 6 warps per SM, 7 ms per 131k instances.
+// (Available memory in the slab, as in the kernel above, was measured here too: the slab grows to 16 KB per warp, six
+// CTAs per SM instead of seven, and the eviction path writes every node back: 2.22 -> 2.78 ms.)
 // -------------------------------------------------------------------------------------------------------------------
 
 // evict_params_for_task (ref schedulers.py:404-442) on one node, as arithmetic. Each of the node's `ncached` params
@@ -978,8 +999,8 @@ int bitmap_words(int n_max) {
   return wds <= kBitmapWordsMax ? wds : 0;
 }
 template <int KMAX>
-size_t smem_simple(bool peak, int bm_words) {
-  return (size_t)(kTPB / 32) * ((size_t)(peak ? 3 : 2) * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX + bm_words) * 32 * 4);
+size_t smem_simple(bool peak, int bm_words, bool critical = false) {
+  return (size_t)(kTPB / 32) * ((size_t)((peak ? 3 : 2) + (critical ? 1 : 0)) * KMAX * 32 * 8 + (size_t)(kSharedCap / 4 + KMAX + bm_words) * 32 * 4);
 }
 template <int KMAX>
 size_t smem_mru(bool peak, int bm_words) {
@@ -1050,7 +1071,7 @@ static cudaError_t launch_stream_sched_k(const dls_batch_t& b, const dls_result_
   }
   if (algo_mask & (1 << DLS_ALGO_CRITICAL)) {
     e = launch_fast(sched_stream_kernel<DLS_ALGO_CRITICAL, KMAX, PEAK>, DLS_KERNEL_STREAM_CRITICAL, grid, kTPB,
-                    smem_simple<KMAX>(PEAK, bmw), ctx, b, r, w, slot, 0, 0, bmw);
+                    smem_simple<KMAX>(PEAK, bmw, true), ctx, b, r, w, slot, 0, 0, bmw);
     if (e != cudaSuccess) return e;
     sk.kind[slot++] = kOrderCP;
   }
